@@ -1,0 +1,98 @@
+/* tnk.h - C ABI of the B200 exact-KSD hot path (libtnk_b200.so).
+ *
+ * The reference (sozoluffy/TensorNetworks) is pure Python and has no FFI; the boundary it
+ * offers is its module API.  Each entry point below replaces the body of one reference
+ * function (or loop) on the path; the Python shim in tensornetworks_b200/ keeps the
+ * reference signatures and calls these through ctypes.
+ *
+ * Conventions: every function returns 0 on success, non-zero on failure with the message
+ * available from tnk_last_error() (thread-local).  Pointers marked "device" are CUDA
+ * device pointers owned by the caller and valid on `stream`'s device; nothing is allocated
+ * or freed behind the caller's back; all work is enqueued on `stream` (a cudaStream_t
+ * passed as void*) and the call returns without synchronising unless stated.
+ */
+#ifndef TNK_H
+#define TNK_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* precision modes of the pair kernel */
+#define TNK_PREC_FP64 0        /* DFMA pair arithmetic, fp64 accumulation (1e-6 parity mode) */
+#define TNK_PREC_FP32 1        /* FFMA pair arithmetic, fp64 accumulation across tiles (1e-4 mode) */
+#define TNK_PREC_FP64_SIMPLE 2 /* one-thread-per-row fp64 check kernel (debug / cross-check only) */
+
+/* node kinds of the flattened network (tnk_bn_joint) */
+#define TNK_NODE_LATENT 0 /* value = bit `arg` of the packed state index            */
+#define TNK_NODE_CONST 1  /* value = `arg` (clamped evidence)                       */
+#define TNK_NODE_HIDDEN 2 /* value = bit `arg` of the hidden-assignment counter     */
+
+#define TNK_MAX_NODES 64
+#define TNK_MAX_LATENT 30
+
+const char* tnk_last_error(void);
+int tnk_version(void);
+
+/* p(x,z) for all 2^n latent states, evidence clamped, hidden nodes summed out.
+ * Replaces the 2^n calls of compute_prob_joint_xz (reference stein_utils.py:58-112), each of
+ * which calls BayesianNetwork.get_joint_probability (bayesian_network.py:111-146) 2^m times.
+ * Bit-exact: the product runs over nodes in bn.nodes order from 1.0 and the hidden sum over
+ * generate_all_binary_outcomes(m) order from 0.0, in non-fused IEEE fp64.
+ *   node_kind,node_arg [n_nodes] device int32;  pa_off [n_nodes+1], pa_idx [pa_off[n_nodes]]
+ *   device int32 (parents in CPT-key order, most significant first);  cpt_off [n_nodes] device
+ *   int32 (row offset of the node's table);  cpt device double [rows][2] = {P(v=0|cfg),P(v=1|cfg)}.
+ *   P: device double [2^n_latent] (out). */
+int tnk_bn_joint(int n_latent, int n_hidden, int n_nodes,
+                 const int32_t* node_kind, const int32_t* node_arg,
+                 const int32_t* pa_off, const int32_t* pa_idx,
+                 const int32_t* cpt_off, const double* cpt,
+                 double* P, void* stream);
+
+/* Layout of the packed score table consumed by tnk_ksd_rows for (n, precision):
+ *   *np      padded score-vector length (multiple of 4, >= n)
+ *   *n_pad   number of rows of the packed table (2^n rounded up to the tile granularity)
+ *   *elem    bytes per element (4 or 8) */
+int tnk_ksd_layout(int n_latent, int precision, int* np, int64_t* n_pad, int* elem);
+
+/* Discrete score function for all states from the joint table.
+ * Replaces _precompute_all_s_p (reference ksd_vi.py:55-60) = 2^n calls of
+ * get_score_function_sp_for_z (stein_utils.py:115-136): S[z][k] = 1 - P[z ^ (1<<(n-1-k))]/P[z],
+ * the whole row zero where |P[z]| < 1e-12.  Non-fused fp64 division then subtraction (bit-exact).
+ *   S64    device double [2^n][n], latent-variable order (may be NULL)
+ *   ST     device [n_pad][np] of float/double per `precision`, indexed by BIT position
+ *          (column p = latent variable n-1-p), zero padded (may be NULL)
+ *   Cst    device [n_pad] same type: alpha*R(z) + gamma*rho0(z) (NULL iff ST NULL) */
+int tnk_score(int n_latent, double length_scale, const double* P,
+              double* S64, int precision, void* ST, void* Cst, void* stream);
+
+/* Bytes of caller-provided workspace tnk_ksd_rows needs for this row range. */
+size_t tnk_ksd_workspace_bytes(int n_latent, int precision, int64_t row_begin, int64_t row_end);
+
+/* Rows [row_begin,row_end) of u = K_p q and the partial sum_{i in rows} q_i u_i.
+ * Replaces the O(4^n) double loop of reference ksd_vi.py:114-131 (== ksd_vi_quantum.py:125-142),
+ * i.e. 4^n calls of get_stein_kernel_kp_value (stein_utils.py:138-197), and the autograd pass
+ * of ksd_vi.py:145: K = sum of the partials over all row ranges, dK/dq = 2u.
+ *   q        device [2^n], q_dtype 0 = double, 1 = float
+ *   ST,Cst   from tnk_score with the same (n, length_scale, precision)
+ *   u        device double [2^n]; only rows [row_begin,row_end) are written
+ *   ksd_part device double [1] (out)
+ *   n_launch optional host int*: number of kernels enqueued (for gpu_launches accounting) */
+int tnk_ksd_rows(int n_latent, double length_scale, int precision,
+                 const void* q, int q_dtype, const void* ST, const void* Cst,
+                 int64_t row_begin, int64_t row_end,
+                 double* u, double* ksd_part,
+                 void* workspace, size_t workspace_bytes, int* n_launch, void* stream);
+
+/* ALU roofline probe: runs a dependent-chain FMA kernel (precision 0: DFMA, 1: FFMA) that
+ * fills the chip, times it with CUDA events on `stream` (synchronises) and returns the
+ * achieved lane-ops/s (one FMA on one lane = 1).  scratch: device double [>= 1]. */
+int tnk_alu_peak(int precision, int iters, double* scratch, double* lane_ops_per_s, float* ms, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* TNK_H */
