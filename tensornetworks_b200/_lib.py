@@ -1,0 +1,115 @@
+"""Build and load libtnk_b200.so (the C-ABI of include/tnk.h) through ctypes.
+
+The library is built in-tree (tensornetworks_b200/libtnk_b200.so) with
+    nvcc -gencode arch=compute_100a,code=sm_100a -lineinfo
+so it travels with the repo snapshot to the GPU box.  There is no CPU fallback: if the
+library cannot be loaded every compute entry point raises.
+"""
+import ctypes
+import os
+import shutil
+import subprocess
+from concurrent.futures import ThreadPoolExecutor
+
+PKG_DIR = os.path.dirname(os.path.abspath(__file__))
+REPO_DIR = os.path.dirname(PKG_DIR)
+CSRC = os.path.join(PKG_DIR, "csrc")
+INCLUDE = os.path.join(REPO_DIR, "include")
+LIB_PATH = os.path.join(PKG_DIR, "libtnk_b200.so")
+SOURCES = ["tnk_enum.cu", "tnk_ksd.cu", "tnk_peak.cu"]
+NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
+              "-Xcompiler", "-fPIC", "-I", INCLUDE]
+
+PREC_FP64, PREC_FP32, PREC_FP64_SIMPLE = 0, 1, 2
+
+# every symbol include/tnk.h declares
+EXPORTS = ["tnk_last_error", "tnk_version", "tnk_bn_joint", "tnk_ksd_layout", "tnk_score",
+           "tnk_ksd_workspace_bytes", "tnk_ksd_rows", "tnk_alu_peak"]
+
+
+def _nvcc():
+    return shutil.which("nvcc") or "/usr/local/cuda/bin/nvcc"
+
+
+def _stale():
+    if not os.path.exists(LIB_PATH):
+        return True
+    built = os.path.getmtime(LIB_PATH)
+    deps = [os.path.join(CSRC, f) for f in os.listdir(CSRC)] + [os.path.join(INCLUDE, "tnk.h")]
+    return any(os.path.getmtime(d) > built for d in deps)
+
+
+def build(force=False, verbose=False):
+    """Compile the CUDA sources for sm_100a and link the shared library (no GPU needed)."""
+    if not force and not _stale():
+        return LIB_PATH
+    obj_dir = os.path.join(PKG_DIR, "build")
+    os.makedirs(obj_dir, exist_ok=True)
+
+    def compile_one(src):
+        obj = os.path.join(obj_dir, src.replace(".cu", ".o"))
+        cmd = [_nvcc(), *NVCC_FLAGS, "-c", os.path.join(CSRC, src), "-o", obj]
+        res = subprocess.run(cmd, capture_output=True, text=True)
+        if res.returncode != 0:
+            raise RuntimeError(f"nvcc failed for {src}:\n{res.stdout}\n{res.stderr}")
+        if verbose:
+            print(" ".join(cmd))
+        return obj
+
+    with ThreadPoolExecutor(max_workers=len(SOURCES)) as pool:
+        objs = list(pool.map(compile_one, SOURCES))
+    cmd = [_nvcc(), "-shared", "-o", LIB_PATH, *objs, "-lcudart"]
+    res = subprocess.run(cmd, capture_output=True, text=True)
+    if res.returncode != 0:
+        raise RuntimeError(f"link failed:\n{res.stdout}\n{res.stderr}")
+    return LIB_PATH
+
+
+_lib = None
+
+
+def load():
+    """Return the ctypes handle, building first if the .so is missing or stale."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if _stale():
+        try:
+            build()
+        except Exception as exc:  # no toolchain: refuse loudly, never fall back
+            if not os.path.exists(LIB_PATH):
+                raise RuntimeError(f"libtnk_b200.so is missing and could not be built: {exc}") from exc
+    lib = ctypes.CDLL(LIB_PATH)
+    c_int, c_i64, c_dbl, c_vp, c_sz = ctypes.c_int, ctypes.c_int64, ctypes.c_double, ctypes.c_void_p, ctypes.c_size_t
+    lib.tnk_last_error.restype = ctypes.c_char_p
+    lib.tnk_last_error.argtypes = []
+    lib.tnk_version.restype = c_int
+    lib.tnk_bn_joint.restype = c_int
+    lib.tnk_bn_joint.argtypes = [c_int, c_int, c_int, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp]
+    lib.tnk_ksd_layout.restype = c_int
+    lib.tnk_ksd_layout.argtypes = [c_int, c_int, ctypes.POINTER(c_int), ctypes.POINTER(c_i64), ctypes.POINTER(c_int)]
+    lib.tnk_score.restype = c_int
+    lib.tnk_score.argtypes = [c_int, c_dbl, c_vp, c_vp, c_int, c_vp, c_vp, c_vp]
+    lib.tnk_ksd_workspace_bytes.restype = c_sz
+    lib.tnk_ksd_workspace_bytes.argtypes = [c_int, c_int, c_i64, c_i64]
+    lib.tnk_ksd_rows.restype = c_int
+    lib.tnk_ksd_rows.argtypes = [c_int, c_dbl, c_int, c_vp, c_int, c_vp, c_vp, c_i64, c_i64, c_vp, c_vp,
+                                 c_vp, c_sz, ctypes.POINTER(c_int), c_vp]
+    lib.tnk_alu_peak.restype = c_int
+    lib.tnk_alu_peak.argtypes = [c_int, c_int, c_vp, ctypes.POINTER(c_dbl), ctypes.POINTER(ctypes.c_float), c_vp]
+    _lib = lib
+    return lib
+
+
+def check(rc, what):
+    if rc != 0:
+        msg = load().tnk_last_error().decode("utf-8", "replace")
+        raise RuntimeError(f"{what} failed (code {rc}): {msg}")
+
+
+def layout(n, precision):
+    """(np, n_pad, elem_bytes) of the packed score table for (n, precision)."""
+    lib = load()
+    np_, n_pad, elem = ctypes.c_int(), ctypes.c_int64(), ctypes.c_int()
+    check(lib.tnk_ksd_layout(n, precision, ctypes.byref(np_), ctypes.byref(n_pad), ctypes.byref(elem)), "tnk_ksd_layout")
+    return np_.value, n_pad.value, elem.value

@@ -1,0 +1,187 @@
+// Enumeration kernels: K1 joint table p(x,z) and K2 score / packed-table builder.
+// HBM-bound streaming kernels over the 2^n packed states (one thread per state).
+#include "tnk_common.cuh"
+
+static thread_local char g_err[512] = "";
+
+void tnk_set_error(const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+
+extern "C" const char* tnk_last_error(void) { return g_err; }
+extern "C" int tnk_version(void) { return 100; }
+
+extern "C" int tnk_ksd_layout(int n_latent, int precision, int* np, int64_t* n_pad, int* elem) {
+    TnkGeom g;
+    TNK_REQUIRE(tnk_geom(n_latent, precision, &g) == 0, "tnk_ksd_layout: unsupported n=%d precision=%d", n_latent, precision);
+    if (np) *np = g.np;
+    if (n_pad) *n_pad = g.n_pad;
+    if (elem) *elem = g.elem;
+    return 0;
+}
+
+// ------------------------------------------------------------------------------------
+// K1.  Replaces compute_prob_joint_xz (reference stein_utils.py:58-112) for every state.
+// The network descriptor is tiny and identical for all threads: it is staged in shared
+// memory once per CTA; each thread then walks the nodes in bn.nodes order.
+// ------------------------------------------------------------------------------------
+struct BnDesc {
+    int32_t kind[TNK_MAX_NODES];
+    int32_t arg[TNK_MAX_NODES];
+    int32_t pa_off[TNK_MAX_NODES + 1];
+    int32_t cpt_off[TNK_MAX_NODES];
+};
+
+__global__ void __launch_bounds__(256)
+bn_joint_kernel(int n_latent, int n_hidden, int n_nodes,
+                const int32_t* __restrict__ node_kind, const int32_t* __restrict__ node_arg,
+                const int32_t* __restrict__ pa_off, const int32_t* __restrict__ pa_idx,
+                const int32_t* __restrict__ cpt_off, const double* __restrict__ cpt,
+                double* __restrict__ P) {
+    __shared__ BnDesc d;
+    extern __shared__ int32_t s_pa[];  // parent lists
+    for (int v = threadIdx.x; v < n_nodes; v += blockDim.x) {
+        d.kind[v] = node_kind[v];
+        d.arg[v] = node_arg[v];
+        d.cpt_off[v] = cpt_off[v];
+    }
+    for (int v = threadIdx.x; v <= n_nodes; v += blockDim.x) d.pa_off[v] = pa_off[v];
+    __syncthreads();
+    const int n_pa = d.pa_off[n_nodes];
+    for (int t = threadIdx.x; t < n_pa; t += blockDim.x) s_pa[t] = pa_idx[t];
+    __syncthreads();
+
+    const int64_t N = (int64_t)1 << n_latent;
+    const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= N) return;
+
+    // node values that do not depend on the hidden assignment
+    uint64_t fixed = 0;
+    for (int v = 0; v < n_nodes; ++v) {
+        uint64_t bit = 0;
+        if (d.kind[v] == TNK_NODE_LATENT) bit = (uint64_t)(idx >> d.arg[v]) & 1u;
+        else if (d.kind[v] == TNK_NODE_CONST) bit = (uint64_t)(d.arg[v] & 1);
+        fixed |= bit << v;
+    }
+    const uint32_t n_hid_cfg = 1u << n_hidden;
+    double total = 0.0;
+    for (uint32_t hcfg = 0; hcfg < n_hid_cfg; ++hcfg) {
+        uint64_t assign = fixed;
+        if (n_hidden) {
+            for (int v = 0; v < n_nodes; ++v)
+                if (d.kind[v] == TNK_NODE_HIDDEN) assign |= (uint64_t)((hcfg >> d.arg[v]) & 1u) << v;
+        }
+        double prob = 1.0;  // bayesian_network.py:129
+        for (int v = 0; v < n_nodes; ++v) {
+            int cfg = 0;
+            for (int t = d.pa_off[v]; t < d.pa_off[v + 1]; ++t)
+                cfg = (cfg << 1) | (int)((assign >> s_pa[t]) & 1u);
+            const int val = (int)((assign >> v) & 1u);
+            prob = __dmul_rn(prob, __ldg(&cpt[2 * ((int64_t)d.cpt_off[v] + cfg) + val]));  // :144
+        }
+        total = (n_hidden == 0) ? prob : __dadd_rn(total, prob);  // stein_utils.py:96-111
+    }
+    P[idx] = total;
+}
+
+extern "C" int tnk_bn_joint(int n_latent, int n_hidden, int n_nodes,
+                            const int32_t* node_kind, const int32_t* node_arg,
+                            const int32_t* pa_off, const int32_t* pa_idx,
+                            const int32_t* cpt_off, const double* cpt,
+                            double* P, void* stream) {
+    TNK_REQUIRE(n_latent >= 0 && n_latent <= TNK_MAX_LATENT, "tnk_bn_joint: n_latent=%d out of range", n_latent);
+    TNK_REQUIRE(n_hidden >= 0 && n_hidden <= 20, "tnk_bn_joint: n_hidden=%d out of range", n_hidden);
+    TNK_REQUIRE(n_nodes >= 0 && n_nodes <= TNK_MAX_NODES, "tnk_bn_joint: n_nodes=%d exceeds %d", n_nodes, TNK_MAX_NODES);
+    TNK_REQUIRE(P != nullptr, "tnk_bn_joint: P is NULL");
+    int32_t n_pa = 0;
+    if (n_nodes > 0) {
+        TNK_CUDA_OK(cudaMemcpyAsync(&n_pa, pa_off + n_nodes, sizeof(int32_t), cudaMemcpyDeviceToHost, (cudaStream_t)stream));
+        TNK_CUDA_OK(cudaStreamSynchronize((cudaStream_t)stream));
+    }
+    TNK_REQUIRE(n_pa >= 0 && n_pa <= 8192, "tnk_bn_joint: %d parent references exceed the 8192 limit", n_pa);
+    const int64_t N = (int64_t)1 << n_latent;
+    const unsigned blocks = (unsigned)((N + 255) / 256);
+    bn_joint_kernel<<<blocks, 256, (size_t)(n_pa + 1) * sizeof(int32_t), (cudaStream_t)stream>>>(
+        n_latent, n_hidden, n_nodes, node_kind, node_arg, pa_off, pa_idx, cpt_off, cpt, P);
+    TNK_CUDA_OK(cudaGetLastError());
+    return 0;
+}
+
+// ------------------------------------------------------------------------------------
+// K2.  Replaces get_score_function_sp_for_z (reference stein_utils.py:115-136) for every
+// state and emits the packed operands of the pair kernel.  flip_bit(z,k) is
+// idx ^ (1 << (n-1-k)), so the n neighbour probabilities are gathers from P itself.
+// Each CTA computes 256 rows into shared memory and writes them out coalesced.
+// ------------------------------------------------------------------------------------
+template <typename T>
+__global__ void __launch_bounds__(256)
+score_kernel(int n, int np, int64_t N, double alpha, double gamma,
+             const double* __restrict__ P, double* __restrict__ S64,
+             T* __restrict__ ST, T* __restrict__ Cst) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    double* sS = reinterpret_cast<double*>(smem_raw);                       // [256][n]
+    T* sT = reinterpret_cast<T*>(smem_raw + (size_t)256 * n * sizeof(double));  // [256][np]
+    const int tid = threadIdx.x;
+    const int64_t base = (int64_t)blockIdx.x * 256;
+    const int64_t i = base + tid;
+    double Rsum = 0.0, rho0 = 0.0;
+    if (ST) for (int p = 0; p < np; ++p) sT[tid * np + p] = (T)0;
+    if (i < N) {
+        const double p = P[i];
+        const bool dead = fabs(p) < 1e-12;  // stein_utils.py:126
+        for (int k = 0; k < n; ++k) {
+            const int bit = n - 1 - k;
+            double s = 0.0;
+            if (!dead) s = __dsub_rn(1.0, __ddiv_rn(P[i ^ ((int64_t)1 << bit)], p));  // :134
+            if (S64) sS[tid * n + k] = s;
+            if (ST) sT[tid * np + bit] = (T)s;
+            const double r = 1.0 - s;
+            Rsum += r;
+            if ((i >> bit) & 1) rho0 += r;
+        }
+        if (Cst) Cst[i] = (T)(alpha * Rsum + gamma * rho0);
+    } else if (Cst) {
+        Cst[i] = (T)0;  // padding rows of the packed table
+    }
+    __syncthreads();
+    if (S64) {
+        const int64_t live = (N - base < 256 ? (N - base > 0 ? N - base : 0) : 256) * n;
+        for (int64_t t = tid; t < live; t += 256) S64[base * n + t] = sS[t];
+    }
+    if (ST) {
+        for (int t = tid; t < 256 * np; t += 256) ST[base * np + t] = sT[t];
+    }
+}
+
+extern "C" int tnk_score(int n_latent, double length_scale, const double* P,
+                         double* S64, int precision, void* ST, void* Cst, void* stream) {
+    TnkGeom g;
+    TNK_REQUIRE(tnk_geom(n_latent, precision, &g) == 0, "tnk_score: unsupported n=%d precision=%d", n_latent, precision);
+    TNK_REQUIRE(P != nullptr, "tnk_score: P is NULL");
+    TNK_REQUIRE((ST == nullptr) == (Cst == nullptr), "tnk_score: ST and Cst must both be given or both NULL");
+    const int n = n_latent;
+    const int64_t N = (int64_t)1 << n;
+    double alpha = 0.0, gamma = 0.0;
+    if (n > 0) {
+        TNK_REQUIRE((double)n * length_scale != 0.0, "tnk_score: num_vars*length_scale must be non-zero");
+        const double a = exp(-1.0 / ((double)n * length_scale));
+        alpha = 1.0 - a;
+        gamma = a - 1.0 / a;
+    }
+    const int64_t rows = ST ? g.n_pad : N;
+    const unsigned blocks = (unsigned)((rows + 255) / 256);
+    const size_t smem = (size_t)256 * ((size_t)n * sizeof(double) + (size_t)g.np * g.elem);
+    cudaStream_t st = (cudaStream_t)stream;
+    if (g.elem == 4) {
+        TNK_CUDA_OK(cudaFuncSetAttribute(score_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        score_kernel<float><<<blocks, 256, smem, st>>>(n, g.np, N, alpha, gamma, P, S64, (float*)ST, (float*)Cst);
+    } else {
+        TNK_CUDA_OK(cudaFuncSetAttribute(score_kernel<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        score_kernel<double><<<blocks, 256, smem, st>>>(n, g.np, N, alpha, gamma, P, S64, (double*)ST, (double*)Cst);
+    }
+    TNK_CUDA_OK(cudaGetLastError());
+    return 0;
+}

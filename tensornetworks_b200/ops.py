@@ -1,0 +1,208 @@
+"""Batched entry points of the exact-KSD path on top of the C-ABI (include/tnk.h).
+
+  joint_table      2^n calls of compute_prob_joint_xz          (reference stein_utils.py:58-112)
+  SteinTables      _precompute_all_s_p                         (reference ksd_vi.py:55-60)
+  ksd_quadratic_form   the O(4^n) loop + autograd backward     (reference ksd_vi.py:110-131,145)
+
+All arithmetic runs in libtnk_b200.so on the current CUDA device; torch only owns the
+memory, the stream and (for several GPUs) the process group.  No CPU fallback exists.
+"""
+import ctypes
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+from . import _lib
+from .flatten import flatten_bn
+
+PRECISIONS = {"fp64": _lib.PREC_FP64, "fp32": _lib.PREC_FP32, "fp64_simple": _lib.PREC_FP64_SIMPLE}
+launch_counter = {"kernels": 0}  # kernels of ours enqueued since last reset (bench.py's gpu_launches)
+
+
+def _require_cuda(device):
+    device = torch.device(device)
+    if device.type != "cuda" or not torch.cuda.is_available():
+        raise RuntimeError("the exact-KSD path runs on a CUDA device only (B200, sm_100a); there is no CPU fallback")
+    return device
+
+
+def _stream_ptr(device):
+    return ctypes.c_void_p(torch.cuda.current_stream(device).cuda_stream)
+
+
+def _ptr(t):
+    return ctypes.c_void_p(t.data_ptr()) if t is not None else ctypes.c_void_p(0)
+
+
+def joint_table(bn, x_dict, latent_vars_names, device="cuda", n_latent=None):
+    """p(x,z) for every latent state, fp64 tensor [2^n] on `device`, enumeration order
+    (bit-exact with compute_prob_joint_xz, reference stein_utils.py:58-112)."""
+    device = _require_cuda(device)
+    flat = flatten_bn(bn, x_dict, latent_vars_names, n_latent=n_latent)
+    lib = _lib.load()
+    with torch.cuda.device(device):
+        dev = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(device)
+        kind, arg, pa_off, cpt_off = dev(flat.node_kind), dev(flat.node_arg), dev(flat.pa_off), dev(flat.cpt_off)
+        pa_idx = dev(flat.pa_idx) if flat.pa_idx.size else torch.zeros(1, dtype=torch.int32, device=device)
+        cpt = dev(flat.cpt) if flat.cpt.size else torch.zeros((1, 2), dtype=torch.float64, device=device)
+        P = torch.empty(1 << flat.n_latent, dtype=torch.float64, device=device)
+        _lib.check(lib.tnk_bn_joint(flat.n_latent, flat.n_hidden, flat.n_nodes, _ptr(kind), _ptr(arg), _ptr(pa_off),
+                                    _ptr(pa_idx), _ptr(cpt_off), _ptr(cpt), _ptr(P), _stream_ptr(device)), "tnk_bn_joint")
+        launch_counter["kernels"] += 1
+        if np.isnan(flat.cpt).any() and bool(torch.isnan(P).any()):
+            raise ValueError("CPT entry for a node/parent configuration that the enumeration reaches was not found.")
+    return P
+
+
+class SteinTables:
+    """Device-resident, per-(network, evidence) operands of the pair kernel.
+
+    P    fp64 [N]        joint table p(x,z)
+    S    fp64 [N, n]     score table in latent-variable order (None unless keep_scores)
+    ST   [n_pad, np]     packed scores by bit position in the compute dtype
+    Cst  [n_pad]         alpha*R(z) + gamma*rho0(z)
+    """
+
+    def __init__(self, P, n, length_scale=1.0, precision="fp32", keep_scores=False):
+        if precision not in PRECISIONS:
+            raise ValueError(f"precision must be one of {sorted(PRECISIONS)}")
+        device = _require_cuda(P.device)
+        if P.dtype != torch.float64 or P.numel() != (1 << n):
+            raise ValueError("P must be a float64 tensor with 2^n entries")
+        self.n, self.length_scale, self.precision = int(n), float(length_scale), precision
+        self.prec_code = PRECISIONS[precision]
+        self.device, self.N = device, 1 << n
+        self.P = P.contiguous()
+        lib = _lib.load()
+        np_, n_pad, elem = _lib.layout(self.n, self.prec_code)
+        dtype = torch.float32 if elem == 4 else torch.float64
+        self.np, self.n_pad, self.dtype = np_, n_pad, dtype
+        with torch.cuda.device(device):
+            self.S = torch.empty((self.N, self.n), dtype=torch.float64, device=device) if keep_scores else None
+            self.ST = torch.empty((n_pad, np_), dtype=dtype, device=device)
+            self.Cst = torch.empty(n_pad, dtype=dtype, device=device)
+            _lib.check(lib.tnk_score(self.n, self.length_scale, _ptr(self.P), _ptr(self.S), self.prec_code,
+                                     _ptr(self.ST), _ptr(self.Cst), _stream_ptr(device)), "tnk_score")
+            launch_counter["kernels"] += 1
+        self._ws = {}
+
+    @classmethod
+    def from_network(cls, bn, x_dict, latent_vars_names, length_scale=1.0, precision="fp32",
+                     device="cuda", keep_scores=False, n_latent=None):
+        n = len(latent_vars_names) if n_latent is None else int(n_latent)
+        P = joint_table(bn, x_dict, latent_vars_names, device=device, n_latent=n)
+        return cls(P, n, length_scale=length_scale, precision=precision, keep_scores=keep_scores)
+
+    def posterior(self):
+        """p(z|x) = P / sum(P) as an fp64 device tensor (tensor form of get_true_posterior)."""
+        return self.P / self.P.sum()
+
+    def workspace(self, row_begin, row_end):
+        key = (row_begin, row_end)
+        if key not in self._ws:
+            nbytes = _lib.load().tnk_ksd_workspace_bytes(self.n, self.prec_code, row_begin, row_end)
+            if nbytes == 0:
+                raise RuntimeError("tnk_ksd_workspace_bytes rejected the row range")
+            self._ws[key] = torch.empty(nbytes, dtype=torch.uint8, device=self.device)
+        return self._ws[key]
+
+    def ksd_rows(self, q, row_begin=0, row_end=None, u=None):
+        """u[row_begin:row_end] = (K_p q)[rows] and the partial sum_i q_i u_i over those rows.
+        q: fp32/fp64 CUDA tensor [N].  Returns (u [N] fp64 - only the row range is written, part [1] fp64)."""
+        row_end = self.N if row_end is None else row_end
+        if q.device != self.device or q.dim() != 1 or q.numel() != self.N:
+            raise ValueError(f"q must be a 1-D tensor of {self.N} entries on {self.device}")
+        if q.dtype not in (torch.float32, torch.float64):
+            raise ValueError("q must be float32 or float64")
+        q = q.contiguous()
+        lib = _lib.load()
+        with torch.cuda.device(self.device):
+            if u is None:
+                u = torch.empty(self.N, dtype=torch.float64, device=self.device)
+            part = torch.empty(1, dtype=torch.float64, device=self.device)
+            ws = self.workspace(row_begin, row_end)
+            launched = ctypes.c_int(0)
+            _lib.check(lib.tnk_ksd_rows(self.n, self.length_scale, self.prec_code, _ptr(q),
+                                        0 if q.dtype == torch.float64 else 1, _ptr(self.ST), _ptr(self.Cst),
+                                        row_begin, row_end, _ptr(u), _ptr(part), _ptr(ws), ws.numel(),
+                                        ctypes.byref(launched), _stream_ptr(self.device)), "tnk_ksd_rows")
+            launch_counter["kernels"] += launched.value
+        return u, part
+
+
+def shard_rows(num_states, rank, world):
+    """Contiguous row block of rank `rank` among `world` ranks."""
+    return (num_states * rank) // world, (num_states * (rank + 1)) // world
+
+
+def combine_row_shards(u_rows, part, num_states, rank, world, group=None):
+    """Exchange step of the sharded evaluation: every rank contributes its rows of u = K_p q and
+    its partial of q.u, every rank receives the full u [N] and K [1].  One all_gather of
+    [rows | partial] blocks when the rows divide evenly, else one sum-all_reduce of a padded
+    vector.  Backend-neutral (NCCL on the GPUs, gloo in the CPU tests)."""
+    if world == 1:
+        return u_rows, part.clone()
+    r0, r1 = shard_rows(num_states, rank, world)
+    if u_rows.numel() != r1 - r0:
+        raise ValueError("u_rows does not match this rank's row block")
+    if num_states % world == 0:
+        block = torch.cat([u_rows, part.reshape(1)])
+        gathered = torch.empty(world * block.numel(), dtype=block.dtype, device=block.device)
+        dist.all_gather_into_tensor(gathered, block, group=group)
+        gathered = gathered.view(world, -1)
+        return gathered[:, :-1].reshape(-1), gathered[:, -1].sum().reshape(1)
+    buf = torch.zeros(num_states + 1, dtype=u_rows.dtype, device=u_rows.device)
+    buf[r0:r1] = u_rows
+    buf[num_states] = part.reshape(())
+    dist.all_reduce(buf, op=dist.ReduceOp.SUM, group=group)
+    return buf[:num_states], buf[num_states:].clone()
+
+
+class _KsdQuadraticForm(torch.autograd.Function):
+    """K(q) = q^T K_p q with dK/dq = 2 K_p q, one pass over the pair space for both."""
+
+    @staticmethod
+    def forward(ctx, q, tables, group):
+        q_dev = q.detach()
+        if q_dev.dtype not in (torch.float32, torch.float64):
+            q_dev = q_dev.to(torch.float64)
+        q_dev = q_dev.to(tables.device)
+        world = dist.get_world_size(group) if (dist.is_available() and dist.is_initialized()) else 1
+        rank = dist.get_rank(group) if world > 1 else 0
+        r0, r1 = shard_rows(tables.N, rank, world)
+        u, part = tables.ksd_rows(q_dev, r0, r1)
+        if world > 1:
+            u, part = combine_row_shards(u[r0:r1], part, tables.N, rank, world, group)
+        ctx.save_for_backward(u)
+        ctx.q_meta = (q.dtype, q.device)
+        return part.reshape(()).to(q.device)
+
+    @staticmethod
+    def backward(ctx, grad_out):
+        (u,) = ctx.saved_tensors
+        dtype, device = ctx.q_meta
+        grad = (2.0 * grad_out.to(u.device, torch.float64)) * u
+        return grad.to(device=device, dtype=dtype), None, None
+
+
+def ksd_quadratic_form(q, tables, group=None):
+    """KSD^2 = sum_ij q_i q_j k_p(z_i, z_j) as an fp64 scalar tensor on q's device, differentiable
+    w.r.t. q (any float dtype, CPU or CUDA; e.g. PennyLane probabilities).  Drop-in for the double
+    loop of reference ksd_vi.py:110-131 / ksd_vi_quantum.py:122-142.  When torch.distributed is
+    initialised the rows of the pair space are sharded over the ranks of `group`."""
+    if q.dim() != 1 or q.numel() != tables.N:
+        raise ValueError(f"Probabilities shape mismatch: {tuple(q.shape)}")
+    return _KsdQuadraticForm.apply(q, tables, group)
+
+
+def alu_peak(precision="fp32", iters=4096, device="cuda"):
+    """Measured FMA-chain rate of the device in lane-ops/s (the pair kernel's roofline denominator)."""
+    device = _require_cuda(device)
+    lib = _lib.load()
+    with torch.cuda.device(device):
+        scratch = torch.zeros(8, dtype=torch.float64, device=device)
+        rate, ms = ctypes.c_double(0.0), ctypes.c_float(0.0)
+        _lib.check(lib.tnk_alu_peak(PRECISIONS[precision], iters, _ptr(scratch), ctypes.byref(rate),
+                                    ctypes.byref(ms), _stream_ptr(device)), "tnk_alu_peak")
+    return rate.value, ms.value

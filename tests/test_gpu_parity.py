@@ -1,0 +1,164 @@
+"""GPU parity tests: the CUDA path (through the C-ABI) against the oracle and the
+reference-generated goldens.  Tolerances are BASELINE.json's: enumeration bit-exact;
+KSD^2 and gradient (normwise) 1e-6 in fp64 mode, 1e-4 in fp32 mode."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import ksd_oracle as orc
+from tensornetworks_b200.bayesian_network import BayesianNetwork, get_sprinkler_network
+from tensornetworks_b200.synthetic import random_binary_bn, random_q
+
+pytestmark = pytest.mark.gpu
+
+TOL = {"fp64": 1e-6, "fp32": 1e-4, "fp64_simple": 1e-6}
+RANDOM_CASES = [(n, n, 0) for n in range(2, 7)] + [(4, 104, 2)]
+TABLE_CASES = [(10, 0, 0), (10, 1, 2), (8, 7, 1)]
+
+
+@pytest.fixture(scope="module")
+def ops():
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    from tensornetworks_b200 import ops as _ops
+    return _ops
+
+
+def _tables(ops, bn, x, lat, precision, length_scale=1.0):
+    return ops.SteinTables.from_network(bn, x, lat, length_scale=length_scale, precision=precision, keep_scores=True)
+
+
+def _check(K, g, Kref, gref, tol, Kscale=None):
+    scale = abs(Kref) if Kscale is None else Kscale
+    assert abs(K - Kref) <= tol * scale, (K, Kref)
+    assert np.max(np.abs(g - gref)) <= tol * np.max(np.abs(gref)), np.max(np.abs(g - gref)) / np.max(np.abs(gref))
+
+
+def _eval(ops, tabs, q):
+    qd = torch.as_tensor(q, dtype=torch.float64, device="cuda").requires_grad_(True)
+    K = ops.ksd_quadratic_form(qd, tabs)
+    K.backward()
+    return float(K.item()), qd.grad.cpu().numpy()
+
+
+def test_known_answers_ab(ops, golden):
+    bn = BayesianNetwork()
+    bn.add_node('A', cpt={(): {0: 0.8, 1: 0.2}})
+    bn.add_node('B', cpt={(0,): {0: 0.7, 1: 0.3}, (1,): {0: 0.4, 1: 0.6}}, parent_names=['A'])
+    tabs = _tables(ops, bn, {'B': 1}, ['A'], "fp64")
+    assert np.array_equal(tabs.P.cpu().numpy(), golden["ab_P"])
+    assert np.array_equal(tabs.S.cpu().numpy(), golden["ab_S"])
+    # k_p(0,1) and k_p(0,0) of stein_utils.py:245-251 through one-hot q
+    e0 = torch.tensor([1.0, 0.0], dtype=torch.float64, device="cuda")
+    u, _ = tabs.ksd_rows(e0)
+    torch.cuda.synchronize()
+    assert np.isclose(u[0].item(), 1.25 - np.exp(-1.0), rtol=1e-12)
+    assert np.isclose(u[1].item(), 2 * np.exp(-1.0) - 2.5, rtol=1e-12)
+
+
+@pytest.mark.parametrize("precision", ["fp64", "fp32", "fp64_simple"])
+def test_sprinkler(ops, golden, precision):
+    bn = get_sprinkler_network(False)
+    tabs = _tables(ops, bn, {'W': 1}, ['C', 'S', 'R'], precision)
+    assert np.array_equal(tabs.P.cpu().numpy(), golden["spr_P"])
+    assert np.array_equal(tabs.S.cpu().numpy(), golden["spr_S"])
+    for name in ("uniform", "ramp"):
+        K, g = _eval(ops, tabs, golden[f"spr_q_{name}"])
+        _check(K, g, float(golden[f"spr_K_{name}"]), golden[f"spr_g_{name}"], TOL[precision])
+    # q = exact posterior: K ~ 0, compare against the scale of the uniform-q value
+    K, g = _eval(ops, tabs, golden["spr_q_post"])
+    assert abs(K - float(golden["spr_K_post"])) <= TOL[precision] * float(golden["spr_K_uniform"])
+    for ls in (0.5, 2.0):
+        t2 = _tables(ops, bn, {'W': 1}, ['C', 'S', 'R'], precision, length_scale=ls)
+        K, g = _eval(ops, t2, golden["spr_q_ramp"])
+        _check(K, g, float(golden[f"spr_K_ramp_ls{ls}"]), golden[f"spr_g_ramp_ls{ls}"], TOL[precision])
+
+
+@pytest.mark.parametrize("precision", ["fp64", "fp32", "fp64_simple"])
+@pytest.mark.parametrize("n,seed,nh", RANDOM_CASES)
+def test_random_bn_vs_reference_loop(ops, golden, n, seed, nh, precision):
+    bn, lat, obs, x = random_binary_bn(n, seed=seed, n_hidden=nh)
+    tag = f"rnd_n{n}_s{seed}_h{nh}"
+    tabs = _tables(ops, bn, x, lat, precision)
+    assert np.array_equal(tabs.P.cpu().numpy(), golden[tag + "_P"])
+    assert np.array_equal(tabs.S.cpu().numpy(), golden[tag + "_S"])
+    K, g = _eval(ops, tabs, golden[tag + "_q"])
+    _check(K, g, float(golden[tag + "_K"]), golden[tag + "_g"], TOL[precision])
+
+
+@pytest.mark.parametrize("n,seed,nh", TABLE_CASES)
+def test_enumeration_tables_bit_exact(ops, golden, n, seed, nh):
+    bn, lat, obs, x = random_binary_bn(n, seed=seed, n_hidden=nh)
+    tag = f"tab_n{n}_s{seed}_h{nh}"
+    tabs = _tables(ops, bn, x, lat, "fp64")
+    assert np.array_equal(tabs.P.cpu().numpy(), golden[tag + "_P"])
+    assert np.array_equal(tabs.S.cpu().numpy(), golden[tag + "_S"])
+
+
+@pytest.mark.parametrize("precision", ["fp64", "fp32"])
+@pytest.mark.parametrize("n,seed", [(7, 0), (9, 1), (10, 2), (11, 3), (12, 0)])
+def test_vs_dense_oracle(ops, n, seed, precision):
+    bn, lat, obs, x = random_binary_bn(n, seed=seed)
+    tabs = _tables(ops, bn, x, lat, precision)
+    P = orc.joint_table(bn, x, lat)
+    S = orc.score_table(P, n)
+    assert np.array_equal(tabs.P.cpu().numpy(), P)
+    assert np.array_equal(tabs.S.cpu().numpy(), S)
+    q = random_q(1 << n, seed=seed).numpy()
+    Kref, gref = orc.ksd_dense(q, S, n)
+    K, g = _eval(ops, tabs, q)
+    _check(K, g, Kref, gref, TOL[precision])
+
+
+@pytest.mark.parametrize("precision", ["fp64", "fp32"])
+@pytest.mark.parametrize("n,seed", [(13, 1), (14, 2), (16, 0)])
+def test_vs_modeproduct_oracle(ops, n, seed, precision):
+    bn, lat, obs, x = random_binary_bn(n, seed=seed)
+    tabs = _tables(ops, bn, x, lat, precision)
+    P = orc.joint_table(bn, x, lat)
+    S = orc.score_table(P, n)
+    assert np.array_equal(tabs.P.cpu().numpy(), P)
+    assert np.array_equal((np.abs(P) < 1e-12), (tabs.S.cpu().numpy() == 0).all(axis=1) & (np.abs(P) < 1e-12))
+    assert np.array_equal(tabs.S.cpu().numpy(), S)
+    q = random_q(1 << n, seed=seed).numpy()
+    Kref, gref = orc.ksd_modeproduct(q, S, n)
+    K, g = _eval(ops, tabs, q)
+    _check(K, g, Kref, gref, TOL[precision])
+
+
+def test_row_ranges_add_up(ops):
+    """Sharding property: disjoint row ranges reproduce the full u and K (incl. ranges that are
+    not aligned to the kernel's row block)."""
+    n = 12
+    bn, lat, obs, x = random_binary_bn(n, seed=5)
+    tabs = _tables(ops, bn, x, lat, "fp64")
+    q = random_q(1 << n, seed=5).cuda()
+    u_full, k_full = tabs.ksd_rows(q)
+    u = torch.zeros_like(u_full)
+    parts = []
+    cuts = [0, 1000, 1024, 2500, 4096]
+    for a, b in zip(cuts[:-1], cuts[1:]):
+        _, p = tabs.ksd_rows(q, a, b, u=u)
+        parts.append(p.clone())
+    torch.cuda.synchronize()
+    assert torch.allclose(u, u_full, rtol=1e-13, atol=0)
+    assert np.isclose(sum(p.item() for p in parts), k_full.item(), rtol=1e-12)
+
+
+def test_q_dtypes_and_cpu_q(ops, golden):
+    """q may be fp32 or fp64, on CPU (PennyLane) or CUDA; grad comes back in q's dtype/device."""
+    bn = get_sprinkler_network(False)
+    tabs = _tables(ops, bn, {'W': 1}, ['C', 'S', 'R'], "fp64")
+    q32 = torch.tensor(golden["spr_q_ramp"], dtype=torch.float32, requires_grad=True)  # CPU fp32
+    K = ops.ksd_quadratic_form(q32, tabs)
+    K.backward()
+    assert K.device.type == "cpu" and K.dtype == torch.float64
+    assert q32.grad.dtype == torch.float32 and q32.grad.device.type == "cpu"
+    Kref, gref = orc.ksd_dense(q32.detach().double().numpy(), golden["spr_S"], 3)
+    assert np.isclose(K.item(), Kref, rtol=1e-9)
+    assert np.allclose(q32.grad.numpy(), gref, rtol=1e-5)
+    # chain rule through sqrt(clamp(K)) as in ksd_vi.py:133-134
+    q = torch.tensor(golden["spr_q_ramp"], dtype=torch.float64, device="cuda", requires_grad=True)
+    loss = torch.sqrt(ops.ksd_quadratic_form(q, tabs).clamp(min=1e-12))
+    loss.backward()
+    assert np.allclose(q.grad.cpu().numpy(), golden["spr_g_ramp"] / (2 * np.sqrt(golden["spr_K_ramp"])), rtol=1e-9)
