@@ -1,0 +1,302 @@
+#!/usr/bin/env python
+"""Benchmark of the exact-KSD hot path (BASELINE.json metric: ordered state-pairs/s of one
+KSD^2 + dKSD^2/dq evaluation on a synthetic random binary BN with n latent bits).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--n 20] [--precision fp32|fp64]
+
+A step = one evaluation of K = q^T K_p q and 2 K_p q for a fixed network and a given q.
+Prints ONE JSON line on rank 0.  See DESIGN.md "Measurement" for how each field is obtained.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import time
+
+import numpy as np
+
+REPO = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, REPO)
+
+METRIC = "exact KSD+grad state-pairs/s"
+UNIT = "state-pairs/s"
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--n", type=int, default=20, help="latent bits (BASELINE.json quotes the metric at n=20)")
+    ap.add_argument("--precision", default="fp32", choices=["fp32", "fp64"])
+    ap.add_argument("--seed", type=int, default=0)
+    ap.add_argument("--cpu-seconds", type=float, default=12.0, help="target CPU time of the cpu_baseline sample")
+    return ap.parse_args()
+
+
+def workload_name(n):
+    return f"synthetic random binary BN, {n} latent vars, in-degree<=3, exact KSD+grad (seed 0, n_obs={max(1, n // 3)})"
+
+
+# ------------------------------------------------------------------ CPU side (oracle port)
+def cpu_tables(n, seed):
+    """Joint and score tables of the workload from the C oracle (independent of the CUDA path)."""
+    from oracle import c_oracle
+    from tensornetworks_b200.flatten import flatten_bn
+    from tensornetworks_b200.synthetic import random_binary_bn, random_q
+    bn, lat, obs, x = random_binary_bn(n, seed=seed)
+    P = c_oracle.joint_table(flatten_bn(bn, x, lat))
+    S = c_oracle.score_table(P, n)
+    q = random_q(1 << n, seed=seed).numpy()
+    return S, q
+
+
+def cpu_sample(n, S, q, target_seconds, row_start=0):
+    """Time the oracle's literal four-term pair loop (reference stein_utils.py:161-196 per pair,
+    ksd_vi.py:114-131 over pairs) on all host threads over `rows` full rows of the pair space."""
+    from oracle import c_oracle
+    threads = c_oracle.max_threads()
+    N = 1 << n
+    rows = min(N, threads)
+    t0 = time.perf_counter()
+    c_oracle.ksd_rows(q, S, n, row_start, row_start + rows)
+    dt = time.perf_counter() - t0
+    rate = rows * N / dt
+    rows = int(min(N - row_start, max(threads, (target_seconds * rate / N) // threads * threads)))
+    t0 = time.perf_counter()
+    u, part = c_oracle.ksd_rows(q, S, n, row_start, row_start + rows)
+    dt = time.perf_counter() - t0
+    return {"pairs": rows * N, "seconds": dt, "rate": rows * N / dt, "rows": rows, "threads": threads, "u": u}
+
+
+def run_reference(args):
+    """--impl reference: the reference's CPU algorithm for the path.  The reference is pure Python
+    (4^n interpreter iterations, ~1e3 pairs/s) and is not present on the GPU box; its algorithm is
+    timed through the C oracle port on all host cores - a far faster stand-in than the original."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    n = args.n
+    S, q = cpu_tables(n, args.seed)
+    per_step = max(2.0, min(20.0, 120.0 / max(1, args.steps + args.warmup)))
+    rates, info = [], None
+    for step in range(args.warmup + args.steps):
+        info = cpu_sample(n, S, q, per_step, row_start=0)
+        if step >= args.warmup:
+            rates.append(info["rate"])
+    value = float(np.mean(rates))
+    pairs_per_step = 4.0 ** n
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": pairs_per_step / value * 1e3,
+        "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": workload_name(n), "n_latent": n, "pairs_per_step": pairs_per_step,
+                   "note": "ms_per_step extrapolated from the sample rate to the full 4^n pairs"},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": info["threads"], "kind": "port",
+                         "sample": f"{info['rows']} full rows x 2^{n} columns = {info['pairs']:.3g} ordered pairs per step"},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------ clocks during the timed region
+class ClockSampler:
+    FIELDS = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+              "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+              "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.proc, self.gpu_index = None, gpu_index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--query-gpu={self.FIELDS}", "--format=csv,noheader,nounits", "-lms", "100",
+                 "-i", str(self.gpu_index)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+        except OSError:
+            self.proc = None
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            out, _ = self.proc.communicate(timeout=5)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+            out, _ = self.proc.communicate()
+        sm, smax, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in out.strip().splitlines():
+            parts = [p.strip() for p in ln.split(",")]
+            if len(parts) < 7:
+                continue
+            try:
+                sm.append(float(parts[0])); smax.append(float(parts[1]))
+            except ValueError:
+                continue
+            for name, val in zip(names, parts[3:7]):
+                if val.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(smax) if smax else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+# ------------------------------------------------------------------ GPU arm
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    from tensornetworks_b200 import ops
+    from tensornetworks_b200.synthetic import random_binary_bn, random_q
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py --impl ours needs a CUDA device; there is no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    device = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=device)
+    n, N = args.n, 1 << args.n
+    pairs = 4.0 ** n
+
+    bn, lat, obs, x = random_binary_bn(n, seed=args.seed)
+    tables = ops.SteinTables.from_network(bn, x, lat, precision=args.precision, device=device)
+    q_host = random_q(N, seed=args.seed).pin_memory()          # fp64, as ksd_vi.py:112 hands it over
+    q_dev = q_host.to(device)
+    flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=device)  # > 126 MB L2
+    r0, r1 = ops.shard_rows(N, rank, world)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    def device_step():
+        u, part = tables.ksd_rows(q_dev, r0, r1)
+        if world > 1:
+            u, part = ops.combine_row_shards(u[r0:r1], part, N, rank, world)
+        return u, part
+
+    def e2e_step():
+        qh = q_host.requires_grad_(True)
+        qh.grad = None
+        K = ops.ksd_quadratic_form(qh, tables)     # H2D of q inside, public differentiable op
+        K.backward()                               # D2H of dK/dq inside
+        return float(K.item()), qh.grad
+
+    # roofline denominator: measured FMA-chain rate of this GPU, same run
+    peak_rate, _ = ops.alu_peak(args.precision, iters=8192, device=device)
+
+    for _ in range(max(args.warmup, 3)):
+        flush.zero_()
+        device_step()
+    barrier()
+
+    # ---- timed region 1: inputs resident in HBM, per-step CUDA events, L2 flushed between steps
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    kev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    for a, b in kev:
+        a.record(); b.record()                      # materialise the CUDA handles
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    ops.launch_counter["kernels"] = 0
+    barrier()
+    for (e0, e1), (k0, k1) in zip(ev, kev):
+        flush.zero_()
+        ops.time_pair_kernel(k0, k1)
+        e0.record()
+        u, part = device_step()
+        e1.record()
+    barrier()
+    ops.time_pair_kernel(None, None)
+    launches = ops.launch_counter["kernels"]
+    clocks = sampler.stop()
+    step_ms = [a.elapsed_time(b) for a, b in ev]
+    kern_ms = [a.elapsed_time(b) for a, b in kev]
+    total_ms = torch.tensor([sum(step_ms)], dtype=torch.float64, device=device)
+    kmean_ms = torch.tensor([float(np.mean(kern_ms))], dtype=torch.float64, device=device)
+    if world > 1:
+        dist.all_reduce(total_ms, op=dist.ReduceOp.MAX)
+        dist.all_reduce(kmean_ms, op=dist.ReduceOp.MAX)
+    ms_per_step = total_ms.item() / args.steps
+    value = pairs / (ms_per_step * 1e-3)
+    K_value = float(part.item())
+
+    # ---- timed region 2: end to end through the public op with HOST q and HOST gradient
+    for _ in range(2):
+        e2e_step()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        K_e2e, grad_host = e2e_step()
+    barrier()
+    e2e_s = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=device)
+    if world > 1:
+        dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
+    e2e_value = pairs / (e2e_s.item() / args.steps)
+    return locals()
+
+
+def load_measured_peaks():
+    try:
+        with open(os.path.join(REPO, "MEASURED_PEAKS.json")) as f:
+            return json.load(f)
+    except (OSError, ValueError):
+        return {}
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+        return
+    r = run_ours(args)
+    import torch.distributed as dist
+    world, rank, n = r["world"], r["rank"], args.n
+    if rank == 0:
+        pairs = r["pairs"]
+        w_lane = n + 10                                   # lane-ops per executed pair
+        kernel_s = r["kmean_ms"].item() * 1e-3
+        executed = pairs / world                          # this kernel evaluates every ordered pair of its rows
+        achieved = executed * w_lane / kernel_s
+        line = {
+            "metric": METRIC, "value": r["value"], "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": max(args.warmup, 3), "ms_per_step": r["ms_per_step"], "higher_is_better": True,
+            "scaling": "strong", "vs_baseline": None,
+            "dtype": "f32" if args.precision == "fp32" else "f64", "data": "synthetic",
+            "config": {"workload": workload_name(n), "n_latent": n, "pairs_per_step": pairs,
+                       "precision_mode": args.precision + ("-compute/fp64-accumulate" if args.precision == "fp32" else ""),
+                       "parallelism": f"row-sharded x{world}" if world > 1 else "single GPU",
+                       "l2": "256 MB flush written between timed steps", "executed_pairs": "4^n (symmetry not exploited)"},
+            "roofline": {"bound": "alu", "achieved": achieved / 1e12, "peak": r["peak_rate"] / 1e12,
+                         "unit": "Tlane-op/s", "frac": achieved / r["peak_rate"], "traffic": None,
+                         "kernel": "ksd_rows_kernel", "kernel_ms": r["kmean_ms"].item(),
+                         "lane_ops_per_pair": w_lane,
+                         "peak_source": "tnk_alu_peak FMA-chain probe measured in this run (MEASURED_PEAKS.json has no ALU peak)"},
+            "e2e": {"value": r["e2e_value"], "unit": UNIT, "h2d_bytes_per_step": 8 * (1 << n) * world,
+                    "d2h_bytes_per_step": (8 * (1 << n) + 8) * world},
+            "gpu_launches": r["launches"], "clocks": r["clocks"], "ksd_sq": r["K_value"],
+        }
+        if world == 1:
+            S, q = cpu_tables(n, args.seed)
+            info = cpu_sample(n, S, q, args.cpu_seconds)
+            u_gpu = r["u"][: info["rows"]].cpu().numpy()
+            err = float(np.max(np.abs(u_gpu - info["u"])) / np.max(np.abs(info["u"])))
+            line["cpu_baseline"] = {"value": info["rate"], "unit": UNIT, "cores": info["threads"], "kind": "port",
+                                    "sample": f"{info['rows']} full rows x 2^{n} columns = {info['pairs']:.3g} ordered pairs "
+                                              f"in {info['seconds']:.1f} s (oracle/ksd_oracle.c, literal four-term pair loop)",
+                                    "gpu_vs_oracle_rows_max_rel_err": err}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -87,6 +87,11 @@ int tnk_ksd_rows(int n_latent, double length_scale, int precision,
                  double* u, double* ksd_part,
                  void* workspace, size_t workspace_bytes, int* n_launch, void* stream);
 
+/* Measurement hook: when both are non-NULL cudaEvent_t handles, every following tnk_ksd_rows call
+ * on this host thread records them on its stream immediately before and after the pair kernel
+ * (K3) alone, so a benchmark can time the dominant kernel live.  Pass NULL, NULL to switch off. */
+int tnk_ksd_timing_events(void* start_event, void* stop_event);
+
 /* ALU roofline probe: runs a dependent-chain FMA kernel (precision 0: DFMA, 1: FFMA) that
  * fills the chip, times it with CUDA events on `stream` (synchronises) and returns the
  * achieved lane-ops/s (one FMA on one lane = 1).  scratch: device double [>= 1]. */

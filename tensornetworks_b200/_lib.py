@@ -24,7 +24,7 @@ PREC_FP64, PREC_FP32, PREC_FP64_SIMPLE = 0, 1, 2
 
 # every symbol include/tnk.h declares
 EXPORTS = ["tnk_last_error", "tnk_version", "tnk_bn_joint", "tnk_ksd_layout", "tnk_score",
-           "tnk_ksd_workspace_bytes", "tnk_ksd_rows", "tnk_alu_peak"]
+           "tnk_ksd_workspace_bytes", "tnk_ksd_rows", "tnk_ksd_timing_events", "tnk_alu_peak"]
 
 
 def _nvcc():
@@ -95,6 +95,8 @@ def load():
     lib.tnk_ksd_rows.restype = c_int
     lib.tnk_ksd_rows.argtypes = [c_int, c_dbl, c_int, c_vp, c_int, c_vp, c_vp, c_i64, c_i64, c_vp, c_vp,
                                  c_vp, c_sz, ctypes.POINTER(c_int), c_vp]
+    lib.tnk_ksd_timing_events.restype = c_int
+    lib.tnk_ksd_timing_events.argtypes = [c_vp, c_vp]
     lib.tnk_alu_peak.restype = c_int
     lib.tnk_alu_peak.argtypes = [c_int, c_int, c_vp, ctypes.POINTER(c_dbl), ctypes.POINTER(ctypes.c_float), c_vp]
     _lib = lib

@@ -471,6 +471,14 @@ int dispatch_np_wide(int np, const KsdParams& prm, dim3 grid, const void* ST, co
 
 }  // namespace
 
+static thread_local cudaEvent_t g_ev_start = nullptr, g_ev_stop = nullptr;
+
+extern "C" int tnk_ksd_timing_events(void* start_event, void* stop_event) {
+    g_ev_start = (cudaEvent_t)start_event;
+    g_ev_stop = (cudaEvent_t)stop_event;
+    return 0;
+}
+
 extern "C" int tnk_ksd_rows(int n_latent, double length_scale, int precision,
                             const void* q, int q_dtype, const void* ST, const void* Cst,
                             int64_t row_begin, int64_t row_end,
@@ -523,6 +531,7 @@ extern "C" int tnk_ksd_rows(int n_latent, double length_scale, int precision,
     ++launches;
 
     int rc = 0;
+    if (g_ev_start) TNK_CUDA_OK(cudaEventRecord(g_ev_start, st));
     if (precision == TNK_PREC_FP64_SIMPLE) {
         const unsigned blocks = (unsigned)((row_end - row_begin + 127) / 128);
         ksd_rows_simple_kernel<<<blocks, 128, 0, st>>>(prm, p.g.np, p.N, row_begin, row_end,
@@ -539,6 +548,7 @@ extern "C" int tnk_ksd_rows(int n_latent, double length_scale, int precision,
         }
         if (rc) return rc;
     }
+    if (g_ev_stop) TNK_CUDA_OK(cudaEventRecord(g_ev_stop, st));
     ++launches;
 
     if (q_dtype == 0)

@@ -206,3 +206,14 @@ def alu_peak(precision="fp32", iters=4096, device="cuda"):
         _lib.check(lib.tnk_alu_peak(PRECISIONS[precision], iters, _ptr(scratch), ctypes.byref(rate),
                                     ctypes.byref(ms), _stream_ptr(device)), "tnk_alu_peak")
     return rate.value, ms.value
+
+
+def time_pair_kernel(start_event=None, stop_event=None):
+    """Ask tnk_ksd_rows to record the given torch.cuda.Event pair around the pair kernel alone
+    (both must have been recorded once so that their CUDA handles exist); None, None switches off."""
+    lib = _lib.load()
+    if start_event is None or stop_event is None:
+        _lib.check(lib.tnk_ksd_timing_events(None, None), "tnk_ksd_timing_events")
+    else:
+        _lib.check(lib.tnk_ksd_timing_events(ctypes.c_void_p(start_event.cuda_event),
+                                             ctypes.c_void_p(stop_event.cuda_event)), "tnk_ksd_timing_events")
