@@ -73,8 +73,9 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
 
 __host__ __device__ constexpr int ilog2(int v) { return v <= 1 ? 0 : 1 + ilog2(v / 2); }
 __host__ __device__ constexpr int gray(int s) { return s ^ (s >> 1); }
-__host__ __device__ constexpr int ctz_c(int s) { return (s & 1) ? 0 : 1 + ctz_c(s >> 1); }
-__host__ __device__ constexpr int popc_c(int s) { return s == 0 ? 0 : (s & 1) + popc_c(s >> 1); }
+// non-recursive so that the optimiser folds them for unrolled loop indices (s in 1..7, x in 0..7)
+__host__ __device__ constexpr int ctz_c(int s) { return (s & 1) ? 0 : ((s & 2) ? 1 : 2); }
+__host__ __device__ constexpr int popc_c(int x) { return (x & 1) + ((x >> 1) & 1) + ((x >> 2) & 1); }
 
 template <typename T, int NP, int R, int TC>
 struct Smem {
