@@ -1,0 +1,10 @@
+"""Import shim: `import born_machine_classical_sim` resolves to tensornetworks_b200.born_machine_classical_sim when this directory is on
+sys.path, so scripts written against the reference's flat module layout run unchanged."""
+import os as _os
+import sys as _sys
+
+_sys.path.insert(0, _os.path.dirname(_os.path.dirname(_os.path.abspath(__file__))))
+from tensornetworks_b200.born_machine_classical_sim import *  # noqa: E402,F401,F403
+from tensornetworks_b200 import born_machine_classical_sim as _impl  # noqa: E402
+
+globals().update({k: v for k, v in vars(_impl).items() if not k.startswith("__")})

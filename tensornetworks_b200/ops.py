@@ -94,6 +94,17 @@ class SteinTables:
         P = joint_table(bn, x_dict, latent_vars_names, device=device, n_latent=n)
         return cls(P, n, length_scale=length_scale, precision=precision, keep_scores=keep_scores)
 
+    def scores(self):
+        """fp64 [N, n] score table in latent-variable order (what get_score_function_sp_for_z
+        returns per state); computed on first use when the tables were built without it."""
+        if self.S is None:
+            with torch.cuda.device(self.device):
+                self.S = torch.empty((self.N, self.n), dtype=torch.float64, device=self.device)
+                _lib.check(_lib.load().tnk_score(self.n, self.length_scale, _ptr(self.P), _ptr(self.S), self.prec_code,
+                                                 None, None, _stream_ptr(self.device)), "tnk_score")
+                launch_counter["kernels"] += 1
+        return self.S
+
     def posterior(self):
         """p(z|x) = P / sum(P) as an fp64 device tensor (tensor form of get_true_posterior)."""
         return self.P / self.P.sum()
