@@ -26,6 +26,8 @@ extern "C" {
 #define TNK_PREC_FP32 1        /* FFMA pair arithmetic, fp64 accumulation across tiles (1e-4 mode) */
 #define TNK_PREC_FP64_SIMPLE 2 /* one-thread-per-row fp64 check kernel (debug / cross-check only) */
 
+#define TNK_PEAK_FP32X2 3      /* tnk_alu_peak only: packed fma.rn.f32x2 chain (2 lane-ops per instruction) */
+
 /* node kinds of the flattened network (tnk_bn_joint) */
 #define TNK_NODE_LATENT 0 /* value = bit `arg` of the packed state index            */
 #define TNK_NODE_CONST 1  /* value = `arg` (clamped evidence)                       */
@@ -92,7 +94,7 @@ int tnk_ksd_rows(int n_latent, double length_scale, int precision,
  * (K3) alone, so a benchmark can time the dominant kernel live.  Pass NULL, NULL to switch off. */
 int tnk_ksd_timing_events(void* start_event, void* stop_event);
 
-/* ALU roofline probe: runs a dependent-chain FMA kernel (precision 0: DFMA, 1: FFMA) that
+/* ALU roofline probe: runs a dependent-chain FMA kernel (precision 0: DFMA, 1: FFMA, 3: packed FFMA2) that
  * fills the chip, times it with CUDA events on `stream` (synchronises) and returns the
  * achieved lane-ops/s (one FMA on one lane = 1).  scratch: device double [>= 1]. */
 int tnk_alu_peak(int precision, int iters, double* scratch, double* lane_ops_per_s, float* ms, void* stream);

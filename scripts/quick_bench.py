@@ -9,7 +9,7 @@ sizes = [int(a) for a in sys.argv[1].split(",")] if len(sys.argv) > 1 else [14, 
 precs = sys.argv[2].split(",") if len(sys.argv) > 2 else ["fp32", "fp64"]
 reps = int(sys.argv[3]) if len(sys.argv) > 3 else 3
 peaks = {}
-for prec in ("fp32", "fp64"):
+for prec in ("fp32", "fp32x2", "fp64"):
     rate, ms = ops.alu_peak(prec, iters=8192)
     peaks[prec] = rate
     print(json.dumps({"alu_peak": prec, "lane_ops_per_s": rate, "ms": ms}), flush=True)

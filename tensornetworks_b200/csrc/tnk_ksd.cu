@@ -291,10 +291,21 @@ ksd_rows_kernel(const KsdParams prm, const T* __restrict__ ST, const T* __restri
                 load_vec<T, NP>(rawb + c * NP, scol);
 #pragma unroll
                 for (int r = 0; r < R; ++r) {
-                    T acc = colbase + Y[r];
-                    if (r > 0) acc += cm[r];
+                    T acc;
+                    if constexpr (sizeof(T) == 4) {
+                        // packed FFMA2 (fma.rn.f32x2): even/odd partial dot products, seeded with the
+                        // two additive terms so that no separate add is needed for Y
+                        float2 a2 = make_float2(r > 0 ? colbase + cm[r] : colbase, Y[r]);
 #pragma unroll
-                    for (int p = 0; p < NP; ++p) acc = fma(srow[r][p], scol[p], acc);
+                        for (int p = 0; p < NP; p += 2)
+                            a2 = __ffma2_rn(make_float2(srow[r][p], srow[r][p + 1]), make_float2(scol[p], scol[p + 1]), a2);
+                        acc = a2.x + a2.y;
+                    } else {
+                        acc = colbase + Y[r];
+                        if (r > 0) acc += cm[r];
+#pragma unroll
+                        for (int p = 0; p < NP; ++p) acc = fma(srow[r][p], scol[p], acc);
+                    }
                     const int cc = popc_c((jlo & (R - 1)) ^ r);
                     tacc[jlo >> RBITS][r] = fma(acc, qa[cc], tacc[jlo >> RBITS][r]);
                 }

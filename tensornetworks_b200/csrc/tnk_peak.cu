@@ -25,10 +25,30 @@ fma_chain_kernel(int iters, T a, T b, double* sink) {
     if (s == (T)123.456) sink[0] = (double)s;  // keeps the chains alive, never true in practice
 }
 
+// packed variant: one FFMA2 (fma.rn.f32x2) per chain step = 2 lane-ops per instruction
+__global__ void __launch_bounds__(256)
+fma2_chain_kernel(int iters, float a, float b, double* sink) {
+    float2 x[16];
+    const float2 a2 = make_float2(a, a), b2 = make_float2(b, b);
+#pragma unroll
+    for (int c = 0; c < 16; ++c) x[c] = make_float2((threadIdx.x + c) * 1e-3f, (threadIdx.x + c) * 2e-3f);
+    for (int it = 0; it < iters; ++it) {
+#pragma unroll
+        for (int rep = 0; rep < 4; ++rep)
+#pragma unroll
+            for (int c = 0; c < 16; ++c) x[c] = __ffma2_rn(x[c], a2, b2);
+    }
+    float s = 0.f;
+#pragma unroll
+    for (int c = 0; c < 16; ++c) s += x[c].x + x[c].y;
+    if (s == 123.456f) sink[0] = (double)s;
+}
+
 }  // namespace
 
 extern "C" int tnk_alu_peak(int precision, int iters, double* scratch, double* lane_ops_per_s, float* ms_out, void* stream) {
-    TNK_REQUIRE(precision == TNK_PREC_FP64 || precision == TNK_PREC_FP32, "tnk_alu_peak: precision must be 0 or 1");
+    TNK_REQUIRE(precision == TNK_PREC_FP64 || precision == TNK_PREC_FP32 || precision == TNK_PEAK_FP32X2,
+                "tnk_alu_peak: precision must be 0 (DFMA), 1 (FFMA) or 3 (packed FFMA2)");
     TNK_REQUIRE(iters > 0 && scratch && lane_ops_per_s, "tnk_alu_peak: bad arguments");
     cudaStream_t st = (cudaStream_t)stream;
     int dev = 0, sms = 0;
@@ -41,6 +61,7 @@ extern "C" int tnk_alu_peak(int precision, int iters, double* scratch, double* l
     for (int pass = 0; pass < 2; ++pass) {  // pass 0 warms up
         TNK_CUDA_OK(cudaEventRecord(e0, st));
         if (precision == TNK_PREC_FP32) fma_chain_kernel<float><<<blocks, 256, 0, st>>>(iters, 0.999f, 1e-3f, scratch);
+        else if (precision == TNK_PEAK_FP32X2) fma2_chain_kernel<<<blocks, 256, 0, st>>>(iters, 0.999f, 1e-3f, scratch);
         else fma_chain_kernel<double><<<blocks, 256, 0, st>>>(iters, 0.999, 1e-3, scratch);
         TNK_CUDA_OK(cudaGetLastError());
         TNK_CUDA_OK(cudaEventRecord(e1, st));
@@ -50,7 +71,7 @@ extern "C" int tnk_alu_peak(int precision, int iters, double* scratch, double* l
     TNK_CUDA_OK(cudaEventElapsedTime(&ms, e0, e1));
     cudaEventDestroy(e0);
     cudaEventDestroy(e1);
-    const double ops = (double)blocks * 256.0 * (double)iters * 64.0;
+    const double ops = (double)blocks * 256.0 * (double)iters * 64.0 * (precision == TNK_PEAK_FP32X2 ? 2.0 : 1.0);
     *lane_ops_per_s = ops / ((double)ms * 1e-3);
     if (ms_out) *ms_out = ms;
     return 0;

@@ -214,7 +214,7 @@ def alu_peak(precision="fp32", iters=4096, device="cuda"):
     with torch.cuda.device(device):
         scratch = torch.zeros(8, dtype=torch.float64, device=device)
         rate, ms = ctypes.c_double(0.0), ctypes.c_float(0.0)
-        _lib.check(lib.tnk_alu_peak(PRECISIONS[precision], iters, _ptr(scratch), ctypes.byref(rate),
+        _lib.check(lib.tnk_alu_peak(3 if precision == "fp32x2" else PRECISIONS[precision], iters, _ptr(scratch), ctypes.byref(rate),
                                     ctypes.byref(ms), _stream_ptr(device)), "tnk_alu_peak")
     return rate.value, ms.value
 
