@@ -89,6 +89,21 @@ int tnk_ksd_rows(int n_latent, double length_scale, int precision,
                  double* u, double* ksd_part,
                  void* workspace, size_t workspace_bytes, int* n_launch, void* stream);
 
+/* The same u = K_p q and partial of q.u through the Kronecker (mode-product) factorisation of the
+ * Hamming base kernel (reference stein_utils.py:30-55: k = prod_p a^(z_p xor z'_p)), O(n^2 2^n)
+ * instead of O(4^n); fp64 throughout.  Replaces the same reference lines as tnk_ksd_rows
+ * (ksd_vi.py:110-131,145).  Work is split by score component: the call handles bit positions
+ * [bit_begin,bit_end) of [0,n) and writes that partial of u for ALL 2^n rows; partials of
+ * disjoint bit ranges add up to u and K (sum-allreduce across ranks).
+ *   ST64     device double [n_pad][np]: the packed table tnk_score emits for TNK_PREC_FP64
+ *   u        device double [2^n] (out, partial), ksd_part device double [1] (out, partial)
+ *   workspace: tnk_ksd_modeproduct_workspace_bytes(n, bit_begin, bit_end) bytes, 256-byte aligned */
+size_t tnk_ksd_modeproduct_workspace_bytes(int n_latent, int bit_begin, int bit_end);
+int tnk_ksd_modeproduct(int n_latent, double length_scale, const void* q, int q_dtype,
+                        const double* ST64, int bit_begin, int bit_end,
+                        double* u, double* ksd_part,
+                        void* workspace, size_t workspace_bytes, int* n_launch, void* stream);
+
 /* Measurement hook: when both are non-NULL cudaEvent_t handles, every following tnk_ksd_rows call
  * on this host thread records them on its stream immediately before and after the pair kernel
  * (K3) alone, so a benchmark can time the dominant kernel live.  Pass NULL, NULL to switch off. */

@@ -16,7 +16,7 @@ REPO_DIR = os.path.dirname(PKG_DIR)
 CSRC = os.path.join(PKG_DIR, "csrc")
 INCLUDE = os.path.join(REPO_DIR, "include")
 LIB_PATH = os.path.join(PKG_DIR, "libtnk_b200.so")
-SOURCES = ["tnk_enum.cu", "tnk_ksd.cu", "tnk_peak.cu"]
+SOURCES = ["tnk_enum.cu", "tnk_ksd.cu", "tnk_peak.cu", "tnk_modeprod.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC", "-I", INCLUDE]
 
@@ -24,7 +24,8 @@ PREC_FP64, PREC_FP32, PREC_FP64_SIMPLE = 0, 1, 2
 
 # every symbol include/tnk.h declares
 EXPORTS = ["tnk_last_error", "tnk_version", "tnk_bn_joint", "tnk_ksd_layout", "tnk_score",
-           "tnk_ksd_workspace_bytes", "tnk_ksd_rows", "tnk_ksd_timing_events", "tnk_alu_peak"]
+           "tnk_ksd_workspace_bytes", "tnk_ksd_rows", "tnk_ksd_timing_events", "tnk_alu_peak",
+           "tnk_ksd_modeproduct_workspace_bytes", "tnk_ksd_modeproduct"]
 
 
 def _nvcc():
@@ -95,6 +96,11 @@ def load():
     lib.tnk_ksd_rows.restype = c_int
     lib.tnk_ksd_rows.argtypes = [c_int, c_dbl, c_int, c_vp, c_int, c_vp, c_vp, c_i64, c_i64, c_vp, c_vp,
                                  c_vp, c_sz, ctypes.POINTER(c_int), c_vp]
+    lib.tnk_ksd_modeproduct_workspace_bytes.restype = c_sz
+    lib.tnk_ksd_modeproduct_workspace_bytes.argtypes = [c_int, c_int, c_int]
+    lib.tnk_ksd_modeproduct.restype = c_int
+    lib.tnk_ksd_modeproduct.argtypes = [c_int, c_dbl, c_vp, c_int, c_vp, c_int, c_int, c_vp, c_vp, c_vp, c_sz,
+                                        ctypes.POINTER(c_int), c_vp]
     lib.tnk_ksd_timing_events.restype = c_int
     lib.tnk_ksd_timing_events.argtypes = [c_vp, c_vp]
     lib.tnk_alu_peak.restype = c_int

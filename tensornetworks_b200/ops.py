@@ -142,6 +142,51 @@ class SteinTables:
         return u, part
 
 
+    def _st64(self):
+        """fp64 packed score table [n_pad, np] (bit order) for the mode-product path; the fp64-mode
+        tables already hold it, fp32-mode tables build it on first use."""
+        if self.dtype == torch.float64:
+            return self.ST
+        if getattr(self, "_ST64", None) is None:
+            np_, n_pad, _ = _lib.layout(self.n, _lib.PREC_FP64)
+            with torch.cuda.device(self.device):
+                self._ST64 = torch.empty((n_pad, np_), dtype=torch.float64, device=self.device)
+                cst = torch.empty(n_pad, dtype=torch.float64, device=self.device)
+                _lib.check(_lib.load().tnk_score(self.n, self.length_scale, _ptr(self.P), None, _lib.PREC_FP64,
+                                                 _ptr(self._ST64), _ptr(cst), _stream_ptr(self.device)), "tnk_score")
+                launch_counter["kernels"] += 1
+        return self._ST64
+
+    def ksd_modeproduct(self, q, bit_begin=0, bit_end=None):
+        """Partial of u = K_p q over score components (bit positions) [bit_begin, bit_end) for all rows,
+        and the matching partial of q.u, through the Kronecker factorisation (O(n^2 2^n), fp64).
+        Partials over disjoint bit ranges add up to the pair kernel's result."""
+        bit_end = self.n if bit_end is None else bit_end
+        if q.device != self.device or q.dim() != 1 or q.numel() != self.N:
+            raise ValueError(f"q must be a 1-D tensor of {self.N} entries on {self.device}")
+        if q.dtype not in (torch.float32, torch.float64):
+            raise ValueError("q must be float32 or float64")
+        q = q.contiguous()
+        lib = _lib.load()
+        st64 = self._st64()
+        with torch.cuda.device(self.device):
+            key = ("mp", bit_begin, bit_end)
+            if key not in self._ws:
+                nbytes = lib.tnk_ksd_modeproduct_workspace_bytes(self.n, bit_begin, bit_end)
+                if nbytes == 0:
+                    raise RuntimeError("tnk_ksd_modeproduct_workspace_bytes rejected the bit range")
+                self._ws[key] = torch.empty(nbytes, dtype=torch.uint8, device=self.device)
+            ws = self._ws[key]
+            u = torch.empty(self.N, dtype=torch.float64, device=self.device)
+            part = torch.empty(1, dtype=torch.float64, device=self.device)
+            launched = ctypes.c_int(0)
+            _lib.check(lib.tnk_ksd_modeproduct(self.n, self.length_scale, _ptr(q), 0 if q.dtype == torch.float64 else 1,
+                                               _ptr(st64), bit_begin, bit_end, _ptr(u), _ptr(part), _ptr(ws), ws.numel(),
+                                               ctypes.byref(launched), _stream_ptr(self.device)), "tnk_ksd_modeproduct")
+            launch_counter["kernels"] += launched.value
+        return u, part
+
+
 def shard_rows(num_states, rank, world):
     """Contiguous row block of rank `rank` among `world` ranks."""
     return (num_states * rank) // world, (num_states * (rank + 1)) // world
@@ -174,17 +219,25 @@ class _KsdQuadraticForm(torch.autograd.Function):
     """K(q) = q^T K_p q with dK/dq = 2 K_p q, one pass over the pair space for both."""
 
     @staticmethod
-    def forward(ctx, q, tables, group):
+    def forward(ctx, q, tables, group, algorithm="pairs"):
         q_dev = q.detach()
         if q_dev.dtype not in (torch.float32, torch.float64):
             q_dev = q_dev.to(torch.float64)
         q_dev = q_dev.to(tables.device)
         world = dist.get_world_size(group) if (dist.is_available() and dist.is_initialized()) else 1
         rank = dist.get_rank(group) if world > 1 else 0
-        r0, r1 = shard_rows(tables.N, rank, world)
-        u, part = tables.ksd_rows(q_dev, r0, r1)
-        if world > 1:
-            u, part = combine_row_shards(u[r0:r1], part, tables.N, rank, world, group)
+        if algorithm == "modeproduct":
+            b0, b1 = shard_rows(tables.n, rank, world)      # score components split over the ranks
+            u, part = tables.ksd_modeproduct(q_dev, b0, b1)
+            if world > 1:
+                buf = torch.cat([u, part])
+                dist.all_reduce(buf, op=dist.ReduceOp.SUM, group=group)
+                u, part = buf[:-1], buf[-1:].clone()
+        else:
+            r0, r1 = shard_rows(tables.N, rank, world)
+            u, part = tables.ksd_rows(q_dev, r0, r1)
+            if world > 1:
+                u, part = combine_row_shards(u[r0:r1], part, tables.N, rank, world, group)
         ctx.save_for_backward(u)
         ctx.q_meta = (q.dtype, q.device)
         return part.reshape(()).to(q.device)
@@ -194,17 +247,25 @@ class _KsdQuadraticForm(torch.autograd.Function):
         (u,) = ctx.saved_tensors
         dtype, device = ctx.q_meta
         grad = (2.0 * grad_out.to(u.device, torch.float64)) * u
-        return grad.to(device=device, dtype=dtype), None, None
+        return grad.to(device=device, dtype=dtype), None, None, None
 
 
-def ksd_quadratic_form(q, tables, group=None):
+ALGORITHMS = ("pairs", "modeproduct")
+
+
+def ksd_quadratic_form(q, tables, group=None, algorithm="pairs"):
     """KSD^2 = sum_ij q_i q_j k_p(z_i, z_j) as an fp64 scalar tensor on q's device, differentiable
     w.r.t. q (any float dtype, CPU or CUDA; e.g. PennyLane probabilities).  Drop-in for the double
     loop of reference ksd_vi.py:110-131 / ksd_vi_quantum.py:122-142.  When torch.distributed is
-    initialised the rows of the pair space are sharded over the ranks of `group`."""
+    initialised the rows of the pair space are sharded over the ranks of `group`.
+    algorithm="pairs" evaluates all 4^n pairs on the fly (the reference's loop, tiled);
+    algorithm="modeproduct" returns the same value through the Kronecker factorisation of the
+    Hamming kernel in O(n^2 2^n) (fp64), with the score components sharded over the ranks."""
+    if algorithm not in ALGORITHMS:
+        raise ValueError(f"algorithm must be one of {ALGORITHMS}")
     if q.dim() != 1 or q.numel() != tables.N:
         raise ValueError(f"Probabilities shape mismatch: {tuple(q.shape)}")
-    return _KsdQuadraticForm.apply(q, tables, group)
+    return _KsdQuadraticForm.apply(q, tables, group, algorithm)
 
 
 def alu_peak(precision="fp32", iters=4096, device="cuda"):

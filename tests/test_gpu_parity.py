@@ -162,3 +162,62 @@ def test_q_dtypes_and_cpu_q(ops, golden):
     loss = torch.sqrt(ops.ksd_quadratic_form(q, tabs).clamp(min=1e-12))
     loss.backward()
     assert np.allclose(q.grad.cpu().numpy(), golden["spr_g_ramp"] / (2 * np.sqrt(golden["spr_K_ramp"])), rtol=1e-9)
+
+
+# ---------------------------------------------------------------- mode-product (Kronecker) path
+def _eval_mp(ops, tabs, q):
+    qd = torch.as_tensor(q, dtype=torch.float64, device="cuda").requires_grad_(True)
+    K = ops.ksd_quadratic_form(qd, tabs, algorithm="modeproduct")
+    K.backward()
+    return float(K.item()), qd.grad.cpu().numpy()
+
+
+def test_modeproduct_sprinkler_golden(ops, golden):
+    bn = get_sprinkler_network(False)
+    tabs = _tables(ops, bn, {'W': 1}, ['C', 'S', 'R'], "fp64")
+    for name in ("uniform", "ramp"):
+        K, g = _eval_mp(ops, tabs, golden[f"spr_q_{name}"])
+        _check(K, g, float(golden[f"spr_K_{name}"]), golden[f"spr_g_{name}"], 1e-9)
+    t2 = _tables(ops, bn, {'W': 1}, ['C', 'S', 'R'], "fp32", length_scale=0.5)   # fp32 tables build ST64 lazily
+    K, g = _eval_mp(ops, t2, golden["spr_q_ramp"])
+    _check(K, g, float(golden["spr_K_ramp_ls0.5"]), golden["spr_g_ramp_ls0.5"], 1e-9)
+
+
+@pytest.mark.parametrize("n,seed,nh", RANDOM_CASES)
+def test_modeproduct_vs_reference_loop(ops, golden, n, seed, nh):
+    bn, lat, obs, x = random_binary_bn(n, seed=seed, n_hidden=nh)
+    tag = f"rnd_n{n}_s{seed}_h{nh}"
+    tabs = _tables(ops, bn, x, lat, "fp64")
+    K, g = _eval_mp(ops, tabs, golden[tag + "_q"])
+    _check(K, g, float(golden[tag + "_K"]), golden[tag + "_g"], 1e-9)
+
+
+@pytest.mark.parametrize("n,seed", [(1, 0), (7, 0), (11, 3), (12, 0), (13, 1), (14, 2), (16, 0), (18, 1)])
+def test_modeproduct_vs_oracle(ops, n, seed):
+    """Covers every pass plan: single tile (n<=12), one strided pass (13..21) incl. 1-bit and 6-bit ones."""
+    bn, lat, obs, x = random_binary_bn(n, seed=seed)
+    tabs = _tables(ops, bn, x, lat, "fp64")
+    S = tabs.S.cpu().numpy()
+    q = random_q(1 << n, seed=seed).numpy()
+    Kref, gref = (orc.ksd_dense if n <= 12 else orc.ksd_modeproduct)(q, S, n)
+    K, g = _eval_mp(ops, tabs, q)
+    _check(K, g, Kref, gref, 1e-9)
+
+
+def test_modeproduct_matches_pair_kernel_n20(ops):
+    """Full size of BASELINE.json's metric: the two CUDA algorithms agree (no CPU oracle at this size
+    in test time), plus the bit-range partials add up (the multi-GPU split)."""
+    n = 20
+    bn, lat, obs, x = random_binary_bn(n, seed=0)
+    tabs = _tables(ops, bn, x, lat, "fp64")
+    q = random_q(1 << n, seed=0).cuda()
+    u_mp, k_mp = tabs.ksd_modeproduct(q)
+    ua, ka = tabs.ksd_modeproduct(q, 0, 7)
+    ub, kb = tabs.ksd_modeproduct(q, 7, n)
+    torch.cuda.synchronize()
+    assert torch.allclose(ua + ub, u_mp, rtol=1e-12, atol=1e-9 * u_mp.abs().max().item())
+    assert np.isclose(ka.item() + kb.item(), k_mp.item(), rtol=1e-12)
+    u_pair, k_pair = tabs.ksd_rows(q)
+    torch.cuda.synchronize()
+    assert abs(k_pair.item() - k_mp.item()) <= 1e-6 * abs(k_mp.item())
+    assert (u_pair - u_mp).abs().max().item() <= 1e-6 * u_mp.abs().max().item()
