@@ -32,6 +32,9 @@ def parse_args():
     ap.add_argument("--n", type=int, default=20, help="latent bits (BASELINE.json quotes the metric at n=20)")
     ap.add_argument("--precision", default="fp32", choices=["fp32", "fp64"])
     ap.add_argument("--seed", type=int, default=0)
+    ap.add_argument("--exchange", default="fused", choices=["fused", "nccl"],
+                    help="N>1: rows stored into every rank's buffer by the reduction kernel over NVLink (fused) "
+                         "or one NCCL all_gather after it (nccl)")
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="target CPU time of the cpu_baseline sample")
     return ap.parse_args()
 
@@ -172,6 +175,12 @@ def run_ours(args):
     q_dev = q_host.to(device)
     flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=device)  # > 126 MB L2
     r0, r1 = ops.shard_rows(N, rank, world)
+    exchange, exchange_name = None, args.exchange
+    if world > 1 and args.exchange == "fused":
+        try:
+            exchange = ops.PeerExchange(N, device)
+        except Exception as exc:      # no P2P mapping between these GPUs: keep the NCCL exchange, say so
+            exchange_name = f"nccl (symmetric memory unavailable: {type(exc).__name__})"
 
     def barrier():
         torch.cuda.synchronize()
@@ -180,6 +189,8 @@ def run_ours(args):
             torch.cuda.synchronize()
 
     def device_step():
+        if exchange is not None:
+            return ops.ksd_rows_fused(tables, q_dev, exchange)   # K3 + K4 with peer stores + barrier
         u, part = tables.ksd_rows(q_dev, r0, r1)
         if world > 1:
             u, part = ops.combine_row_shards(u[r0:r1], part, N, rank, world)
@@ -188,7 +199,7 @@ def run_ours(args):
     def e2e_step():
         qh = q_host.requires_grad_(True)
         qh.grad = None
-        K = ops.ksd_quadratic_form(qh, tables)     # H2D of q inside, public differentiable op
+        K = ops.ksd_quadratic_form(qh, tables, exchange=exchange)   # H2D of q inside, public differentiable op
         K.backward()                               # D2H of dK/dq inside
         return float(K.item()), qh.grad
 
@@ -274,7 +285,7 @@ def main():
             "dtype": "f32" if args.precision == "fp32" else "f64", "data": "synthetic",
             "config": {"workload": workload_name(n), "n_latent": n, "pairs_per_step": pairs,
                        "precision_mode": args.precision + ("-compute/fp64-accumulate" if args.precision == "fp32" else ""),
-                       "parallelism": f"row-sharded x{world}" if world > 1 else "single GPU",
+                       "parallelism": (f"row-sharded x{world}, exchange={r['exchange_name']}" if world > 1 else "single GPU"),
                        "l2": "256 MB flush written between timed steps", "executed_pairs": "4^n (symmetry not exploited)"},
             "roofline": {"bound": "alu", "achieved": achieved / 1e12, "peak": r["peak_rate"] / 1e12,
                          "unit": "Tlane-op/s", "frac": achieved / r["peak_rate"], "traffic": None,

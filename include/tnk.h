@@ -35,6 +35,7 @@ extern "C" {
 
 #define TNK_MAX_NODES 64
 #define TNK_MAX_LATENT 30
+#define TNK_MAX_PEERS 8   /* GPUs of one NVSwitch box (tnk_ksd_rows_peers) */
 
 const char* tnk_last_error(void);
 int tnk_version(void);
@@ -88,6 +89,27 @@ int tnk_ksd_rows(int n_latent, double length_scale, int precision,
                  int64_t row_begin, int64_t row_end,
                  double* u, double* ksd_part,
                  void* workspace, size_t workspace_bytes, int* n_launch, void* stream);
+
+/* tnk_ksd_rows with the exchange step of the row-sharded evaluation fused into its reduction
+ * kernels (replaces the all_gather + all_reduce a host would otherwise issue after
+ * the loop of reference ksd_vi.py:114-131 on every rank).  Rank `my_rank` of `n_peers` owns rows
+ * [row_begin,row_end); the kernel that finishes a row stores it into the u buffer of EVERY rank
+ * and the kernel that finishes this rank's partial of q.u stores it into slot `my_rank` of EVERY
+ * rank's partial array - plain st.global on peer-mapped device addresses (NVLink P2P / symmetric
+ * memory; the caller maps them, e.g. torch symmetric memory or cudaIpc).  After a cross-rank
+ * barrier on the same streams each rank holds the full u and all n_peers partials, whose sum in
+ * slot order is K.  No NCCL call is involved.
+ *   peer_u      host array [n_peers] of device double* [2^n]   (entry my_rank = the local buffer)
+ *   peer_parts  host array [n_peers] of device double* [n_peers]
+ *   ksd_part    device double [1] local copy of this rank's partial (out)
+ * The caller must not reuse the same sink buffers for the next evaluation until another barrier
+ * has passed (double-buffer them). */
+int tnk_ksd_rows_peers(int n_latent, double length_scale, int precision,
+                       const void* q, int q_dtype, const void* ST, const void* Cst,
+                       int64_t row_begin, int64_t row_end,
+                       int n_peers, int my_rank, void* const* peer_u, void* const* peer_parts,
+                       double* ksd_part,
+                       void* workspace, size_t workspace_bytes, int* n_launch, void* stream);
 
 /* The same u = K_p q and partial of q.u through the Kronecker (mode-product) factorisation of the
  * Hamming base kernel (reference stein_utils.py:30-55: k = prod_p a^(z_p xor z'_p)), O(n^2 2^n)

@@ -21,10 +21,11 @@ NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", 
               "-Xcompiler", "-fPIC", "-I", INCLUDE]
 
 PREC_FP64, PREC_FP32, PREC_FP64_SIMPLE = 0, 1, 2
+MAX_PEERS = 8  # TNK_MAX_PEERS
 
 # every symbol include/tnk.h declares
 EXPORTS = ["tnk_last_error", "tnk_version", "tnk_bn_joint", "tnk_ksd_layout", "tnk_score",
-           "tnk_ksd_workspace_bytes", "tnk_ksd_rows", "tnk_ksd_timing_events", "tnk_alu_peak",
+           "tnk_ksd_workspace_bytes", "tnk_ksd_rows", "tnk_ksd_rows_peers", "tnk_ksd_timing_events", "tnk_alu_peak",
            "tnk_ksd_modeproduct_workspace_bytes", "tnk_ksd_modeproduct"]
 
 
@@ -96,6 +97,10 @@ def load():
     lib.tnk_ksd_rows.restype = c_int
     lib.tnk_ksd_rows.argtypes = [c_int, c_dbl, c_int, c_vp, c_int, c_vp, c_vp, c_i64, c_i64, c_vp, c_vp,
                                  c_vp, c_sz, ctypes.POINTER(c_int), c_vp]
+    lib.tnk_ksd_rows_peers.restype = c_int
+    lib.tnk_ksd_rows_peers.argtypes = [c_int, c_dbl, c_int, c_vp, c_int, c_vp, c_vp, c_i64, c_i64,
+                                       c_int, c_int, ctypes.POINTER(c_vp), ctypes.POINTER(c_vp), c_vp,
+                                       c_vp, c_sz, ctypes.POINTER(c_int), c_vp]
     lib.tnk_ksd_modeproduct_workspace_bytes.restype = c_sz
     lib.tnk_ksd_modeproduct_workspace_bytes.argtypes = [c_int, c_int, c_int]
     lib.tnk_ksd_modeproduct.restype = c_int

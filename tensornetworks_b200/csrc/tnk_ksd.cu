@@ -335,12 +335,23 @@ __global__ void q_pack_kernel(const Q* __restrict__ q, int64_t N, int64_t n_pad,
     if (i < n_pad) qT[i] = (i < N) ? (T)q[i] : (T)0;
 }
 
-// K4a: u[row] = sum over column splits (fixed order); per-block partial of sum q_i u_i
+// Peer sinks of the fused exchange (tnk_ksd_rows_peers): u buffers and partial-K slot arrays of
+// every rank of the box, mapped into this process (NVLink peer / symmetric memory).
+struct PeerSinks {
+    int n, rank;
+    double* u[TNK_MAX_PEERS];
+    double* parts[TNK_MAX_PEERS];
+};
+
+// K4a: u[row] = sum over column splits (fixed order); per-block partial of sum q_i u_i.
+// With peers.n > 0 the finished row is also stored straight into every peer's u buffer
+// (st.global on peer-mapped addresses over NVLink) - the all-gather of SURVEY.md 8(e) fused
+// into the reduction instead of a separate collective.
 template <typename Q>
 __global__ void __launch_bounds__(256)
 finish_rows_kernel(const double* __restrict__ part, int splits, int64_t part_stride, int64_t row0,
                    int64_t row_begin, int64_t row_end, const Q* __restrict__ q,
-                   double* __restrict__ u, double* __restrict__ blockpart) {
+                   double* __restrict__ u, double* __restrict__ blockpart, const PeerSinks peers) {
     __shared__ double red[256];
     const int64_t row = row_begin + (int64_t)blockIdx.x * 256 + threadIdx.x;
     double contrib = 0.0;
@@ -348,6 +359,8 @@ finish_rows_kernel(const double* __restrict__ part, int splits, int64_t part_str
         double acc = 0.0;
         for (int s = 0; s < splits; ++s) acc += part[(size_t)s * part_stride + (row - row0)];
         u[row] = acc;
+        for (int p = 0; p < peers.n; ++p)
+            if (p != peers.rank) peers.u[p][row] = acc;
         contrib = (double)q[row] * acc;
     }
     red[threadIdx.x] = contrib;
@@ -361,7 +374,8 @@ finish_rows_kernel(const double* __restrict__ part, int splits, int64_t part_str
 
 // K4b: one CTA adds the block partials in a fixed order -> deterministic scalar
 __global__ void __launch_bounds__(256)
-finish_scalar_kernel(const double* __restrict__ blockpart, int64_t nblocks, double* __restrict__ out) {
+finish_scalar_kernel(const double* __restrict__ blockpart, int64_t nblocks, double* __restrict__ out,
+                     const PeerSinks peers) {
     __shared__ double red[256];
     double acc = 0.0;
     for (int64_t b = threadIdx.x; b < nblocks; b += 256) acc += blockpart[b];
@@ -371,7 +385,11 @@ finish_scalar_kernel(const double* __restrict__ blockpart, int64_t nblocks, doub
         if (threadIdx.x < off) red[threadIdx.x] += red[threadIdx.x + off];
         __syncthreads();
     }
-    if (threadIdx.x == 0) out[0] = red[0];
+    if (threadIdx.x == 0) {
+        out[0] = red[0];
+        for (int p = 0; p < peers.n; ++p) peers.parts[p][peers.rank] = red[0];  // slot `rank` of every rank
+        __threadfence_system();
+    }
 }
 
 // Cross-check kernel (TNK_PREC_FP64_SIMPLE): one thread per row, plain closed form, no tiling.
@@ -491,11 +509,12 @@ extern "C" int tnk_ksd_timing_events(void* start_event, void* stop_event) {
     return 0;
 }
 
-extern "C" int tnk_ksd_rows(int n_latent, double length_scale, int precision,
-                            const void* q, int q_dtype, const void* ST, const void* Cst,
-                            int64_t row_begin, int64_t row_end,
-                            double* u, double* ksd_part,
-                            void* workspace, size_t workspace_bytes, int* n_launch, void* stream) {
+static int ksd_rows_impl(int n_latent, double length_scale, int precision,
+                         const void* q, int q_dtype, const void* ST, const void* Cst,
+                         int64_t row_begin, int64_t row_end,
+                         double* u, double* ksd_part,
+                         void* workspace, size_t workspace_bytes, int* n_launch, void* stream,
+                         const PeerSinks& peers) {
     Plan p;
     TNK_REQUIRE(make_plan(n_latent, precision, row_begin, row_end, &p) == 0,
                 "tnk_ksd_rows: bad arguments n=%d precision=%d rows=[%lld,%lld)", n_latent, precision,
@@ -516,6 +535,11 @@ extern "C" int tnk_ksd_rows(int n_latent, double length_scale, int precision,
         // n == 0: k_p is identically 0 (reference stein_utils.py:151-152)
         TNK_CUDA_OK(cudaMemsetAsync(ksd_part, 0, sizeof(double), st));
         if (row_end > row_begin) TNK_CUDA_OK(cudaMemsetAsync(u + row_begin, 0, (row_end - row_begin) * sizeof(double), st));
+        for (int pr = 0; pr < peers.n; ++pr) {
+            TNK_CUDA_OK(cudaMemsetAsync(peers.parts[pr] + peers.rank, 0, sizeof(double), st));
+            if (row_end > row_begin && pr != peers.rank)
+                TNK_CUDA_OK(cudaMemsetAsync(peers.u[pr] + row_begin, 0, (row_end - row_begin) * sizeof(double), st));
+        }
         if (n_launch) *n_launch = 0;
         return 0;
     }
@@ -565,14 +589,47 @@ extern "C" int tnk_ksd_rows(int n_latent, double length_scale, int precision,
 
     if (q_dtype == 0)
         finish_rows_kernel<double><<<(unsigned)p.finish_blocks, 256, 0, st>>>(part, p.splits, p.launch_rows, p.row0, row_begin, row_end,
-                                                                             (const double*)q, u, blockpart);
+                                                                             (const double*)q, u, blockpart, peers);
     else
         finish_rows_kernel<float><<<(unsigned)p.finish_blocks, 256, 0, st>>>(part, p.splits, p.launch_rows, p.row0, row_begin, row_end,
-                                                                            (const float*)q, u, blockpart);
+                                                                            (const float*)q, u, blockpart, peers);
     TNK_CUDA_OK(cudaGetLastError());
-    finish_scalar_kernel<<<1, 256, 0, st>>>(blockpart, p.finish_blocks, ksd_part);
+    finish_scalar_kernel<<<1, 256, 0, st>>>(blockpart, p.finish_blocks, ksd_part, peers);
     TNK_CUDA_OK(cudaGetLastError());
     launches += 2;
     if (n_launch) *n_launch = launches;
     return 0;
+}
+
+extern "C" int tnk_ksd_rows(int n_latent, double length_scale, int precision,
+                            const void* q, int q_dtype, const void* ST, const void* Cst,
+                            int64_t row_begin, int64_t row_end,
+                            double* u, double* ksd_part,
+                            void* workspace, size_t workspace_bytes, int* n_launch, void* stream) {
+    PeerSinks none;
+    none.n = 0;
+    none.rank = 0;
+    return ksd_rows_impl(n_latent, length_scale, precision, q, q_dtype, ST, Cst, row_begin, row_end, u, ksd_part,
+                         workspace, workspace_bytes, n_launch, stream, none);
+}
+
+extern "C" int tnk_ksd_rows_peers(int n_latent, double length_scale, int precision,
+                                  const void* q, int q_dtype, const void* ST, const void* Cst,
+                                  int64_t row_begin, int64_t row_end,
+                                  int n_peers, int my_rank, void* const* peer_u, void* const* peer_parts,
+                                  double* ksd_part,
+                                  void* workspace, size_t workspace_bytes, int* n_launch, void* stream) {
+    TNK_REQUIRE(n_peers >= 1 && n_peers <= TNK_MAX_PEERS, "tnk_ksd_rows_peers: n_peers must be in [1,%d]", TNK_MAX_PEERS);
+    TNK_REQUIRE(my_rank >= 0 && my_rank < n_peers, "tnk_ksd_rows_peers: my_rank %d outside [0,%d)", my_rank, n_peers);
+    TNK_REQUIRE(peer_u && peer_parts, "tnk_ksd_rows_peers: NULL peer pointer table");
+    PeerSinks peers;
+    peers.n = n_peers;
+    peers.rank = my_rank;
+    for (int p = 0; p < n_peers; ++p) {
+        TNK_REQUIRE(peer_u[p] && peer_parts[p], "tnk_ksd_rows_peers: NULL buffer for peer %d", p);
+        peers.u[p] = (double*)peer_u[p];
+        peers.parts[p] = (double*)peer_parts[p];
+    }
+    return ksd_rows_impl(n_latent, length_scale, precision, q, q_dtype, ST, Cst, row_begin, row_end,
+                         peers.u[my_rank], ksd_part, workspace, workspace_bytes, n_launch, stream, peers);
 }

@@ -215,11 +215,80 @@ def combine_row_shards(u_rows, part, num_states, rank, world, group=None):
     return buf[:num_states], buf[num_states:].clone()
 
 
+class PeerExchange:
+    """Sinks of the fused exchange (tnk_ksd_rows_peers): per rank a symmetric-memory buffer
+    [buffers][N + world] of fp64 - u rows followed by one partial-K slot per rank - mapped into
+    every rank of the box (torch symmetric memory: cuMem + NVLink P2P).  The kernels that finish
+    a rank's rows store them into all ranks' buffers; `wait()` is the cross-rank barrier that
+    makes them visible.  Two buffers alternate so that a fast rank's next evaluation never
+    overwrites rows a slow rank is still reading."""
+
+    def __init__(self, num_states, device, group=None, buffers=2):
+        import torch.distributed._symmetric_memory as symm_mem
+        device = _require_cuda(device)
+        group = dist.group.WORLD if group is None else group
+        self.group, self.device = group, device
+        self.world, self.rank = dist.get_world_size(group), dist.get_rank(group)
+        if self.world > _lib.MAX_PEERS:
+            raise ValueError(f"the fused exchange covers one NVSwitch box (<= {_lib.MAX_PEERS} ranks)")
+        self.N, self.buffers = int(num_states), int(buffers)
+        self.stride = (self.N + self.world + 31) // 32 * 32            # doubles per buffer, 256-byte multiple
+        with torch.cuda.device(device):
+            self.local = symm_mem.empty(self.buffers * self.stride, dtype=torch.float64, device=device)
+            self.local.zero_()
+            self.handle = symm_mem.rendezvous(self.local, group)
+        self.base = [int(p) for p in self.handle.buffer_ptrs]
+        self.step = 0
+
+    def sinks(self):
+        """(peer_u, peer_parts) ctypes pointer tables of the buffer the next evaluation writes, and
+        the local views (u [N], parts [world]) of that buffer."""
+        b = self.step % self.buffers
+        self.step += 1
+        off = b * self.stride * 8
+        VP = ctypes.c_void_p * self.world
+        peer_u = VP(*[base + off for base in self.base])
+        peer_parts = VP(*[base + off + self.N * 8 for base in self.base])
+        view = self.local[b * self.stride:(b + 1) * self.stride]
+        return peer_u, peer_parts, view[:self.N], view[self.N:self.N + self.world]
+
+    def wait(self):
+        """Cross-rank barrier on the current stream (signal pads over NVLink, no NCCL)."""
+        with torch.cuda.device(self.device):
+            self.handle.barrier(channel=0)
+
+
+def ksd_rows_fused(tables, q, exchange):
+    """Row-sharded u = K_p q with the exchange fused into the reduction kernels: returns the full
+    u [N] (fp64 view of the symmetric buffer) and K [1] on every rank.  SURVEY.md section 8(e)."""
+    N, rank, world = tables.N, exchange.rank, exchange.world
+    if q.device != tables.device or q.dim() != 1 or q.numel() != N:
+        raise ValueError(f"q must be a 1-D tensor of {N} entries on {tables.device}")
+    if q.dtype not in (torch.float32, torch.float64):
+        raise ValueError("q must be float32 or float64")
+    q = q.contiguous()
+    r0, r1 = shard_rows(N, rank, world)
+    lib = _lib.load()
+    with torch.cuda.device(tables.device):
+        peer_u, peer_parts, u, parts = exchange.sinks()
+        part = torch.empty(1, dtype=torch.float64, device=tables.device)
+        ws = tables.workspace(r0, r1)
+        launched = ctypes.c_int(0)
+        _lib.check(lib.tnk_ksd_rows_peers(tables.n, tables.length_scale, tables.prec_code, _ptr(q),
+                                          0 if q.dtype == torch.float64 else 1, _ptr(tables.ST), _ptr(tables.Cst),
+                                          r0, r1, world, rank, peer_u, peer_parts, _ptr(part), _ptr(ws), ws.numel(),
+                                          ctypes.byref(launched), _stream_ptr(tables.device)), "tnk_ksd_rows_peers")
+        launch_counter["kernels"] += launched.value
+        exchange.wait()
+        K = parts.sum(dim=0, keepdim=True)          # fixed slot order: identical bits on every rank
+    return u, K
+
+
 class _KsdQuadraticForm(torch.autograd.Function):
     """K(q) = q^T K_p q with dK/dq = 2 K_p q, one pass over the pair space for both."""
 
     @staticmethod
-    def forward(ctx, q, tables, group, algorithm="pairs"):
+    def forward(ctx, q, tables, group, algorithm="pairs", exchange=None):
         q_dev = q.detach()
         if q_dev.dtype not in (torch.float32, torch.float64):
             q_dev = q_dev.to(torch.float64)
@@ -233,6 +302,9 @@ class _KsdQuadraticForm(torch.autograd.Function):
                 buf = torch.cat([u, part])
                 dist.all_reduce(buf, op=dist.ReduceOp.SUM, group=group)
                 u, part = buf[:-1], buf[-1:].clone()
+        elif exchange is not None and world > 1:
+            u, part = ksd_rows_fused(tables, q_dev, exchange)
+            u = u.clone()     # the symmetric buffer is rewritten two evaluations later
         else:
             r0, r1 = shard_rows(tables.N, rank, world)
             u, part = tables.ksd_rows(q_dev, r0, r1)
@@ -247,25 +319,27 @@ class _KsdQuadraticForm(torch.autograd.Function):
         (u,) = ctx.saved_tensors
         dtype, device = ctx.q_meta
         grad = (2.0 * grad_out.to(u.device, torch.float64)) * u
-        return grad.to(device=device, dtype=dtype), None, None, None
+        return grad.to(device=device, dtype=dtype), None, None, None, None
 
 
 ALGORITHMS = ("pairs", "modeproduct")
 
 
-def ksd_quadratic_form(q, tables, group=None, algorithm="pairs"):
+def ksd_quadratic_form(q, tables, group=None, algorithm="pairs", exchange=None):
     """KSD^2 = sum_ij q_i q_j k_p(z_i, z_j) as an fp64 scalar tensor on q's device, differentiable
     w.r.t. q (any float dtype, CPU or CUDA; e.g. PennyLane probabilities).  Drop-in for the double
     loop of reference ksd_vi.py:110-131 / ksd_vi_quantum.py:122-142.  When torch.distributed is
     initialised the rows of the pair space are sharded over the ranks of `group`.
     algorithm="pairs" evaluates all 4^n pairs on the fly (the reference's loop, tiled);
     algorithm="modeproduct" returns the same value through the Kronecker factorisation of the
-    Hamming kernel in O(n^2 2^n) (fp64), with the score components sharded over the ranks."""
+    Hamming kernel in O(n^2 2^n) (fp64), with the score components sharded over the ranks.
+    exchange: a PeerExchange makes the sharded "pairs" evaluation store its rows straight into every
+    rank's buffer over NVLink (tnk_ksd_rows_peers) instead of calling an NCCL collective."""
     if algorithm not in ALGORITHMS:
         raise ValueError(f"algorithm must be one of {ALGORITHMS}")
     if q.dim() != 1 or q.numel() != tables.N:
         raise ValueError(f"Probabilities shape mismatch: {tuple(q.shape)}")
-    return _KsdQuadraticForm.apply(q, tables, group, algorithm)
+    return _KsdQuadraticForm.apply(q, tables, group, algorithm, exchange)
 
 
 def alu_peak(precision="fp32", iters=4096, device="cuda"):

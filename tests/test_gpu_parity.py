@@ -221,3 +221,17 @@ def test_modeproduct_matches_pair_kernel_n20(ops):
     torch.cuda.synchronize()
     assert abs(k_pair.item() - k_mp.item()) <= 1e-6 * abs(k_mp.item())
     assert (u_pair - u_mp).abs().max().item() <= 1e-6 * u_mp.abs().max().item()
+
+
+def test_fused_peer_exchange_world2(ops):
+    """tnk_ksd_rows_peers on 2 GPUs of the box: same u and K as the NCCL path on every rank."""
+    import os, subprocess, sys
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs on one box")
+    repo = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2",
+           "--master-addr", "127.0.0.1", "--master-port", "29531",
+           os.path.join(repo, "scripts", "check_fused_exchange.py"), "12", "fp64"]
+    res = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+    assert res.returncode == 0, res.stdout[-2000:] + res.stderr[-4000:]
+    assert '"fused_exchange": "ok"' in res.stdout
