@@ -26,6 +26,9 @@ extern "C" {
 #define TNK_PREC_FP32 1        /* FFMA pair arithmetic, fp64 accumulation across tiles (1e-4 mode) */
 #define TNK_PREC_FP64_SIMPLE 2 /* one-thread-per-row fp64 check kernel (debug / cross-check only) */
 
+#define TNK_PREC_TC32 4        /* tensor-core tiles: tcgen05.mma kind::tf32 with a 3xTF32 split (fp32-grade, 1e-4 mode),
+                                  Hamming weights and row sums on the ALU; 7 <= n <= 24, else the FP32 kernel runs */
+
 #define TNK_PEAK_FP32X2 3      /* tnk_alu_peak only: packed fma.rn.f32x2 chain (2 lane-ops per instruction) */
 
 /* node kinds of the flattened network (tnk_bn_joint) */
@@ -125,6 +128,12 @@ int tnk_ksd_modeproduct(int n_latent, double length_scale, const void* q, int q_
                         const double* ST64, int bit_begin, int bit_end,
                         double* u, double* ksd_part,
                         void* workspace, size_t workspace_bytes, int* n_launch, void* stream);
+
+/* Introspection of the tensor-core variant (TNK_PREC_TC32): padded score length, chunks (4 floats)
+ * per state of the row and column operand tables, and the MMA K-step list - step k multiplies row
+ * chunks {s[4k], s[4k]+s[4k+1]} with column chunks {s[4k+2], s[4k+2]+s[4k+3]}.  steps: host int32
+ * [4*32] or NULL.  Used by the CPU tests to check that the steps cover the bracket exactly. */
+int tnk_tc_plan(int n_latent, int* np, int* ka, int* kb, int* nsteps, int32_t* steps);
 
 /* Measurement hook: when both are non-NULL cudaEvent_t handles, every following tnk_ksd_rows call
  * on this host thread records them on its stream immediately before and after the pair kernel

@@ -16,17 +16,17 @@ REPO_DIR = os.path.dirname(PKG_DIR)
 CSRC = os.path.join(PKG_DIR, "csrc")
 INCLUDE = os.path.join(REPO_DIR, "include")
 LIB_PATH = os.path.join(PKG_DIR, "libtnk_b200.so")
-SOURCES = ["tnk_enum.cu", "tnk_ksd.cu", "tnk_peak.cu", "tnk_modeprod.cu"]
+SOURCES = ["tnk_enum.cu", "tnk_ksd.cu", "tnk_peak.cu", "tnk_modeprod.cu", "tnk_tc.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC", "-I", INCLUDE]
 
-PREC_FP64, PREC_FP32, PREC_FP64_SIMPLE = 0, 1, 2
+PREC_FP64, PREC_FP32, PREC_FP64_SIMPLE, PREC_TC32 = 0, 1, 2, 4
 MAX_PEERS = 8  # TNK_MAX_PEERS
 
 # every symbol include/tnk.h declares
 EXPORTS = ["tnk_last_error", "tnk_version", "tnk_bn_joint", "tnk_ksd_layout", "tnk_score",
            "tnk_ksd_workspace_bytes", "tnk_ksd_rows", "tnk_ksd_rows_peers", "tnk_ksd_timing_events", "tnk_alu_peak",
-           "tnk_ksd_modeproduct_workspace_bytes", "tnk_ksd_modeproduct"]
+           "tnk_ksd_modeproduct_workspace_bytes", "tnk_ksd_modeproduct", "tnk_tc_plan"]
 
 
 def _nvcc():
@@ -106,6 +106,9 @@ def load():
     lib.tnk_ksd_modeproduct.restype = c_int
     lib.tnk_ksd_modeproduct.argtypes = [c_int, c_dbl, c_vp, c_int, c_vp, c_int, c_int, c_vp, c_vp, c_vp, c_sz,
                                         ctypes.POINTER(c_int), c_vp]
+    lib.tnk_tc_plan.restype = c_int
+    lib.tnk_tc_plan.argtypes = [c_int, ctypes.POINTER(c_int), ctypes.POINTER(c_int), ctypes.POINTER(c_int),
+                                ctypes.POINTER(c_int), ctypes.POINTER(ctypes.c_int32)]
     lib.tnk_ksd_timing_events.restype = c_int
     lib.tnk_ksd_timing_events.argtypes = [c_vp, c_vp]
     lib.tnk_alu_peak.restype = c_int

@@ -46,7 +46,7 @@ static inline int tnk_geom(int n, int precision, TnkGeom* g) {
     if (np < 4) np = 4;
     if (np > 32) return 1;
     g->np = np;
-    if (precision == TNK_PREC_FP32) {
+    if (precision == TNK_PREC_FP32 || precision == TNK_PREC_TC32) {
         g->elem = 4; g->R = (np <= 24) ? 4 : 2; g->TC = 256;
     } else if (precision == TNK_PREC_FP64 || precision == TNK_PREC_FP64_SIMPLE) {
         g->elem = 8; g->R = (np <= 24) ? 2 : 1; g->TC = 128;

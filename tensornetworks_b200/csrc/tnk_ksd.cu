@@ -23,6 +23,7 @@
 // a^h: h = popc(upper bits) + popc(low bits); the low part is a compile-time power of a
 // folded into q_j, the upper part is one LUT fetch per (thread, 8 columns).
 #include "tnk_common.cuh"
+#include "tnk_tc.cuh"
 
 namespace {
 
@@ -433,19 +434,22 @@ struct Plan {
     TnkGeom g;
     int64_t N, row0, launch_rows, n_tiles, finish_blocks;
     int row_blocks, splits;
-    size_t off_q, off_part, off_block, total;
+    bool tensor;          // TNK_PREC_TC32 with a tensor-core plan (7 <= n <= 24); else the ALU kernels
+    TnkTcPlan tc;
+    size_t off_q, off_part, off_block, off_a, off_b, total;
 };
 
 int make_plan(int n, int precision, int64_t row_begin, int64_t row_end, Plan* p) {
     if (tnk_geom(n, precision, &p->g)) return 1;
     p->N = (int64_t)1 << n;
     if (row_begin < 0 || row_end > p->N || row_begin > row_end) return 1;
-    const int64_t RB = (int64_t)kThreads * p->g.R;
+    p->tensor = precision == TNK_PREC_TC32 && tnk_tc_make_plan(n, &p->tc) == 0;
+    const int64_t RB = p->tensor ? (int64_t)TNK_TC_TILE : (int64_t)kThreads * p->g.R;
     p->row0 = (row_begin / RB) * RB;
     const int64_t row_hi = ((row_end + RB - 1) / RB) * RB;
     p->row_blocks = (int)((row_hi - p->row0) / RB);
     p->launch_rows = row_hi - p->row0;
-    p->n_tiles = p->g.n_pad / p->g.TC;
+    p->n_tiles = p->tensor ? p->N / TNK_TC_TILE : p->g.n_pad / p->g.TC;
     int sms = 148;
     int splits = 1;
     if (precision != TNK_PREC_FP64_SIMPLE) {
@@ -457,6 +461,11 @@ int make_plan(int n, int precision, int64_t row_begin, int64_t row_end, Plan* p)
     p->off_q = off;      off += ((size_t)p->g.n_pad * p->g.elem + 255) / 256 * 256;
     p->off_part = off;   off += ((size_t)splits * p->launch_rows * sizeof(double) + 255) / 256 * 256;
     p->off_block = off;  off += ((size_t)(p->finish_blocks + 1) * sizeof(double) + 255) / 256 * 256;
+    p->off_a = p->off_b = off;
+    if (p->tensor) {
+        p->off_a = off;  off += (tnk_tc_table_bytes(p->tc, p->launch_rows, false) + 255) / 256 * 256;
+        p->off_b = off;  off += (tnk_tc_table_bytes(p->tc, p->N, true) + 255) / 256 * 256;
+    }
     p->total = off;
     return 0;
 }
@@ -567,6 +576,13 @@ static int ksd_rows_impl(int n_latent, double length_scale, int precision,
     ++launches;
 
     int rc = 0;
+    if (p.tensor) {
+        rc = tnk_tc_launch(n, prm.a, prm.gamma, prm.wl, (const float*)ST, (const float*)Cst, (const float*)qT,
+                           p.row0, p.launch_rows, p.splits, (float*)(ws + p.off_a), (float*)(ws + p.off_b), part,
+                           g_ev_start, g_ev_stop, &launches, st);
+        if (rc) return rc;
+        --launches;   // the common "++launches" below counts the pair kernel
+    } else {
     if (g_ev_start) TNK_CUDA_OK(cudaEventRecord(g_ev_start, st));
     if (precision == TNK_PREC_FP64_SIMPLE) {
         const unsigned blocks = (unsigned)((row_end - row_begin + 127) / 128);
@@ -575,7 +591,7 @@ static int ksd_rows_impl(int n_latent, double length_scale, int precision,
         TNK_CUDA_OK(cudaGetLastError());
     } else {
         dim3 grid((unsigned)p.row_blocks, (unsigned)p.splits, 1);
-        if (precision == TNK_PREC_FP32) {
+        if (precision == TNK_PREC_FP32 || precision == TNK_PREC_TC32) {
             if (p.g.R == 4) rc = dispatch_np<float, 4, 256>(p.g.np, prm, grid, ST, Cst, qT, part, st);
             else rc = dispatch_np_wide<float, 2, 256>(p.g.np, prm, grid, ST, Cst, qT, part, st);
         } else {
@@ -585,6 +601,7 @@ static int ksd_rows_impl(int n_latent, double length_scale, int precision,
         if (rc) return rc;
     }
     if (g_ev_stop) TNK_CUDA_OK(cudaEventRecord(g_ev_stop, st));
+    }
     ++launches;
 
     if (q_dtype == 0)

@@ -16,7 +16,8 @@ import torch.distributed as dist
 from . import _lib
 from .flatten import flatten_bn
 
-PRECISIONS = {"fp64": _lib.PREC_FP64, "fp32": _lib.PREC_FP32, "fp64_simple": _lib.PREC_FP64_SIMPLE}
+PRECISIONS = {"fp64": _lib.PREC_FP64, "fp32": _lib.PREC_FP32, "fp64_simple": _lib.PREC_FP64_SIMPLE,
+              "tc32": _lib.PREC_TC32}
 launch_counter = {"kernels": 0}  # kernels of ours enqueued since last reset (bench.py's gpu_launches)
 
 

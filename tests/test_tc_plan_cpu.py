@@ -1,0 +1,93 @@
+"""CPU checks of the tensor-core variant's host planner (tnk_tc_plan): the MMA K-steps must cover
+every chunk product of the bracket exactly once with increasing chunk offsets, and the feature
+layout it assumes (csrc/tnk_tc.cu header) must reproduce u = K_p q of the oracle when the steps,
+the 3xTF32 split and the epilogue's Hamming weights are emulated in numpy."""
+import ctypes
+
+import numpy as np
+import pytest
+
+from oracle import ksd_oracle as orc
+from tensornetworks_b200 import _lib
+from tensornetworks_b200.synthetic import random_binary_bn, random_q
+
+FA = [0, 0, 1, 2, 2, 3, 3, 4]
+FB = [0, 1, 0, 2, 3, 4, 5, 4]
+
+
+def plan(n):
+    lib = _lib.load()
+    np_, ka, kb, ns = ctypes.c_int(), ctypes.c_int(), ctypes.c_int(), ctypes.c_int()
+    steps = (ctypes.c_int32 * 128)()
+    _lib.check(lib.tnk_tc_plan(n, ctypes.byref(np_), ctypes.byref(ka), ctypes.byref(kb), ctypes.byref(ns), steps), "tnk_tc_plan")
+    return np_.value, ka.value, kb.value, [tuple(steps[4 * k:4 * k + 4]) for k in range(ns.value)]
+
+
+@pytest.mark.parametrize("n", range(7, 25))
+def test_steps_cover_the_bracket(n):
+    np_, ka, kb, steps = plan(n)
+    nc = np_ // 4
+    assert np_ == (n + 3) // 4 * 4 and ka == 5 * nc + 2 and kb == 6 * nc + 2
+    want = sorted([(FA[f] * nc + c, FB[f] * nc + c) for f in range(8) for c in range(nc)]
+                  + [(5 * nc, 6 * nc), (5 * nc + 1, 6 * nc + 1)])
+    got = []
+    for a0, alb, b0, blb in steps:
+        assert alb > 0 and blb > 0 and a0 + alb < ka and b0 + blb < kb
+        assert alb * 128 < (1 << 14) and blb * 128 < (1 << 14)      # 14-bit LBO field in 16-byte units
+        got += [(a0, b0), (a0 + alb, b0 + blb)]
+    assert sorted(got) == want
+    assert len(steps) <= 32
+
+
+def test_unsupported_sizes_are_rejected():
+    lib = _lib.load()
+    for n in (0, 3, 6, 25, 30):
+        assert lib.tnk_tc_plan(n, None, None, None, None, None) != 0
+
+
+def _tf_hi(x):
+    return (np.asarray(x, dtype=np.float32).view(np.uint32) & np.uint32(0xFFFFE000)).view(np.float32)
+
+
+@pytest.mark.parametrize("n", [7, 9])
+def test_emulated_tiles_match_oracle(n):
+    """numpy emulation of tc_pack_kernel + the K-step list + the epilogue weights."""
+    bn, lat, obs, x = random_binary_bn(n, seed=n)
+    P = orc.joint_table(bn, x, lat)
+    S = orc.score_table(P, n)                      # [N, n], latent-variable order
+    q64 = random_q(1 << n, seed=n).numpy()
+    Kref, gref = orc.ksd_dense(q64, S, n)
+    N = 1 << n
+    np_, ka, kb, steps = plan(n)
+    nc = np_ // 4
+    a = np.exp(-1.0 / n)
+    alpha, gamma = 1.0 - a, a - 1.0 / a
+    z = np.arange(N)
+    s = np.zeros((N, np_), dtype=np.float32)
+    s[:, :n] = S[:, ::-1].astype(np.float32)       # bit position p = latent variable n-1-p
+    bit = np.zeros((N, np_), dtype=np.float32)
+    bit[:, :n] = ((z[:, None] >> np.arange(n)[None, :]) & 1)
+    valid = np.zeros(np_, dtype=np.float32); valid[:n] = 1
+    rho = (1 - s) * (1 - 2 * bit) * valid
+    R = ((1 - s) * valid).sum(1)
+    C = (alpha * R + gamma * ((1 - s) * bit).sum(1)).astype(np.float32)
+    q = q64.astype(np.float32)
+    hi, lo = _tf_hi, lambda v: np.asarray(v, dtype=np.float32) - _tf_hi(v)
+    g = np.float32(gamma) * rho
+    t = q[:, None] * s
+    r = (np.float32(gamma) * q)[:, None] * rho
+    zero = np.zeros(N, dtype=np.float32)
+    A = np.concatenate([hi(s), lo(s), bit, hi(g), lo(g),
+                        np.stack([zero + 1, zero + 1, hi(C), hi(C)], 1), np.stack([lo(C), zero, zero, zero], 1)], 1)
+    B = np.concatenate([hi(t), lo(t), hi(r), lo(r), bit * hi(q)[:, None], bit * lo(q)[:, None],
+                        np.stack([hi(q * C), lo(q * C), hi(q), lo(q)], 1), np.stack([hi(q), zero, zero, zero], 1)], 1)
+    assert A.shape[1] == 4 * ka and B.shape[1] == 4 * kb
+    A64, B64 = A.astype(np.float64), B.astype(np.float64)
+    D = np.zeros((N, N))
+    for a0, alb, b0, blb in steps:
+        for ca, cb in ((a0, b0), (a0 + alb, b0 + blb)):
+            D += A64[:, 4 * ca:4 * ca + 4] @ B64[:, 4 * cb:4 * cb + 4].T
+    h = np.array([[bin(i ^ j).count("1") for j in range(N)] for i in range(N)])
+    u = (np.exp(-h / n) * D).sum(1)
+    assert abs(q64 @ u - Kref) <= 2e-6 * abs(Kref)
+    assert np.max(np.abs(2 * u - gref)) <= 2e-6 * np.max(np.abs(gref))
