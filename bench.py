@@ -30,7 +30,8 @@ def parse_args():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--n", type=int, default=20, help="latent bits (BASELINE.json quotes the metric at n=20)")
-    ap.add_argument("--precision", default="fp32", choices=["fp32", "fp64"])
+    ap.add_argument("--precision", default="fp32", choices=["fp32", "fp64", "tc32"],
+                    help="pair-kernel arithmetic: fp32/fp64 ALU kernels or tc32 = tcgen05 tf32 tiles with 3xTF32 split")
     ap.add_argument("--seed", type=int, default=0)
     ap.add_argument("--exchange", default="fused", choices=["fused", "nccl"],
                     help="N>1: rows stored into every rank's buffer by the reduction kernel over NVLink (fused) "
@@ -203,8 +204,8 @@ def run_ours(args):
         K.backward()                               # D2H of dK/dq inside
         return float(K.item()), qh.grad
 
-    # roofline denominator: measured FMA-chain rate of this GPU, same run
-    peak_rate, _ = ops.alu_peak(args.precision, iters=8192, device=device)
+    # roofline denominator of the ALU kernels: measured FMA-chain rate of this GPU, same run
+    peak_rate, _ = ops.alu_peak("fp32" if args.precision == "tc32" else args.precision, iters=8192, device=device)
 
     for _ in range(max(args.warmup, 3)):
         flush.zero_()
@@ -278,20 +279,38 @@ def main():
         kernel_s = r["kmean_ms"].item() * 1e-3
         executed = pairs / world                          # this kernel evaluates every ordered pair of its rows
         achieved = executed * w_lane / kernel_s
+        roofline = {"bound": "alu", "achieved": achieved / 1e12, "peak": r["peak_rate"] / 1e12,
+                    "unit": "Tlane-op/s", "frac": achieved / r["peak_rate"], "traffic": None,
+                    "kernel": "ksd_rows_kernel", "kernel_ms": r["kmean_ms"].item(),
+                    "lane_ops_per_pair": w_lane,
+                    "peak_source": "tnk_alu_peak FMA-chain probe measured in this run (MEASURED_PEAKS.json has no ALU peak)"}
+        if args.precision == "tc32":
+            from tensornetworks_b200 import ops as _ops
+            plan = _ops.tc_plan(n)
+            flops_pair = 2 * 8 * plan["nsteps"]            # MMA flops issued per pair (K = 8 per tf32 K-step)
+            peaks = load_measured_peaks()
+            bf16 = peaks.get("bf16_tflops_sustained") or peaks.get("bf16_tflops")
+            peak_tf = (bf16 / 2.0) if bf16 else 1590.0 / 2.0
+            ach_tf = executed * flops_pair / kernel_s / 1e12
+            roofline = {"bound": "tensor", "achieved": ach_tf, "peak": peak_tf, "unit": "TFLOP/s",
+                        "frac": ach_tf / peak_tf, "traffic": None, "kernel": "tc_rows_kernel",
+                        "kernel_ms": r["kmean_ms"].item(), "mma_flops_per_pair": flops_pair,
+                        "k_steps": plan["nsteps"],
+                        "peak_source": ("half of MEASURED_PEAKS.json bf16_tflops_sustained (kind::tf32 runs at half the "
+                                        "bf16 rate; the kernel is timed inside a long step)" if bf16 else
+                                        "half of the fallback 1.59 PFLOP/s bf16 figure of B200_PROFILING.md"),
+                        "alu_epilogue_lane_ops_per_pair": 1.5}
         line = {
             "metric": METRIC, "value": r["value"], "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": r["ms_per_step"], "higher_is_better": True,
             "scaling": "strong", "vs_baseline": None,
-            "dtype": "f32" if args.precision == "fp32" else "f64", "data": "synthetic",
+            "dtype": {"fp32": "f32", "fp64": "f64", "tc32": "tf32x3"}[args.precision], "data": "synthetic",
             "config": {"workload": workload_name(n), "n_latent": n, "pairs_per_step": pairs,
-                       "precision_mode": args.precision + ("-compute/fp64-accumulate" if args.precision == "fp32" else ""),
+                       "precision_mode": {"fp32": "fp32-compute/fp64-accumulate", "fp64": "fp64",
+                                          "tc32": "3xTF32 tensor-core tiles (fp32 accumulate per tile, fp64 across tiles)"}[args.precision],
                        "parallelism": (f"row-sharded x{world}, exchange={r['exchange_name']}" if world > 1 else "single GPU"),
                        "l2": "256 MB flush written between timed steps", "executed_pairs": "4^n (symmetry not exploited)"},
-            "roofline": {"bound": "alu", "achieved": achieved / 1e12, "peak": r["peak_rate"] / 1e12,
-                         "unit": "Tlane-op/s", "frac": achieved / r["peak_rate"], "traffic": None,
-                         "kernel": "ksd_rows_kernel", "kernel_ms": r["kmean_ms"].item(),
-                         "lane_ops_per_pair": w_lane,
-                         "peak_source": "tnk_alu_peak FMA-chain probe measured in this run (MEASURED_PEAKS.json has no ALU peak)"},
+            "roofline": roofline,
             "e2e": {"value": r["e2e_value"], "unit": UNIT, "h2d_bytes_per_step": 8 * (1 << n) * world,
                     "d2h_bytes_per_step": (8 * (1 << n) + 8) * world},
             "gpu_launches": r["launches"], "clocks": r["clocks"], "ksd_sq": r["K_value"],

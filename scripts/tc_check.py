@@ -5,7 +5,7 @@ import torch
 from tensornetworks_b200 import ops
 from tensornetworks_b200.synthetic import random_binary_bn, random_q
 
-sizes = [int(a) for a in sys.argv[1].split(",")] if len(sys.argv) > 1 else [7, 8, 10, 12, 14]
+sizes = [int(a) for a in sys.argv[1].split(",") if a] if len(sys.argv) > 1 else [7, 8, 10, 12, 14]
 time_sizes = [int(a) for a in sys.argv[2].split(",")] if len(sys.argv) > 2 and sys.argv[2] else []
 for n in sizes:
     bn, lat, obs, x = random_binary_bn(n, seed=n)

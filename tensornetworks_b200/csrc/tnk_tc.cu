@@ -99,8 +99,6 @@ struct TcParams {
     int64_t n_tiles;     // column tiles in total (2^n / 128)
     int col_splits;      // gridDim.y
     int64_t part_stride; // rows covered by the launch
-    int ka, kb, nsteps;
-    uint16_t a0[TNK_TC_MAX_STEPS], alb[TNK_TC_MAX_STEPS], b0[TNK_TC_MAX_STEPS], blb[TNK_TC_MAX_STEPS];
     float wl[32];        // w[h] = exp(-h/(n l))
 };
 
@@ -163,13 +161,16 @@ tc_pack_kernel(int n, int np, int64_t first_state, int64_t n_tiles, float gamma,
     out[idx] = make_float4(v[0], v[1], v[2], v[3]);
 }
 
-// ---- the tile kernel
+// ---- the tile kernel, NC = 4-float chunks per field (np / 4)
+template <int NC>
 __global__ void __launch_bounds__(kTcThreads, 1)
 tc_rows_kernel(const __grid_constant__ TcParams prm, const float* __restrict__ A_tab, const float* __restrict__ B_tab,
                double* __restrict__ part) {
     extern __shared__ __align__(1024) unsigned char smem[];
-    const uint32_t a_bytes = (uint32_t)prm.ka * kChunkBytes;
-    const uint32_t b_bytes = (uint32_t)prm.kb * kChunkBytes;
+    constexpr TnkTcSteps P = tnk_tc_steps(NC);
+    static_assert(P.ok, "no K-step plan for this chunk count");
+    constexpr uint32_t a_bytes = (uint32_t)(5 * NC + 2) * kChunkBytes;
+    constexpr uint32_t b_bytes = (uint32_t)(6 * NC + 2) * kChunkBytes;
     unsigned char* sA = smem;
     unsigned char* sB = smem + a_bytes;
     float* sWl = reinterpret_cast<float*>(smem + a_bytes + 2 * b_bytes);
@@ -229,8 +230,10 @@ tc_rows_kernel(const __grid_constant__ TcParams prm, const float* __restrict__ A
         }
     } else if (warp == 1) {
         if (lane == 0) {
-            // ===== MMA issuer
-            const uint32_t a_addr = smem_u32(sA);
+            // ===== MMA issuer.  Every descriptor is the tile's base descriptor plus a compile-time
+            // offset (address field and LBO field in 16-byte units), so a K-step costs a few uniform
+            // integer instructions around the UTCHMMA.
+            const uint64_t a_desc = smem_desc(smem_u32(sA), 0);
             mbar_wait(bar_afull, 0);
             for (int64_t it = 0; it < n_local; ++it) {
                 const int s = (int)(it & 1);
@@ -238,11 +241,13 @@ tc_rows_kernel(const __grid_constant__ TcParams prm, const float* __restrict__ A
                 mbar_wait(bar_tempty + s, ph ^ 1u);
                 mbar_wait(bar_full + s, ph);
                 tc_fence_after();
-                const uint32_t b_addr = smem_u32(sB + (size_t)s * b_bytes);
+                const uint64_t b_desc = smem_desc(smem_u32(sB) + (uint32_t)s * b_bytes, 0);
                 const uint32_t d_addr = tmem_base + (uint32_t)(s * kTile);
-                for (int ks = 0; ks < prm.nsteps; ++ks) {
-                    const uint64_t da = smem_desc(a_addr + (uint32_t)prm.a0[ks] * kChunkBytes, (uint32_t)prm.alb[ks] * kChunkBytes);
-                    const uint64_t db = smem_desc(b_addr + (uint32_t)prm.b0[ks] * kChunkBytes, (uint32_t)prm.blb[ks] * kChunkBytes);
+#pragma unroll
+                for (int ks = 0; ks < P.nsteps; ++ks) {
+                    constexpr uint32_t cu = kChunkBytes >> 4;   // one chunk in descriptor address units
+                    const uint64_t da = a_desc + (uint64_t)((uint32_t)P.a0[ks] * cu + (((uint32_t)P.alb[ks] * cu) << 16));
+                    const uint64_t db = b_desc + (uint64_t)((uint32_t)P.b0[ks] * cu + (((uint32_t)P.blb[ks] * cu) << 16));
                     umma_tf32(d_addr, da, db, kIdesc, ks > 0 ? 1u : 0u);
                 }
                 umma_commit(bar_empty + s);   // B stage free once these MMAs have read it
@@ -310,32 +315,6 @@ tc_rows_kernel(const __grid_constant__ TcParams prm, const float* __restrict__ A
     }
 }
 
-struct Prod { int a, b; };
-
-bool match_rest(Prod* items, int count, bool* used, TnkTcPlan* p) {
-    int x = -1;
-    for (int k = 0; k < count; ++k)
-        if (!used[k]) { x = k; break; }
-    if (x < 0) return true;
-    used[x] = true;
-    for (int y = x + 1; y < count; ++y) {
-        if (used[y]) continue;
-        int lo = -1, hi = -1;
-        if (items[x].a < items[y].a && items[x].b < items[y].b) { lo = x; hi = y; }
-        else if (items[y].a < items[x].a && items[y].b < items[x].b) { lo = y; hi = x; }
-        if (lo < 0) continue;
-        used[y] = true;
-        const int ks = p->nsteps++;
-        p->a0[ks] = (uint16_t)items[lo].a; p->alb[ks] = (uint16_t)(items[hi].a - items[lo].a);
-        p->b0[ks] = (uint16_t)items[lo].b; p->blb[ks] = (uint16_t)(items[hi].b - items[lo].b);
-        if (match_rest(items, count, used, p)) return true;
-        --p->nsteps;
-        used[y] = false;
-    }
-    used[x] = false;
-    return false;
-}
-
 }  // namespace
 
 // Host planner: chunk products (A-chunk x B-chunk) of the bracket, two per MMA K-step.
@@ -343,25 +322,9 @@ int tnk_tc_make_plan(int n, TnkTcPlan* p) {
     if (n < TNK_TC_MIN_LATENT || n > TNK_TC_MAX_LATENT) return 1;
     const int np = ((n + 3) / 4) * 4;
     const int nc = np / 4;
-    p->np = np; p->nc = nc; p->ka = 5 * nc + 2; p->kb = 6 * nc + 2; p->nsteps = 0;
-    static const int FA[8] = {0, 0, 1, 2, 2, 3, 3, 4};   // s_hi s_hi s_lo bits bits g_hi g_hi g_lo
-    static const int FB[8] = {0, 1, 0, 2, 3, 4, 5, 4};   // t_hi t_lo t_hi r_hi r_lo bq_hi bq_lo bq_hi
-    Prod rest[16];
-    int nrest = 0;
-    for (int f = 0; f < 8; ++f) {
-        int c = 0;
-        for (; c + 1 < nc; c += 2) {
-            const int ks = p->nsteps++;
-            p->a0[ks] = (uint16_t)(FA[f] * nc + c); p->alb[ks] = 1;
-            p->b0[ks] = (uint16_t)(FB[f] * nc + c); p->blb[ks] = 1;
-        }
-        if (c < nc) rest[nrest++] = Prod{FA[f] * nc + c, FB[f] * nc + c};
-    }
-    rest[nrest++] = Prod{5 * nc, 6 * nc};
-    rest[nrest++] = Prod{5 * nc + 1, 6 * nc + 1};
-    bool used[16] = {false};
-    if ((nrest & 1) || !match_rest(rest, nrest, used, p)) return 1;
-    return p->nsteps <= TNK_TC_MAX_STEPS ? 0 : 1;
+    p->np = np; p->nc = nc; p->ka = 5 * nc + 2; p->kb = 6 * nc + 2;
+    p->s = tnk_tc_steps(nc);
+    return p->s.ok ? 0 : 1;
 }
 
 extern "C" int tnk_tc_plan(int n_latent, int* np, int* ka, int* kb, int* nsteps, int32_t* steps) {
@@ -371,11 +334,11 @@ extern "C" int tnk_tc_plan(int n_latent, int* np, int* ka, int* kb, int* nsteps,
     if (np) *np = p.np;
     if (ka) *ka = p.ka;
     if (kb) *kb = p.kb;
-    if (nsteps) *nsteps = p.nsteps;
+    if (nsteps) *nsteps = p.s.nsteps;
     if (steps)
-        for (int ks = 0; ks < p.nsteps; ++ks) {
-            steps[4 * ks + 0] = p.a0[ks]; steps[4 * ks + 1] = p.alb[ks];
-            steps[4 * ks + 2] = p.b0[ks]; steps[4 * ks + 3] = p.blb[ks];
+        for (int ks = 0; ks < p.s.nsteps; ++ks) {
+            steps[4 * ks + 0] = p.s.a0[ks]; steps[4 * ks + 1] = p.s.alb[ks];
+            steps[4 * ks + 2] = p.s.b0[ks]; steps[4 * ks + 3] = p.s.blb[ks];
         }
     return 0;
 }
@@ -383,6 +346,18 @@ extern "C" int tnk_tc_plan(int n_latent, int* np, int* ka, int* kb, int* nsteps,
 size_t tnk_tc_table_bytes(const TnkTcPlan& p, int64_t states, bool is_b) {
     return (size_t)states * (size_t)(is_b ? p.kb : p.ka) * 16;
 }
+
+namespace {
+template <int NC>
+int launch_tiles(const TcParams& prm, dim3 grid, const float* A_tab, const float* B_tab, double* part, cudaStream_t st) {
+    const size_t smem = (size_t)((5 * NC + 2) + 2 * (6 * NC + 2)) * kChunkBytes + 32 * sizeof(float) + 9 * sizeof(uint64_t) + 16;
+    auto kern = tc_rows_kernel<NC>;
+    TNK_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    kern<<<grid, kTcThreads, smem, st>>>(prm, A_tab, B_tab, part);
+    TNK_CUDA_OK(cudaGetLastError());
+    return 0;
+}
+}  // namespace
 
 // Builds both operand tables and launches the tile kernel.  qT: packed fp32 q [>= 2^n].
 int tnk_tc_launch(int n, double a, double gamma, const double* wl, const float* ST, const float* Cst, const float* qT,
@@ -407,17 +382,19 @@ int tnk_tc_launch(int n, double a, double gamma, const double* wl, const float* 
     }
     TcParams prm;
     prm.n = n; prm.row0 = row0; prm.n_tiles = col_tiles; prm.col_splits = splits; prm.part_stride = launch_rows;
-    prm.ka = p.ka; prm.kb = p.kb; prm.nsteps = p.nsteps;
-    for (int ks = 0; ks < TNK_TC_MAX_STEPS; ++ks) {
-        prm.a0[ks] = p.a0[ks]; prm.alb[ks] = p.alb[ks]; prm.b0[ks] = p.b0[ks]; prm.blb[ks] = p.blb[ks];
-    }
     for (int h = 0; h < 32; ++h) prm.wl[h] = (float)wl[h];
-    const size_t smem = (size_t)(p.ka + 2 * p.kb) * kChunkBytes + 32 * sizeof(float) + 9 * sizeof(uint64_t) + 16;
-    TNK_CUDA_OK(cudaFuncSetAttribute(tc_rows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     if (ev_start) TNK_CUDA_OK(cudaEventRecord(ev_start, st));
     dim3 grid((unsigned)row_tiles, (unsigned)splits, 1);
-    tc_rows_kernel<<<grid, kTcThreads, smem, st>>>(prm, A_tab, B_tab, part);
-    TNK_CUDA_OK(cudaGetLastError());
+    int rc = 2;
+    switch (p.nc) {
+        case 2: rc = launch_tiles<2>(prm, grid, A_tab, B_tab, part, st); break;
+        case 3: rc = launch_tiles<3>(prm, grid, A_tab, B_tab, part, st); break;
+        case 4: rc = launch_tiles<4>(prm, grid, A_tab, B_tab, part, st); break;
+        case 5: rc = launch_tiles<5>(prm, grid, A_tab, B_tab, part, st); break;
+        case 6: rc = launch_tiles<6>(prm, grid, A_tab, B_tab, part, st); break;
+        default: tnk_set_error("tnk_ksd_rows: no tensor-core kernel instance for %d chunks", p.nc); break;
+    }
+    if (rc) return rc;
     if (ev_stop) TNK_CUDA_OK(cudaEventRecord(ev_stop, st));
     if (launches) *launches += 3;
     return 0;

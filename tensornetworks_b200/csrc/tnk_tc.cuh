@@ -8,11 +8,67 @@
 #define TNK_TC_MIN_LATENT 7    // one full 128-state tile
 #define TNK_TC_MAX_LATENT 24   // shared memory: A tile + 2 B stages at np = 24 is 221 KB
 
+// K-step list for `nc` 4-float chunks per field.  Step ks multiplies A chunks {a0, a0+alb} with
+// B chunks {b0, b0+blb}.  constexpr so that the kernel (templated on nc) folds every descriptor
+// offset into an immediate; the host uses the same function for table sizes and the C-ABI dump.
+struct TnkTcSteps {
+    int nsteps;
+    bool ok;
+    int a0[TNK_TC_MAX_STEPS], alb[TNK_TC_MAX_STEPS], b0[TNK_TC_MAX_STEPS], blb[TNK_TC_MAX_STEPS];
+};
+
+// perfect matching of the left-over chunk products into steps with strictly increasing offsets
+__host__ __device__ constexpr bool tnk_tc_match(const int* ia, const int* ib, int count, bool* used, TnkTcSteps& p) {
+    int x = -1;
+    for (int k = 0; k < count; ++k)
+        if (!used[k]) { x = k; break; }
+    if (x < 0) return true;
+    used[x] = true;
+    for (int y = x + 1; y < count; ++y) {
+        if (used[y]) continue;
+        int lo = -1, hi = -1;
+        if (ia[x] < ia[y] && ib[x] < ib[y]) { lo = x; hi = y; }
+        else if (ia[y] < ia[x] && ib[y] < ib[x]) { lo = y; hi = x; }
+        if (lo < 0) continue;
+        used[y] = true;
+        const int ks = p.nsteps++;
+        p.a0[ks] = ia[lo]; p.alb[ks] = ia[hi] - ia[lo];
+        p.b0[ks] = ib[lo]; p.blb[ks] = ib[hi] - ib[lo];
+        if (tnk_tc_match(ia, ib, count, used, p)) return true;
+        --p.nsteps;
+        used[y] = false;
+    }
+    used[x] = false;
+    return false;
+}
+
+__host__ __device__ constexpr TnkTcSteps tnk_tc_steps(int nc) {
+    TnkTcSteps p{};
+    // field pairs: A {s_hi s_hi s_lo bits bits g_hi g_hi g_lo} x B {t_hi t_lo t_hi r_hi r_lo bq_hi bq_lo bq_hi}
+    const int FA[8] = {0, 0, 1, 2, 2, 3, 3, 4};
+    const int FB[8] = {0, 1, 0, 2, 3, 4, 5, 4};
+    int ra[16] = {}, rb[16] = {};
+    int nrest = 0;
+    for (int f = 0; f < 8; ++f) {
+        int c = 0;
+        for (; c + 1 < nc; c += 2) {
+            const int ks = p.nsteps++;
+            p.a0[ks] = FA[f] * nc + c; p.alb[ks] = 1;
+            p.b0[ks] = FB[f] * nc + c; p.blb[ks] = 1;
+        }
+        if (c < nc) { ra[nrest] = FA[f] * nc + c; rb[nrest] = FB[f] * nc + c; ++nrest; }
+    }
+    ra[nrest] = 5 * nc; rb[nrest] = 6 * nc; ++nrest;          // [1,1,C_hi,C_hi] x [(qC)_hi,(qC)_lo,q_hi,q_lo]
+    ra[nrest] = 5 * nc + 1; rb[nrest] = 6 * nc + 1; ++nrest;  // [C_lo,0,0,0]     x [q_hi,0,0,0]
+    bool used[16] = {};
+    p.ok = !(nrest & 1) && tnk_tc_match(ra, rb, nrest, used, p) && p.nsteps <= TNK_TC_MAX_STEPS;
+    return p;
+}
+
 struct TnkTcPlan {
     int np, nc;      // padded score length, 4-float chunks per field
     int ka, kb;      // chunks per state in the A (row) and B (column) tables
-    int nsteps;      // MMA K-steps; step ks multiplies A chunks {a0, a0+alb} with B chunks {b0, b0+blb}
-    uint16_t a0[TNK_TC_MAX_STEPS], alb[TNK_TC_MAX_STEPS], b0[TNK_TC_MAX_STEPS], blb[TNK_TC_MAX_STEPS];
+    TnkTcSteps s;
 };
 
 int tnk_tc_make_plan(int n, TnkTcPlan* p);

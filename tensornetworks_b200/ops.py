@@ -343,6 +343,16 @@ def ksd_quadratic_form(q, tables, group=None, algorithm="pairs", exchange=None):
     return _KsdQuadraticForm.apply(q, tables, group, algorithm, exchange)
 
 
+def tc_plan(n):
+    """K-step plan of the tensor-core variant for n latent bits (tnk_tc_plan)."""
+    lib = _lib.load()
+    np_, ka, kb, ns = ctypes.c_int(), ctypes.c_int(), ctypes.c_int(), ctypes.c_int()
+    steps = (ctypes.c_int32 * 128)()
+    _lib.check(lib.tnk_tc_plan(n, ctypes.byref(np_), ctypes.byref(ka), ctypes.byref(kb), ctypes.byref(ns), steps), "tnk_tc_plan")
+    return {"np": np_.value, "ka": ka.value, "kb": kb.value, "nsteps": ns.value,
+            "steps": [tuple(steps[4 * k:4 * k + 4]) for k in range(ns.value)]}
+
+
 def alu_peak(precision="fp32", iters=4096, device="cuda"):
     """Measured FMA-chain rate of the device in lane-ops/s (the pair kernel's roofline denominator)."""
     device = _require_cuda(device)

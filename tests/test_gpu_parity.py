@@ -11,7 +11,7 @@ from tensornetworks_b200.synthetic import random_binary_bn, random_q
 
 pytestmark = pytest.mark.gpu
 
-TOL = {"fp64": 1e-6, "fp32": 1e-4, "fp64_simple": 1e-6}
+TOL = {"fp64": 1e-6, "fp32": 1e-4, "fp64_simple": 1e-6, "tc32": 1e-4}
 RANDOM_CASES = [(n, n, 0) for n in range(2, 7)] + [(4, 104, 2)]
 TABLE_CASES = [(10, 0, 0), (10, 1, 2), (8, 7, 1)]
 
@@ -56,7 +56,7 @@ def test_known_answers_ab(ops, golden):
     assert np.isclose(u[1].item(), 2 * np.exp(-1.0) - 2.5, rtol=1e-12)
 
 
-@pytest.mark.parametrize("precision", ["fp64", "fp32", "fp64_simple"])
+@pytest.mark.parametrize("precision", ["fp64", "fp32", "fp64_simple", "tc32"])
 def test_sprinkler(ops, golden, precision):
     bn = get_sprinkler_network(False)
     tabs = _tables(ops, bn, {'W': 1}, ['C', 'S', 'R'], precision)
@@ -95,7 +95,7 @@ def test_enumeration_tables_bit_exact(ops, golden, n, seed, nh):
     assert np.array_equal(tabs.S.cpu().numpy(), golden[tag + "_S"])
 
 
-@pytest.mark.parametrize("precision", ["fp64", "fp32"])
+@pytest.mark.parametrize("precision", ["fp64", "fp32", "tc32"])
 @pytest.mark.parametrize("n,seed", [(7, 0), (9, 1), (10, 2), (11, 3), (12, 0)])
 def test_vs_dense_oracle(ops, n, seed, precision):
     bn, lat, obs, x = random_binary_bn(n, seed=seed)
@@ -110,7 +110,7 @@ def test_vs_dense_oracle(ops, n, seed, precision):
     _check(K, g, Kref, gref, TOL[precision])
 
 
-@pytest.mark.parametrize("precision", ["fp64", "fp32"])
+@pytest.mark.parametrize("precision", ["fp64", "fp32", "tc32"])
 @pytest.mark.parametrize("n,seed", [(13, 1), (14, 2), (16, 0)])
 def test_vs_modeproduct_oracle(ops, n, seed, precision):
     bn, lat, obs, x = random_binary_bn(n, seed=seed)
@@ -221,6 +221,62 @@ def test_modeproduct_matches_pair_kernel_n20(ops):
     torch.cuda.synchronize()
     assert abs(k_pair.item() - k_mp.item()) <= 1e-6 * abs(k_mp.item())
     assert (u_pair - u_mp).abs().max().item() <= 1e-6 * u_mp.abs().max().item()
+
+
+def test_tensor_core_row_ranges_and_splits(ops):
+    """tc32: disjoint row ranges (not aligned to the 128-row tile) reproduce the full u and K, and
+    the tensor-core result agrees with the fp64 pair kernel within the fp32-mode tolerance."""
+    n = 12
+    bn, lat, obs, x = random_binary_bn(n, seed=5)
+    tabs = _tables(ops, bn, x, lat, "tc32")
+    ref = _tables(ops, bn, x, lat, "fp64")
+    q = random_q(1 << n, seed=5).cuda()
+    u_full, k_full = tabs.ksd_rows(q)
+    u_ref, k_ref = ref.ksd_rows(q)
+    u = torch.zeros_like(u_full)
+    parts = []
+    cuts = [0, 100, 128, 1000, 2500, 4096]
+    for a, b in zip(cuts[:-1], cuts[1:]):
+        _, p = tabs.ksd_rows(q, a, b, u=u)
+        parts.append(p.clone())
+    torch.cuda.synchronize()
+    assert torch.equal(u, u_full)          # same tiles, same order of operations per row
+    assert np.isclose(sum(p.item() for p in parts), k_full.item(), rtol=1e-12)
+    assert abs(k_full.item() - k_ref.item()) <= 1e-4 * abs(k_ref.item())
+    assert (u_full - u_ref).abs().max().item() <= 1e-4 * u_ref.abs().max().item()
+
+
+def test_tensor_core_q_dtypes_and_posterior(ops):
+    """tc32 with fp32 q (the classical Born machine's dtype) and at q = posterior (KSD^2 ~ 0: the
+    gradient must still agree normwise with the fp64 kernel; K is compared on the scale of |q|^T|K_p||q|)."""
+    n = 10
+    bn, lat, obs, x = random_binary_bn(n, seed=3)
+    tabs = _tables(ops, bn, x, lat, "tc32")
+    ref = _tables(ops, bn, x, lat, "fp64")
+    q32 = random_q(1 << n, seed=3).to(torch.float32).cuda()
+    u1, k1 = tabs.ksd_rows(q32)
+    u0, k0 = ref.ksd_rows(q32)
+    assert abs(k1.item() - k0.item()) <= 1e-4 * abs(k0.item())
+    assert (u1 - u0).abs().max().item() <= 1e-4 * u0.abs().max().item()
+    post = ref.posterior()
+    u1, k1 = tabs.ksd_rows(post)
+    u0, k0 = ref.ksd_rows(post)
+    uni = torch.full_like(post, 1.0 / post.numel())
+    _, kscale = ref.ksd_rows(uni)
+    assert abs(k1.item() - k0.item()) <= 1e-4 * abs(kscale.item())
+
+
+def test_tensor_core_matches_modeproduct_n20(ops):
+    """Full size of BASELINE.json's metric through the tensor-core variant."""
+    n = 20
+    bn, lat, obs, x = random_binary_bn(n, seed=0)
+    tabs = _tables(ops, bn, x, lat, "tc32")
+    q = random_q(1 << n, seed=0).cuda()
+    u_mp, k_mp = tabs.ksd_modeproduct(q)
+    u_tc, k_tc = tabs.ksd_rows(q)
+    torch.cuda.synchronize()
+    assert abs(k_tc.item() - k_mp.item()) <= 1e-4 * abs(k_mp.item())
+    assert (u_tc - u_mp).abs().max().item() <= 1e-4 * u_mp.abs().max().item()
 
 
 def test_fused_peer_exchange_world2(ops):
