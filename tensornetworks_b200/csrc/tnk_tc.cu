@@ -1,41 +1,50 @@
 // K3-TC: tensor-core tile variant of the Stein pair kernel.
 //
-// The bracket of k_p(z,z') is bilinear in per-state feature vectors,
-//   q_j * [ s(i).s(j) + C(i) + C(j) + g*T1(i,j) + g*T2(i,j) ] = U(i) . V(j),
-// so a 128 x 128 tile of brackets is one GEMM tile: tcgen05.mma (kind::tf32) with the
-// accumulator in TMEM.  fp32-grade accuracy (the 1e-4 parity mode) comes from the usual
-// 3xTF32 split x = hi + lo (hi = top 10 mantissa bits, lo = x - hi exactly): every real
-// product x*y is issued as hi*hi + hi*lo + lo*hi; factors that are exact in tf32 (bits, 1)
-// need no split.  The a^popc(i^j) weight does NOT factorise into a low-rank form, so it is
-// applied per pair in the epilogue: each epilogue thread owns one row (TMEM lane), pulls 32
-// accumulator columns at a time with tcgen05.ld and folds them with a 16-entry register table
-// a^popc((i^c)&15) (one FFMA per pair) times one shared-memory LUT value per 16 columns.
+// With j the column state, the bracket of k_p splits into
+//   q_j * [ s(i).s(j) + g*T2(i,j) + C(j) ]           bilinear in per-state feature vectors -> tensor cores
+//   q_j * [ C(i) + g*T1(i,j) ],  T1 = sum_p rho_p(i) b_p(j)   depends on j only through its BITS -> ALU
+// A 128 x 128 tile of the first part is one GEMM tile: tcgen05.mma (kind::tf32), accumulator in
+// TMEM.  fp32-grade accuracy (the 1e-4 parity mode) comes from the 3xTF32 split x = hi + lo
+// (hi = top 10 mantissa bits, lo = x - hi exactly): a real product x*y is issued as
+// hi*hi + hi*lo + lo*hi; factors that are exact in tf32 (bits, 1) need no split.
+// The a^popc(i^j) weight does not factorise into a low-rank form, so it is applied per pair in
+// the epilogue: a thread owns one row (TMEM lane) and 64 of the tile's columns, pulls 32
+// accumulator columns at a time with tcgen05.ld and folds each group of 16 columns with a register
+// table W[c] = a^popc((i^c)&15) (packed FFMA2) times one LUT value per group.  The second part
+// needs per group only Q0 = sum_c W[c] q_c and Q1 = sum_c W[c] G_lo(i,c) q_c (two more packed
+// FMA chains on the q tile in shared memory), because C(i) + g*T1 is constant over a group up to
+// the 4 low column bits: contribution = w_group * (main + E(i,J,group)*Q0 + Q1).
 // Every ordered pair of the rows x columns handed to the kernel is evaluated (4^n in total).
 //
 // Operand tables (built per call by tc_pack_kernel, K-major "interleaved" no-swizzle UMMA
-// layout, one 128-state tile contiguous so that a whole tile is one cp.async.bulk):
+// layout, one 128-state tile contiguous so that a whole tile is one run of cp.async.bulk):
 //   tile t, chunk c, row r:  float4 at ((t*K + c)*128 + r)       (chunk = 4 consecutive k)
-// A (rows i):     s_hi | s_lo | bits | g_hi | g_lo | [1,1,C_hi,C_hi] | [C_lo,0,0,0]
-// B (columns j):  t_hi | t_lo | r_hi | r_lo | bq_hi | bq_lo | [(qC)_hi,(qC)_lo,q_hi,q_lo] | [q_hi,0,0,0]
-//   t = q_j s(j),  g = gamma*rho(i),  r = gamma*q_j*rho(j),  bq = b(j) q_j,  rho_p = (1-s_p)(1-2b_p)
-// One MMA K-step (K = 8 tf32) consumes two (A-chunk, B-chunk) products; the host planner
-// pairs the products so that both chunk offsets increase inside a step (they become the
-// descriptor's leading-dimension byte offsets) - shared chunks (s_hi, t_hi, bits, ...) are
-// stored once and referenced by several steps.
+// A (rows i):     s_hi | s_lo | bits | [1,1,0,0] (| 0)
+// B (columns j):  t_hi | t_lo | r_hi | r_lo | [(qC)_hi,(qC)_lo,0,0] (| 0)
+//   t = q_j s(j),  r = gamma*q_j*rho(j),  rho_p = (1-s_p)(1-2b_p)
+// One MMA K-step (K = 8 tf32) consumes two (A-chunk, B-chunk) products; the constexpr planner
+// (tnk_tc.cuh) pairs the products so that both chunk offsets increase inside a step (they become
+// the descriptor's leading-dimension byte offsets) - shared chunks (s_hi, t_hi, bits) are stored
+// once and referenced by several steps.  n = 20: 26 products = 13 K-steps per tile.
 //
-// Roles in a CTA of 192 threads (one CTA per SM, ~190 KB shared memory):
-//   warp 0   producer: A tile once, then B column tiles through a 2-stage ring (bulk copy + mbarrier)
-//   warp 1   allocates TMEM (2 x 128 columns), one lane issues the MMAs and commits
-//   warps 2-5 epilogue: TMEM -> registers, Hamming weights, row sums in fp32 per tile / fp64 across tiles
+// Roles in a CTA of 320 threads (one CTA per SM):
+//   warp 0    producer: A tile once, then B column tiles (+ their 128 q values) through a ring of
+//             kStages shared-memory stages (bulk copy + mbarrier)
+//   warp 1    allocates TMEM (2 x 128 columns), one lane issues the MMAs and commits
+//   warps 2-9 epilogue: TMEM -> registers, Hamming weights, row sums in fp32 per tile / fp64 across tiles
 #include "tnk_common.cuh"
 #include "tnk_tc.cuh"
 
 namespace {
 
-constexpr int kTcThreads = 192;
+constexpr int kTcThreads = 320;
+constexpr int kMaxStages = 4;                 // B ring depth is 4 (NC <= 5) or 3 (NC = 6, shared-memory limit)
+constexpr int kQSlots = 8;                    // q-table ring depth >= kStages + 2 + 1 (see the producer comment)
+constexpr int kQTab = 5 * 8 * 16;             // floats per column tile: [Q0,Qb0..Qb3][8 groups][16 row variants]
 constexpr int kTile = TNK_TC_TILE;            // rows per CTA = columns per stage = 128
 constexpr int kChunkBytes = kTile * 16;       // one chunk of one tile
-constexpr int kTmemCols = 2 * kTile;          // two accumulator stages
+constexpr int kTmemCols = 512;                // 2 accumulator stages (2 x 128 columns) + the A operand (8 columns per K-step)
+constexpr int kTmemA = 2 * kTile;             // first TMEM column of the A operand
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
@@ -67,16 +76,27 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
         if (clock64() - t0 > 8000000000LL) __trap();
     }
 }
+// one lane of a converged warp (elect.sync): lets ptxas issue UTCHMMA/UTCBAR without a per-lane loop
+__device__ __forceinline__ bool elect_one() {
+    uint32_t pred;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "elect.sync _|p, 0xffffffff;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(pred));
+    return pred != 0;
+}
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 
-// D[tmem] (+)= A[smem] . B[smem]^T, one K-step of 8 tf32, issued by one thread for the CTA
-__device__ __forceinline__ void umma_tf32(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc, uint32_t accumulate) {
+// D[tmem] (+)= A[tmem] . B[smem]^T, one K-step of 8 tf32, issued by one thread for the CTA;
+// A operand in TMEM: lane = row, one 32-bit column per tf32 element
+__device__ __forceinline__ void umma_tf32_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t desc_b, uint32_t idesc, uint32_t accumulate) {
     asm volatile(
         "{\n\t.reg .pred p;\n\t"
         "setp.ne.b32 p, %4, 0;\n\t"
-        "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
-        ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate) : "memory");
+        "tcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], %2, %3, p;\n\t}"
+        ::"r"(tmem_d), "r"(tmem_a), "l"(desc_b), "r"(idesc), "r"(accumulate) : "memory");
 }
 __device__ __forceinline__ void umma_commit(uint64_t* bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
@@ -99,6 +119,7 @@ struct TcParams {
     int64_t n_tiles;     // column tiles in total (2^n / 128)
     int col_splits;      // gridDim.y
     int64_t part_stride; // rows covered by the launch
+    float gamma;         // a - 1/a
     float wl[32];        // w[h] = exp(-h/(n l))
 };
 
@@ -112,7 +133,7 @@ tc_pack_kernel(int n, int np, int64_t first_state, int64_t n_tiles, float gamma,
                const float* __restrict__ ST, const float* __restrict__ Cst, const float* __restrict__ qT,
                float4* __restrict__ out) {
     const int nc = np >> 2;
-    const int K = IS_B ? 6 * nc + 2 : 5 * nc + 2;
+    const int K = IS_B ? tnk_tc_kb(nc) : tnk_tc_ka(nc);
     const int64_t idx = (int64_t)blockIdx.x * 256 + threadIdx.x;
     const int row = (int)(idx & (kTile - 1));
     const int64_t t = idx >> 7;
@@ -120,7 +141,7 @@ tc_pack_kernel(int n, int np, int64_t first_state, int64_t n_tiles, float gamma,
     const int64_t tile = t / K;
     if (tile >= n_tiles) return;
     const int64_t z = first_state + tile * kTile + row;
-    const int nfield = IS_B ? 6 : 5;
+    const int nfield = IS_B ? 4 : 3;
     float v[4] = {0.f, 0.f, 0.f, 0.f};
     if (chunk < nfield * nc) {
         const int f = chunk / nc, c = chunk - f * nc;
@@ -132,66 +153,96 @@ tc_pack_kernel(int n, int np, int64_t first_state, int64_t n_tiles, float gamma,
             const int p = 4 * c + e;
             const bool valid = p < n;
             const bool bit = valid && ((z >> p) & 1);
-            const float rho = valid ? (bit ? -(1.f - s[e]) : (1.f - s[e])) : 0.f;
             float x;
             if (!IS_B) {
-                const float g = gamma * rho;
-                x = f == 0 ? tf_hi(s[e]) : f == 1 ? tf_lo(s[e]) : f == 2 ? (bit ? 1.f : 0.f) : f == 3 ? tf_hi(g) : tf_lo(g);
+                x = f == 0 ? tf_hi(s[e]) : f == 1 ? tf_lo(s[e]) : (bit ? 1.f : 0.f);
             } else {
+                const float rho = valid ? (bit ? -(1.f - s[e]) : (1.f - s[e])) : 0.f;
                 const float ts = q * s[e];
                 const float r = (gamma * q) * rho;
-                x = f == 0 ? tf_hi(ts) : f == 1 ? tf_lo(ts) : f == 2 ? tf_hi(r) : f == 3 ? tf_lo(r)
-                  : f == 4 ? (bit ? tf_hi(q) : 0.f) : (bit ? tf_lo(q) : 0.f);
+                x = f == 0 ? tf_hi(ts) : f == 1 ? tf_lo(ts) : f == 2 ? tf_hi(r) : tf_lo(r);
             }
             v[e] = x;
         }
-    } else {
-        const float C = Cst[z];
-        const bool first = chunk == nfield * nc;
-        if (!IS_B) {
-            if (first) { v[0] = 1.f; v[1] = 1.f; v[2] = tf_hi(C); v[3] = tf_hi(C); }
-            else { v[0] = tf_lo(C); }
-        } else {
-            const float q = qT[z];
-            const float qc = q * C;
-            if (first) { v[0] = tf_hi(qc); v[1] = tf_lo(qc); v[2] = tf_hi(q); v[3] = tf_lo(q); }
-            else { v[0] = tf_hi(q); }
-        }
-    }
+    } else if (chunk == nfield * nc) {
+        if (!IS_B) { v[0] = 1.f; v[1] = 1.f; }
+        else { const float qc = qT[z] * Cst[z]; v[0] = tf_hi(qc); v[1] = tf_lo(qc); }
+    }   // else: the zero chunk that pads an odd number of chunk products
     out[idx] = make_float4(v[0], v[1], v[2], v[3]);
+}
+
+// ---- per-column-tile q tables of the ALU part.  For group g (16 columns) and row variant v = i & 15:
+//   Q0[g][v]   = sum_c a^popc(v^c) q_c          Qb_p[g][v] = sum_c a^popc(v^c) b_p(c) q_c   (p = 0..3)
+// so that a row needs per group only Q0 and Q1 = sum_{p<4} g_p(i) Qb_p.  They depend on the column
+// tile alone, hence are built once per evaluation: grid = column tiles, 128 threads = (g, v).
+__global__ void __launch_bounds__(128)
+tc_qtab_kernel(const float* __restrict__ qT, float w1, float* __restrict__ out) {
+    const int g = threadIdx.x >> 4, v = threadIdx.x & 15;
+    const float* q = qT + (size_t)blockIdx.x * kTile + g * 16;
+    float wp[5];
+    wp[0] = 1.f;
+#pragma unroll
+    for (int h = 1; h < 5; ++h) wp[h] = wp[h - 1] * w1;     // a^h, h <= 4
+    float acc[5] = {0.f, 0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+    for (int c = 0; c < 16; ++c) {
+        const float wq = wp[__popc((unsigned)(v ^ c))] * q[c];
+        acc[0] += wq;
+#pragma unroll
+        for (int p = 0; p < 4; ++p) acc[1 + p] += ((c >> p) & 1) ? wq : 0.f;
+    }
+    float* o = out + (size_t)blockIdx.x * kQTab;
+#pragma unroll
+    for (int k = 0; k < 5; ++k) o[(k * 8 + g) * 16 + v] = acc[k];
 }
 
 // ---- the tile kernel, NC = 4-float chunks per field (np / 4)
 template <int NC>
+struct TcSmem {
+    static constexpr int stages = NC <= 5 ? kMaxStages : 3;
+    static constexpr uint32_t b_bytes = (uint32_t)tnk_tc_kb(NC) * kChunkBytes;
+    static constexpr uint32_t off_b = 0;
+    static constexpr uint32_t off_q = off_b + stages * b_bytes;           // [kQSlots][kQTab] float
+    static constexpr uint32_t off_wl = off_q + kQSlots * kQTab * 4;       // [32] float
+    static constexpr uint32_t off_red = off_wl + 32 * 4;                  // [128] double
+    static constexpr uint32_t off_bar = off_red + kTile * 8;              // mbarriers
+    static constexpr int n_bars = 1 + 2 * kMaxStages + 4 + kQSlots;
+    static constexpr uint32_t off_tmem = off_bar + n_bars * 8;
+    static constexpr uint32_t total = off_tmem + 16;
+};
+
+template <int NC>
 __global__ void __launch_bounds__(kTcThreads, 1)
-tc_rows_kernel(const __grid_constant__ TcParams prm, const float* __restrict__ A_tab, const float* __restrict__ B_tab,
+tc_rows_kernel(const __grid_constant__ TcParams prm, const float* __restrict__ B_tab,
+               const float* __restrict__ ST, const float* __restrict__ Cst, const float* __restrict__ Qtab,
                double* __restrict__ part) {
     extern __shared__ __align__(1024) unsigned char smem[];
+    using SM = TcSmem<NC>;
     constexpr TnkTcSteps P = tnk_tc_steps(NC);
     static_assert(P.ok, "no K-step plan for this chunk count");
-    constexpr uint32_t a_bytes = (uint32_t)(5 * NC + 2) * kChunkBytes;
-    constexpr uint32_t b_bytes = (uint32_t)(6 * NC + 2) * kChunkBytes;
-    unsigned char* sA = smem;
-    unsigned char* sB = smem + a_bytes;
-    float* sWl = reinterpret_cast<float*>(smem + a_bytes + 2 * b_bytes);
-    uint64_t* bars = reinterpret_cast<uint64_t*>(sWl + 32);
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 9);
-    uint64_t* bar_afull = bars;
-    uint64_t* bar_full = bars + 1;    // [2] B stage landed
-    uint64_t* bar_empty = bars + 3;   // [2] B stage consumed by the MMAs
-    uint64_t* bar_tfull = bars + 5;   // [2] accumulator stage complete
-    uint64_t* bar_tempty = bars + 7;  // [2] accumulator stage drained by the 4 epilogue warps
+    constexpr int NP = 4 * NC;
+    constexpr int kStages = SM::stages;
+    constexpr uint32_t b_bytes = SM::b_bytes;
+    unsigned char* sB = smem + SM::off_b;
+    float* sQ = reinterpret_cast<float*>(smem + SM::off_q);
+    float* sWl = reinterpret_cast<float*>(smem + SM::off_wl);
+    double* sRed = reinterpret_cast<double*>(smem + SM::off_red);
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + SM::off_bar);
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + SM::off_tmem);
+    uint64_t* bar_aready = bars;                        // A operand stored to TMEM by the 8 epilogue warps
+    uint64_t* bar_full = bars + 1;                      // [kStages] B stage landed
+    uint64_t* bar_empty = bar_full + kStages;           // [kStages] B stage consumed by the MMAs
+    uint64_t* bar_tfull = bar_empty + kStages;          // [2] accumulator stage complete
+    uint64_t* bar_tempty = bar_tfull + 2;               // [2] accumulator stage drained by the 8 epilogue warps
+    uint64_t* bar_qfull = bar_tempty + 2;               // [kQSlots] q tile landed
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     if (threadIdx.x < 32) sWl[threadIdx.x] = prm.wl[threadIdx.x];
     if (threadIdx.x == 0) {
-        mbar_init(bar_afull, 1);
-        for (int s = 0; s < 2; ++s) {
-            mbar_init(bar_full + s, 1);
-            mbar_init(bar_empty + s, 1);
-            mbar_init(bar_tfull + s, 1);
-            mbar_init(bar_tempty + s, 4);
-        }
+        mbar_init(bar_aready, 8);
+        for (int s = 0; s < kStages; ++s) { mbar_init(bar_full + s, 1); mbar_init(bar_empty + s, 1); }
+        for (int s = 0; s < 2; ++s) { mbar_init(bar_tfull + s, 1); mbar_init(bar_tempty + s, 8); }
+        for (int s = 0; s < kQSlots; ++s) mbar_init(bar_qfull + s, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 1) {
@@ -203,22 +254,24 @@ tc_rows_kernel(const __grid_constant__ TcParams prm, const float* __restrict__ A
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
 
-    const int64_t n_local = (prm.n_tiles - blockIdx.y + prm.col_splits - 1) / prm.col_splits;
+    // Column split y owns a CONTIGUOUS range of column tiles and the grid is row-tile-major, so all
+    // CTAs resident at one time stream the same slice of the B table (sized by the host to fit L2).
+    const int64_t n_local = prm.n_tiles / prm.col_splits;
+    const int64_t j_first = (int64_t)blockIdx.y * n_local;
 
     if (warp == 0) {
         if (lane == 0) {
-            // ===== producer
-            const unsigned char* srcA = reinterpret_cast<const unsigned char*>(A_tab) + (size_t)blockIdx.x * a_bytes;
-            mbar_expect_tx(bar_afull, a_bytes);
-            for (uint32_t off = 0; off < a_bytes; off += 8 * kChunkBytes) {
-                const uint32_t len = min(a_bytes - off, (uint32_t)(8 * kChunkBytes));
-                bulk_g2s(sA + off, srcA + off, len, bar_afull);
-            }
+            // ===== producer (B column tiles and their q tables).  It runs at most kStages tiles ahead of the MMAs, which run at most 2 tiles
+            // (accumulator stages) ahead of the epilogue: while epilogue(it) still reads its q tile the
+            // producer can be loading tile it + kStages + 1 at most, so kQSlots = 8 slots never alias.
+            int s = 0;
+            uint32_t ph = 0;
             for (int64_t it = 0; it < n_local; ++it) {
-                const int s = (int)(it & 1);
-                const uint32_t ph = (uint32_t)((it >> 1) & 1);
-                const int64_t J = (int64_t)blockIdx.y + it * prm.col_splits;
+                const int64_t J = j_first + it;
                 mbar_wait(bar_empty + s, ph ^ 1u);
+                const int qs = (int)(it & (kQSlots - 1));
+                mbar_expect_tx(bar_qfull + qs, kQTab * 4);
+                bulk_g2s(sQ + qs * kQTab, Qtab + J * kQTab, kQTab * 4, bar_qfull + qs);
                 const unsigned char* srcB = reinterpret_cast<const unsigned char*>(B_tab) + (size_t)J * b_bytes;
                 unsigned char* dstB = sB + (size_t)s * b_bytes;
                 mbar_expect_tx(bar_full + s, b_bytes);
@@ -226,85 +279,185 @@ tc_rows_kernel(const __grid_constant__ TcParams prm, const float* __restrict__ A
                     const uint32_t len = min(b_bytes - off, (uint32_t)(8 * kChunkBytes));
                     bulk_g2s(dstB + off, srcB + off, len, bar_full + s);
                 }
+                if (++s == kStages) { s = 0; ph ^= 1u; }
             }
         }
     } else if (warp == 1) {
-        if (lane == 0) {
-            // ===== MMA issuer.  Every descriptor is the tile's base descriptor plus a compile-time
-            // offset (address field and LBO field in 16-byte units), so a K-step costs a few uniform
-            // integer instructions around the UTCHMMA.
-            const uint64_t a_desc = smem_desc(smem_u32(sA), 0);
-            mbar_wait(bar_afull, 0);
+        {
+            // ===== MMA issuer.  A comes from TMEM (8 columns per K-step, written once by the epilogue
+            // warps), B from shared memory: its descriptor is the stage's base descriptor plus a
+            // compile-time offset (address and LBO fields in 16-byte units), so a K-step costs a few
+            // uniform integer instructions around the UTCHMMA and reads only 4 KB of shared memory.
+            mbar_wait(bar_aready, 0);
+            tc_fence_after();
+            int s = 0;
+            uint32_t ph = 0;
             for (int64_t it = 0; it < n_local; ++it) {
-                const int s = (int)(it & 1);
-                const uint32_t ph = (uint32_t)((it >> 1) & 1);
-                mbar_wait(bar_tempty + s, ph ^ 1u);
+                const int ts = (int)(it & 1);
+                const uint32_t tph = (uint32_t)((it >> 1) & 1);
+                mbar_wait(bar_tempty + ts, tph ^ 1u);
                 mbar_wait(bar_full + s, ph);
                 tc_fence_after();
                 const uint64_t b_desc = smem_desc(smem_u32(sB) + (uint32_t)s * b_bytes, 0);
-                const uint32_t d_addr = tmem_base + (uint32_t)(s * kTile);
+                const uint32_t d_addr = tmem_base + (uint32_t)(ts * kTile);
+                if (elect_one()) {
 #pragma unroll
                 for (int ks = 0; ks < P.nsteps; ++ks) {
                     constexpr uint32_t cu = kChunkBytes >> 4;   // one chunk in descriptor address units
-                    const uint64_t da = a_desc + (uint64_t)((uint32_t)P.a0[ks] * cu + (((uint32_t)P.alb[ks] * cu) << 16));
                     const uint64_t db = b_desc + (uint64_t)((uint32_t)P.b0[ks] * cu + (((uint32_t)P.blb[ks] * cu) << 16));
-                    umma_tf32(d_addr, da, db, kIdesc, ks > 0 ? 1u : 0u);
+                    umma_tf32_ts(d_addr, tmem_base + (uint32_t)(kTmemA + 8 * ks), db, kIdesc, ks > 0 ? 1u : 0u);
                 }
-                umma_commit(bar_empty + s);   // B stage free once these MMAs have read it
-                umma_commit(bar_tfull + s);   // accumulator stage ready
+                umma_commit(bar_empty + s);    // B stage free once these MMAs have read it
+                umma_commit(bar_tfull + ts);   // accumulator stage ready
+                }
+                __syncwarp();
+                if (++s == kStages) { s = 0; ph ^= 1u; }
             }
         }
     } else {
-        // ===== epilogue: thread <-> TMEM lane <-> row
+        // ===== epilogue: thread <-> TMEM lane <-> row; warps w and w+4 share a lane quarter and split the columns
         const int lq = (warp & 3) * 32;
+        const int half = (warp - 2) >> 2;                  // columns [64*half, 64*half+64) of every tile
         const int L = lq + lane;
         const int64_t i = prm.row0 + (int64_t)blockIdx.x * kTile + L;
-        float W[16];
+        const int n = prm.n;
+        // row-side constants of the ALU part: g_p = gamma*rho_p(i)
+        float gp[NP];
+        {
+            float sv[NP];
 #pragma unroll
-        for (int cc = 0; cc < 16; ++cc) W[cc] = sWl[__popc(((uint32_t)i ^ (uint32_t)cc) & 15u)];
+            for (int c = 0; c < NC; ++c) {
+                const float4 s4 = *reinterpret_cast<const float4*>(ST + i * NP + 4 * c);
+                sv[4 * c] = s4.x; sv[4 * c + 1] = s4.y; sv[4 * c + 2] = s4.z; sv[4 * c + 3] = s4.w;
+            }
+            // A operand of this row -> TMEM: K-step ks occupies columns kTmemA + 8*ks .. +7 (its two
+            // chunks side by side); the two warps of a lane quarter write alternate steps.
+            // Chunk c of the row table: s_hi | s_lo | bits | [1,1,0,0] | 0  (see the file header).
+            auto a_val = [&](int chunk, int e) -> float {
+                const int f = chunk / NC, p = 4 * (chunk - f * NC) + e;
+                if (chunk >= 3 * NC) return (chunk == 3 * NC && e < 2) ? 1.f : 0.f;
+                const float x = sv[p < NP ? p : 0];
+                return f == 0 ? tf_hi(x) : f == 1 ? tf_lo(x) : ((p < n && ((i >> p) & 1)) ? 1.f : 0.f);
+            };
+#pragma unroll
+            for (int ks = 0; ks < P.nsteps; ++ks) {
+                if ((ks & 1) == half) {
+                    uint32_t av[8];
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) {
+                        av[e] = __float_as_uint(a_val(P.a0[ks], e));
+                        av[4 + e] = __float_as_uint(a_val(P.a0[ks] + P.alb[ks], e));
+                    }
+                    asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};"
+                                 ::"r"(tmem_base + ((uint32_t)lq << 16) + (uint32_t)(kTmemA + 8 * ks)),
+                                   "r"(av[0]), "r"(av[1]), "r"(av[2]), "r"(av[3]), "r"(av[4]), "r"(av[5]), "r"(av[6]), "r"(av[7])
+                                 : "memory");
+                }
+            }
+            asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(bar_aready);
+#pragma unroll
+            for (int p = 0; p < NP; ++p) {
+                const float v = prm.gamma * (1.f - sv[p]);
+                gp[p] = (p < n) ? (((i >> p) & 1) ? -v : v) : 0.f;
+            }
+        }
+        const float Ci = Cst[i];
+        float2 W2[8];                                      // W[c] = a^popc((i^c)&15), packed for FFMA2
+#pragma unroll
+        for (int cc = 0; cc < 16; ++cc) {
+            const float w = sWl[__popc(((uint32_t)i ^ (uint32_t)cc) & 15u)];
+            if (cc & 1) W2[cc >> 1].y = w; else W2[cc >> 1].x = w;
+        }
+        float Gmid[4];                                     // column bits 4..6 of this warp's 4 groups
+#pragma unroll
+        for (int gl = 0; gl < 4; ++gl) {
+            const int g = half * 4 + gl;
+            float v = 0.f;
+#pragma unroll
+            for (int b = 0; b < 3; ++b) v += ((g >> b) & 1) ? gp[4 + b] : 0.f;
+            Gmid[gl] = v;
+        }
         const uint32_t imid = ((uint32_t)i >> 4) & 7u;
         const uint32_t ihi = (uint32_t)(i >> 7);
-        double udbl = 0.0;
+        const int tab_off = (half * 4) * 16 + (int)(i & 15);   // [k][g][v] -> k*128 + g*16 + v
+        // Row sum across tiles in compensated fp32 (Fast2Sum): the FP64 pipe stalls for hundreds of
+        // cycles behind the tensor pipe (ncu: math-pipe throttle on a per-tile DADD), so fp64 is
+        // touched only once, after the sweep.
+        float uhi = 0.f, ulo = 0.f;
         for (int64_t it = 0; it < n_local; ++it) {
-            const int s = (int)(it & 1);
-            const uint32_t ph = (uint32_t)((it >> 1) & 1);
-            const int64_t J = (int64_t)blockIdx.y + it * prm.col_splits;
+            const int ts = (int)(it & 1);
+            const uint32_t tph = (uint32_t)((it >> 1) & 1);
+            const int qs = (int)(it & (kQSlots - 1));
+            const uint32_t qph = (uint32_t)((it / kQSlots) & 1);
+            const int64_t J = j_first + it;
             const int xhi = __popc(ihi ^ (uint32_t)J);
-            mbar_wait(bar_tfull + s, ph);
-            tc_fence_after();
-            const uint32_t taddr = tmem_base + ((uint32_t)lq << 16) + (uint32_t)(s * kTile);
-            float utile = 0.f;
+            float Ehi = Ci;                                // C(i) + sum_{p>=7} g_p b_p(J)
 #pragma unroll
-            for (int g2 = 0; g2 < kTile / 32; ++g2) {
-                uint32_t v[32];
+            for (int p = 7; p < NP; ++p) Ehi += ((J >> (p - 7)) & 1) ? gp[p] : 0.f;
+            mbar_wait(bar_qfull + qs, qph);
+            mbar_wait(bar_tfull + ts, tph);
+            tc_fence_after();
+            const uint32_t taddr = tmem_base + ((uint32_t)lq << 16) + (uint32_t)(ts * kTile + half * 64);
+            uint32_t v[64];
+#pragma unroll
+            for (int g2 = 0; g2 < 2; ++g2) {
                 asm volatile(
                     "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
                     "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
                     "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
-                    : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
-                      "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]),
-                      "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]),
-                      "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+                    : "=r"(v[g2 * 32 + 0]), "=r"(v[g2 * 32 + 1]), "=r"(v[g2 * 32 + 2]), "=r"(v[g2 * 32 + 3]),
+                      "=r"(v[g2 * 32 + 4]), "=r"(v[g2 * 32 + 5]), "=r"(v[g2 * 32 + 6]), "=r"(v[g2 * 32 + 7]),
+                      "=r"(v[g2 * 32 + 8]), "=r"(v[g2 * 32 + 9]), "=r"(v[g2 * 32 + 10]), "=r"(v[g2 * 32 + 11]),
+                      "=r"(v[g2 * 32 + 12]), "=r"(v[g2 * 32 + 13]), "=r"(v[g2 * 32 + 14]), "=r"(v[g2 * 32 + 15]),
+                      "=r"(v[g2 * 32 + 16]), "=r"(v[g2 * 32 + 17]), "=r"(v[g2 * 32 + 18]), "=r"(v[g2 * 32 + 19]),
+                      "=r"(v[g2 * 32 + 20]), "=r"(v[g2 * 32 + 21]), "=r"(v[g2 * 32 + 22]), "=r"(v[g2 * 32 + 23]),
+                      "=r"(v[g2 * 32 + 24]), "=r"(v[g2 * 32 + 25]), "=r"(v[g2 * 32 + 26]), "=r"(v[g2 * 32 + 27]),
+                      "=r"(v[g2 * 32 + 28]), "=r"(v[g2 * 32 + 29]), "=r"(v[g2 * 32 + 30]), "=r"(v[g2 * 32 + 31])
                     : "r"(taddr + (uint32_t)(g2 * 32)));
-                asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-#pragma unroll
-                for (int half = 0; half < 2; ++half) {
-                    float acc0 = 0.f, acc1 = 0.f;
-#pragma unroll
-                    for (int cc = 0; cc < 16; cc += 2) {
-                        acc0 = fmaf(W[cc], __uint_as_float(v[half * 16 + cc]), acc0);
-                        acc1 = fmaf(W[cc + 1], __uint_as_float(v[half * 16 + cc + 1]), acc1);
-                    }
-                    const int g = g2 * 2 + half;
-                    utile = fmaf(sWl[xhi + __popc(imid ^ (uint32_t)g)], acc0 + acc1, utile);
-                }
             }
+            // ALU part of the four groups (table lookups) overlaps the TMEM load latency
+            const float* tab = sQ + qs * kQTab + tab_off;
+            float alu[4], wg[4];
+#pragma unroll
+            for (int gl = 0; gl < 4; ++gl) {
+                const float Q0 = tab[gl * 16];
+                float Q1 = gp[0] * tab[128 + gl * 16];
+                Q1 = fmaf(gp[1], tab[256 + gl * 16], Q1);
+                Q1 = fmaf(gp[2], tab[384 + gl * 16], Q1);
+                Q1 = fmaf(gp[3], tab[512 + gl * 16], Q1);
+                alu[gl] = fmaf(Ehi + Gmid[gl], Q0, Q1);
+                wg[gl] = sWl[xhi + __popc(imid ^ (uint32_t)(half * 4 + gl))];
+            }
+            asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
             tc_fence_before();
             __syncwarp();
-            if (lane == 0) mbar_arrive(bar_tempty + s);
-            udbl += (double)utile;
+            if (lane == 0) mbar_arrive(bar_tempty + ts);   // all 64 accumulator values are in registers: stage is free
+            float utile = 0.f;
+#pragma unroll
+            for (int gl = 0; gl < 4; ++gl) {
+                float2 m0 = make_float2(alu[gl], 0.f), m1 = make_float2(0.f, 0.f);
+#pragma unroll
+                for (int k = 0; k < 8; k += 2) {
+                    m0 = __ffma2_rn(W2[k], make_float2(__uint_as_float(v[gl * 16 + 2 * k]), __uint_as_float(v[gl * 16 + 2 * k + 1])), m0);
+                    m1 = __ffma2_rn(W2[k + 1], make_float2(__uint_as_float(v[gl * 16 + 2 * k + 2]), __uint_as_float(v[gl * 16 + 2 * k + 3])), m1);
+                }
+                utile = fmaf(wg[gl], (m0.x + m0.y) + (m1.x + m1.y), utile);
+            }
+            {
+                const float sum = uhi + utile;              // TwoSum (no magnitude assumption)
+                const float bb = sum - uhi;
+                ulo += (uhi - (sum - bb)) + (utile - bb);
+                uhi = sum;
+            }
         }
-        part[(size_t)blockIdx.y * prm.part_stride + (size_t)(i - prm.row0)] = udbl;
+        const double udbl = (double)uhi + (double)ulo;
+        if (half == 1) sRed[L] = udbl;
+        asm volatile("bar.sync 1, 256;" ::: "memory");     // the 8 epilogue warps only
+        if (half == 0)
+            part[(size_t)blockIdx.y * prm.part_stride + (size_t)(i - prm.row0)] = udbl + sRed[L];
     }
 
     tc_fence_before();
@@ -322,7 +475,7 @@ int tnk_tc_make_plan(int n, TnkTcPlan* p) {
     if (n < TNK_TC_MIN_LATENT || n > TNK_TC_MAX_LATENT) return 1;
     const int np = ((n + 3) / 4) * 4;
     const int nc = np / 4;
-    p->np = np; p->nc = nc; p->ka = 5 * nc + 2; p->kb = 6 * nc + 2;
+    p->np = np; p->nc = nc; p->ka = tnk_tc_ka(nc); p->kb = tnk_tc_kb(nc);
     p->s = tnk_tc_steps(nc);
     return p->s.ok ? 0 : 1;
 }
@@ -344,16 +497,19 @@ extern "C" int tnk_tc_plan(int n_latent, int* np, int* ka, int* kb, int* nsteps,
 }
 
 size_t tnk_tc_table_bytes(const TnkTcPlan& p, int64_t states, bool is_b) {
-    return (size_t)states * (size_t)(is_b ? p.kb : p.ka) * 16;
+    return is_b ? (size_t)states * (size_t)p.kb * 16 : 0;   // the row operand is built in TMEM by the kernel
 }
+
+size_t tnk_tc_qtab_bytes(int64_t states) { return (size_t)(states / kTile) * kQTab * sizeof(float); }
 
 namespace {
 template <int NC>
-int launch_tiles(const TcParams& prm, dim3 grid, const float* A_tab, const float* B_tab, double* part, cudaStream_t st) {
-    const size_t smem = (size_t)((5 * NC + 2) + 2 * (6 * NC + 2)) * kChunkBytes + 32 * sizeof(float) + 9 * sizeof(uint64_t) + 16;
+int launch_tiles(const TcParams& prm, dim3 grid, const float* B_tab, const float* ST, const float* Cst,
+                 const float* Qtab, double* part, cudaStream_t st) {
+    const size_t smem = TcSmem<NC>::total;
     auto kern = tc_rows_kernel<NC>;
     TNK_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    kern<<<grid, kTcThreads, smem, st>>>(prm, A_tab, B_tab, part);
+    kern<<<grid, kTcThreads, smem, st>>>(prm, B_tab, ST, Cst, Qtab, part);
     TNK_CUDA_OK(cudaGetLastError());
     return 0;
 }
@@ -361,37 +517,34 @@ int launch_tiles(const TcParams& prm, dim3 grid, const float* A_tab, const float
 
 // Builds both operand tables and launches the tile kernel.  qT: packed fp32 q [>= 2^n].
 int tnk_tc_launch(int n, double a, double gamma, const double* wl, const float* ST, const float* Cst, const float* qT,
-                  int64_t row0, int64_t launch_rows, int splits, float* A_tab, float* B_tab, double* part,
+                  int64_t row0, int64_t launch_rows, int splits, float* A_tab, float* B_tab, float* Qtab, double* part,
                   cudaEvent_t ev_start, cudaEvent_t ev_stop, int* launches, cudaStream_t st) {
-    (void)a;
+    (void)a; (void)A_tab;
     TnkTcPlan p;
     TNK_REQUIRE(tnk_tc_make_plan(n, &p) == 0, "tnk_ksd_rows: no tensor-core plan for n=%d", n);
     const int64_t N = (int64_t)1 << n;
     const int64_t row_tiles = launch_rows / kTile, col_tiles = N / kTile;
-    {
-        const int64_t items = row_tiles * p.ka * kTile;
-        tc_pack_kernel<false><<<(unsigned)((items + 255) / 256), 256, 0, st>>>(n, p.np, row0, row_tiles, (float)gamma, ST, Cst, qT,
-                                                                              reinterpret_cast<float4*>(A_tab));
-        TNK_CUDA_OK(cudaGetLastError());
-    }
     {
         const int64_t items = col_tiles * p.kb * kTile;
         tc_pack_kernel<true><<<(unsigned)((items + 255) / 256), 256, 0, st>>>(n, p.np, 0, col_tiles, (float)gamma, ST, Cst, qT,
                                                                              reinterpret_cast<float4*>(B_tab));
         TNK_CUDA_OK(cudaGetLastError());
     }
+    tc_qtab_kernel<<<(unsigned)col_tiles, 128, 0, st>>>(qT, (float)wl[1], Qtab);
+    TNK_CUDA_OK(cudaGetLastError());
     TcParams prm;
     prm.n = n; prm.row0 = row0; prm.n_tiles = col_tiles; prm.col_splits = splits; prm.part_stride = launch_rows;
+    prm.gamma = (float)gamma;
     for (int h = 0; h < 32; ++h) prm.wl[h] = (float)wl[h];
     if (ev_start) TNK_CUDA_OK(cudaEventRecord(ev_start, st));
     dim3 grid((unsigned)row_tiles, (unsigned)splits, 1);
     int rc = 2;
     switch (p.nc) {
-        case 2: rc = launch_tiles<2>(prm, grid, A_tab, B_tab, part, st); break;
-        case 3: rc = launch_tiles<3>(prm, grid, A_tab, B_tab, part, st); break;
-        case 4: rc = launch_tiles<4>(prm, grid, A_tab, B_tab, part, st); break;
-        case 5: rc = launch_tiles<5>(prm, grid, A_tab, B_tab, part, st); break;
-        case 6: rc = launch_tiles<6>(prm, grid, A_tab, B_tab, part, st); break;
+        case 2: rc = launch_tiles<2>(prm, grid, B_tab, ST, Cst, Qtab, part, st); break;
+        case 3: rc = launch_tiles<3>(prm, grid, B_tab, ST, Cst, Qtab, part, st); break;
+        case 4: rc = launch_tiles<4>(prm, grid, B_tab, ST, Cst, Qtab, part, st); break;
+        case 5: rc = launch_tiles<5>(prm, grid, B_tab, ST, Cst, Qtab, part, st); break;
+        case 6: rc = launch_tiles<6>(prm, grid, B_tab, ST, Cst, Qtab, part, st); break;
         default: tnk_set_error("tnk_ksd_rows: no tensor-core kernel instance for %d chunks", p.nc); break;
     }
     if (rc) return rc;

@@ -42,14 +42,20 @@ __host__ __device__ constexpr bool tnk_tc_match(const int* ia, const int* ib, in
     return false;
 }
 
+// Table widths in chunks.  A (rows): s_hi | s_lo | bits | [1,1,0,0] (| zero);
+// B (columns): t_hi | t_lo | r_hi | r_lo | [(qC)_hi,(qC)_lo,0,0] (| zero).  The zero chunks exist only
+// when the number of chunk products 5*nc+1 is odd (nc even) and pad the last K-step.
+__host__ __device__ constexpr int tnk_tc_ka(int nc) { return 3 * nc + 1 + (((5 * nc + 1) & 1) ? 1 : 0); }
+__host__ __device__ constexpr int tnk_tc_kb(int nc) { return 4 * nc + 1 + (((5 * nc + 1) & 1) ? 1 : 0); }
+
 __host__ __device__ constexpr TnkTcSteps tnk_tc_steps(int nc) {
     TnkTcSteps p{};
-    // field pairs: A {s_hi s_hi s_lo bits bits g_hi g_hi g_lo} x B {t_hi t_lo t_hi r_hi r_lo bq_hi bq_lo bq_hi}
-    const int FA[8] = {0, 0, 1, 2, 2, 3, 3, 4};
-    const int FB[8] = {0, 1, 0, 2, 3, 4, 5, 4};
+    // field pairs: A {s_hi s_hi s_lo bits bits} x B {t_hi t_lo t_hi r_hi r_lo}
+    const int FA[5] = {0, 0, 1, 2, 2};
+    const int FB[5] = {0, 1, 0, 2, 3};
     int ra[16] = {}, rb[16] = {};
     int nrest = 0;
-    for (int f = 0; f < 8; ++f) {
+    for (int f = 0; f < 5; ++f) {
         int c = 0;
         for (; c + 1 < nc; c += 2) {
             const int ks = p.nsteps++;
@@ -58,10 +64,10 @@ __host__ __device__ constexpr TnkTcSteps tnk_tc_steps(int nc) {
         }
         if (c < nc) { ra[nrest] = FA[f] * nc + c; rb[nrest] = FB[f] * nc + c; ++nrest; }
     }
-    ra[nrest] = 5 * nc; rb[nrest] = 6 * nc; ++nrest;          // [1,1,C_hi,C_hi] x [(qC)_hi,(qC)_lo,q_hi,q_lo]
-    ra[nrest] = 5 * nc + 1; rb[nrest] = 6 * nc + 1; ++nrest;  // [C_lo,0,0,0]     x [q_hi,0,0,0]
+    ra[nrest] = 3 * nc; rb[nrest] = 4 * nc; ++nrest;                   // [1,1,0,0] x [(qC)_hi,(qC)_lo,0,0]
+    if (nrest & 1) { ra[nrest] = 3 * nc + 1; rb[nrest] = 4 * nc + 1; ++nrest; }   // zero x zero
     bool used[16] = {};
-    p.ok = !(nrest & 1) && tnk_tc_match(ra, rb, nrest, used, p) && p.nsteps <= TNK_TC_MAX_STEPS;
+    p.ok = tnk_tc_match(ra, rb, nrest, used, p) && p.nsteps <= TNK_TC_MAX_STEPS;
     return p;
 }
 
@@ -73,6 +79,7 @@ struct TnkTcPlan {
 
 int tnk_tc_make_plan(int n, TnkTcPlan* p);
 size_t tnk_tc_table_bytes(const TnkTcPlan& p, int64_t states, bool is_b);
+size_t tnk_tc_qtab_bytes(int64_t states);
 int tnk_tc_launch(int n, double a, double gamma, const double* wl, const float* ST, const float* Cst, const float* qT,
-                  int64_t row0, int64_t launch_rows, int splits, float* A_tab, float* B_tab, double* part,
+                  int64_t row0, int64_t launch_rows, int splits, float* A_tab, float* B_tab, float* Qtab, double* part,
                   cudaEvent_t ev_start, cudaEvent_t ev_stop, int* launches, cudaStream_t st);
