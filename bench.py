@@ -2,7 +2,7 @@
 """Benchmark of the exact-KSD hot path (BASELINE.json metric: ordered state-pairs/s of one
 KSD^2 + dKSD^2/dq evaluation on a synthetic random binary BN with n latent bits).
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--n 20] [--precision fp32|fp64]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--n 20] [--precision tc32|fp32|fp64]
 
 A step = one evaluation of K = q^T K_p q and 2 K_p q for a fixed network and a given q.
 Prints ONE JSON line on rank 0.  See DESIGN.md "Measurement" for how each field is obtained.
@@ -30,7 +30,7 @@ def parse_args():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--n", type=int, default=20, help="latent bits (BASELINE.json quotes the metric at n=20)")
-    ap.add_argument("--precision", default="fp32", choices=["fp32", "fp64", "tc32"],
+    ap.add_argument("--precision", default="tc32", choices=["fp32", "fp64", "tc32"],
                     help="pair-kernel arithmetic: fp32/fp64 ALU kernels or tc32 = tcgen05 tf32 tiles with 3xTF32 split")
     ap.add_argument("--seed", type=int, default=0)
     ap.add_argument("--exchange", default="fused", choices=["fused", "nccl"],
@@ -254,6 +254,44 @@ def run_ours(args):
     if world > 1:
         dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
     e2e_value = pairs / (e2e_s.item() / args.steps)
+
+    # ---- context lines (not the headline): the fp32 ALU pair kernel on the same rows, and the
+    # enumeration kernels K1+K2 (joint + score tables) as GB/s
+    alu = None
+    if args.precision == "tc32":
+        t_alu = ops.SteinTables(tables.P, n, precision="fp32")
+        a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a0.record(); a1.record()
+        t_alu.ksd_rows(q_dev, r0, r1)
+        times = []
+        for _ in range(2):
+            flush.zero_()
+            ops.time_pair_kernel(a0, a1)
+            t_alu.ksd_rows(q_dev, r0, r1)
+            torch.cuda.synchronize()
+            times.append(a0.elapsed_time(a1))
+        ops.time_pair_kernel(None, None)
+        alu_ms = torch.tensor([float(np.mean(times))], dtype=torch.float64, device=device)
+        if world > 1:
+            dist.all_reduce(alu_ms, op=dist.ReduceOp.MAX)
+        alu = alu_ms.item()
+        del t_alu
+    en0, en1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    enum_ms, joint_ms = [], []
+    for _ in range(3):
+        flush.zero_()
+        en0.record()
+        t_tmp = ops.SteinTables(tables.P, n, precision="fp32", keep_scores=True)     # K2 alone (score tables)
+        en1.record()
+        torch.cuda.synchronize()
+        enum_ms.append(en0.elapsed_time(en1))
+        np_tmp = t_tmp.np
+        del t_tmp
+        t0 = time.perf_counter()
+        ops.joint_table(bn, x, lat, device=device)                                  # K1 incl. host flattening + CPT upload
+        torch.cuda.synchronize()
+        joint_ms.append((time.perf_counter() - t0) * 1e3)
+    enum_best, joint_best = min(enum_ms), min(joint_ms)
     return locals()
 
 
@@ -315,6 +353,22 @@ def main():
                     "d2h_bytes_per_step": (8 * (1 << n) + 8) * world},
             "gpu_launches": r["launches"], "clocks": r["clocks"], "ksd_sq": r["K_value"],
         }
+        if r["alu"] is not None:
+            alu_s = r["alu"] * 1e-3
+            alu_ach = executed * w_lane / alu_s
+            line["alu_kernel"] = {"kernel": "ksd_rows_kernel (fp32 FFMA2 pair kernel, precision fp32)", "kernel_ms": r["alu"],
+                                  "value": pairs / alu_s, "unit": UNIT, "bound": "alu", "achieved": alu_ach / 1e12,
+                                  "peak": r["peak_rate"] / 1e12, "roofline_unit": "Tlane-op/s",
+                                  "frac": alu_ach / r["peak_rate"], "lane_ops_per_pair": w_lane,
+                                  "peak_source": "tnk_alu_peak FMA-chain probe measured in this run"}
+        peaks = load_measured_peaks()
+        enum_bytes = 8.0 * (1 << n) * (n + 1) + 4.0 * (1 << n) * (r["np_tmp"] + 1)   # read P, write S64, ST, Cst
+        hbm = peaks.get("hbm_gbs") or 6650.0
+        line["enumeration"] = {"score_kernel_ms": r["enum_best"], "score_kernel_algorithmic_bytes": enum_bytes,
+                               "score_kernel_GB/s": enum_bytes / (r["enum_best"] * 1e-3) / 1e9, "peak_GB/s": hbm,
+                               "score_kernel_frac": enum_bytes / (r["enum_best"] * 1e-3) / 1e9 / hbm,
+                               "joint_table_ms_incl_host_flatten_and_upload": r["joint_best"],
+                               "joint_table_bytes": 8.0 * (1 << n)}
         if world == 1:
             S, q = cpu_tables(n, args.seed)
             info = cpu_sample(n, S, q, args.cpu_seconds)
