@@ -29,7 +29,7 @@ def parse_args():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--n", type=int, default=20, help="latent bits (BASELINE.json quotes the metric at n=20)")
+    ap.add_argument("--n", "--latent-bits", dest="n", type=int, default=20, help="latent bits (BASELINE.json quotes the metric at n=20)")
     ap.add_argument("--precision", default="tc32", choices=["fp32", "fp64", "tc32"],
                     help="pair-kernel arithmetic: fp32/fp64 ALU kernels or tc32 = tcgen05 tf32 tiles with 3xTF32 split")
     ap.add_argument("--seed", type=int, default=0)
