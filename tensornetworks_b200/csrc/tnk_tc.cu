@@ -11,27 +11,31 @@
 // the epilogue: a thread owns one row (TMEM lane) and 64 of the tile's columns, pulls 32
 // accumulator columns at a time with tcgen05.ld and folds each group of 16 columns with a register
 // table W[c] = a^popc((i^c)&15) (packed FFMA2) times one LUT value per group.  The second part
-// needs per group only Q0 = sum_c W[c] q_c and Q1 = sum_c W[c] G_lo(i,c) q_c (two more packed
-// FMA chains on the q tile in shared memory), because C(i) + g*T1 is constant over a group up to
-// the 4 low column bits: contribution = w_group * (main + E(i,J,group)*Q0 + Q1).
+// needs per group only Q0 = sum_c W[c] q_c and Q1 = sum_{p<4} g_p(i) sum_c W[c] b_p(c) q_c, which
+// depend on the row only through its low nibble: tc_qtab_kernel tabulates them once per column
+// tile and the epilogue looks them up; C(i) + g*T1 is constant over a group up to the 4 low
+// column bits: contribution = w_group * (main + E(i,J,group)*Q0 + Q1).
 // Every ordered pair of the rows x columns handed to the kernel is evaluated (4^n in total).
 //
-// Operand tables (built per call by tc_pack_kernel, K-major "interleaved" no-swizzle UMMA
+// Column operand table B (built per call by tc_pack_kernel, K-major "interleaved" no-swizzle UMMA
 // layout, one 128-state tile contiguous so that a whole tile is one run of cp.async.bulk):
 //   tile t, chunk c, row r:  float4 at ((t*K + c)*128 + r)       (chunk = 4 consecutive k)
-// A (rows i):     s_hi | s_lo | bits | [1,1,0,0] (| 0)
-// B (columns j):  t_hi | t_lo | r_hi | r_lo | [(qC)_hi,(qC)_lo,0,0] (| 0)
+//   t_hi | t_lo | r_hi | r_lo | [(qC)_hi,(qC)_lo,0,0] (| 0)
 //   t = q_j s(j),  r = gamma*q_j*rho(j),  rho_p = (1-s_p)(1-2b_p)
+// Row operand A: s_hi | s_lo | bits | [1,1,0,0] (| 0), written by the epilogue threads straight
+// into TMEM (tcgen05.st), 8 columns per K-step; the MMA is the TS form (A from TMEM, B from smem).
 // One MMA K-step (K = 8 tf32) consumes two (A-chunk, B-chunk) products; the constexpr planner
-// (tnk_tc.cuh) pairs the products so that both chunk offsets increase inside a step (they become
-// the descriptor's leading-dimension byte offsets) - shared chunks (s_hi, t_hi, bits) are stored
-// once and referenced by several steps.  n = 20: 26 products = 13 K-steps per tile.
+// (tnk_tc.cuh) pairs the products so that the B chunk offsets increase inside a step (they become
+// the descriptor's leading-dimension byte offset) - shared chunks (t_hi) are stored once and
+// referenced by several steps.  n = 20: 26 products = 13 K-steps per tile.
 //
 // Roles in a CTA of 320 threads (one CTA per SM):
-//   warp 0    producer: A tile once, then B column tiles (+ their 128 q values) through a ring of
-//             kStages shared-memory stages (bulk copy + mbarrier)
-//   warp 1    allocates TMEM (2 x 128 columns), one lane issues the MMAs and commits
-//   warps 2-9 epilogue: TMEM -> registers, Hamming weights, row sums in fp32 per tile / fp64 across tiles
+//   warp 0    producer: B column tiles and their q tables through a ring of shared-memory stages
+//             (bulk copy + mbarrier tx-count)
+//   warp 1    allocates TMEM (2 x 128 accumulator columns + the A operand), one elect.sync lane
+//             issues the MMAs and commits
+//   warps 2-9 epilogue: A -> TMEM once, then per tile TMEM -> registers, Hamming weights, row sums
+//             in fp32 per tile / compensated fp32 across tiles / one fp64 add at the end
 #include "tnk_common.cuh"
 #include "tnk_tc.cuh"
 

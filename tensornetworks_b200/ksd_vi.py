@@ -11,7 +11,8 @@ changes is where the work happens:
   TVD tracking          tensor arithmetic in enumeration order (was a 2^n-entry dict per epoch)
 
 Extra keyword-only arguments (defaults keep reference behaviour): `precision` ("fp64" |
-"fp32") selects the pair-kernel arithmetic, `compute_device` the CUDA device of the KSD
+"fp32" | "tc32") selects the pair-kernel arithmetic, `algorithm` ("pairs" = all 4^n pairs on the
+fly, "modeproduct" = the Kronecker form, O(n^2 2^n)), `compute_device` the CUDA device of the KSD
 kernels (the Born machine itself stays on `device`, as in the reference).
 """
 from functools import partial
@@ -77,7 +78,7 @@ def posterior_vector(true_posterior, num_latent_vars, device):
 class KSDVariationalInference:
     def __init__(self, bayesian_network, latent_vars_names, observed_vars_names,
                  born_machine_config, base_kernel_length_scale=1.0, device='cpu',
-                 *, precision="fp64", compute_device="cuda"):
+                 *, precision="fp64", compute_device="cuda", algorithm="pairs"):
         self.bn = bayesian_network
         self.latent_vars_names = latent_vars_names
         self.observed_vars_names = observed_vars_names
@@ -95,6 +96,8 @@ class KSDVariationalInference:
                                         length_scale=base_kernel_length_scale)
         self.precision = precision
         self.compute_device = compute_device
+        self.algorithm = algorithm
+        self._exchange = None
         self.tables = None
         self._score_function_cache = ScoreCache()
 
@@ -115,7 +118,22 @@ class KSDVariationalInference:
 
     def ksd_squared(self, q_probs_all_z):
         """K = sum_ij q_i q_j k_p(z_i,z_j) as a differentiable fp64 scalar (the hot loop)."""
-        return ops.ksd_quadratic_form(q_probs_all_z, self.tables)
+        return ops.ksd_quadratic_form(q_probs_all_z, self.tables, algorithm=self.algorithm,
+                                      exchange=self._peer_exchange())
+
+    def _peer_exchange(self):
+        """Under torch.distributed (one rank per GPU of a box) the row-sharded pair evaluation stores
+        its rows straight into every rank's symmetric-memory buffer (ops.PeerExchange); falls back to
+        the NCCL all_gather inside ops when symmetric memory cannot be set up."""
+        import torch.distributed as dist
+        if self.algorithm != "pairs" or not (dist.is_available() and dist.is_initialized()) or dist.get_world_size() == 1:
+            return None
+        if self._exchange is None:
+            try:
+                self._exchange = ops.PeerExchange(self.tables.N, self.tables.device)
+            except Exception:
+                self._exchange = False
+        return self._exchange or None
 
     def train(self, x_observation_dict, num_epochs, lr_born_machine,
               verbose=True, true_posterior_for_tvd=None,

@@ -27,7 +27,7 @@ class KSDVariationalInference:
                  qbm_num_latent_vars, qbm_ansatz_layers=1, qbm_conditioning_dim=0,
                  qbm_pennylane_device_name="default.qubit", qbm_ansatz_type="hardware_efficient",
                  qbm_init_method="small_random", base_kernel_length_scale=1.0, pytorch_device='cpu',
-                 *, precision="fp64", compute_device="cuda"):
+                 *, precision="fp64", compute_device="cuda", algorithm="pairs"):
         self.bn = bayesian_network
         self.latent_vars_names = latent_vars_names
         self.observed_vars_names = observed_vars_names
@@ -43,7 +43,7 @@ class KSDVariationalInference:
         self.base_kernel_length_scale = base_kernel_length_scale
         self.base_kernel_func = partial(base_hamming_kernel_torch, num_vars=self.num_latent_vars,
                                         length_scale=base_kernel_length_scale)
-        self.precision, self.compute_device = precision, compute_device
+        self.precision, self.compute_device, self.algorithm = precision, compute_device, algorithm
         self.tables = None
         self._score_function_cache = ScoreCache()
 
@@ -104,7 +104,7 @@ class KSDVariationalInference:
             if q.shape[0] != self.num_possible_latent_states:
                 raise ValueError("Probabilities from Born machine have unexpected shape")
 
-            K = ops.ksd_quadratic_form(q, self.tables)               # ksd_vi_quantum.py:122-142
+            K = ops.ksd_quadratic_form(q, self.tables, algorithm=self.algorithm)   # ksd_vi_quantum.py:122-142
             loss = torch.sqrt(K.clamp(min=1e-12))                    # :144-145
             if torch.isnan(loss) or torch.isinf(loss):
                 print(f"Warning: NaN or Inf KSD loss: {loss.item()}. Skipping update.")
