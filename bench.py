@@ -325,7 +325,9 @@ def main():
         if args.precision == "tc32":
             from tensornetworks_b200 import ops as _ops
             plan = _ops.tc_plan(n)
-            flops_pair = 2 * 8 * plan["nsteps"]            # MMA flops issued per pair (K = 8 per tf32 K-step)
+            # tf32-equivalent MMA flops issued per pair: a tf32 K-step (K = 8) and a bf16 K-step (K = 16) occupy
+            # the tensor pipe for the same time, so both count 2*8 against the tf32 peak
+            flops_pair = 2 * 8 * (plan["nsteps"] + plan["nsteps16"])
             peaks = load_measured_peaks()
             bf16 = peaks.get("bf16_tflops_sustained") or peaks.get("bf16_tflops")
             peak_tf = (bf16 / 2.0) if bf16 else 1590.0 / 2.0
@@ -333,7 +335,7 @@ def main():
             roofline = {"bound": "tensor", "achieved": ach_tf, "peak": peak_tf, "unit": "TFLOP/s",
                         "frac": ach_tf / peak_tf, "traffic": None, "kernel": "tc_rows_kernel",
                         "kernel_ms": r["kmean_ms"].item(), "mma_flops_per_pair": flops_pair,
-                        "k_steps": plan["nsteps"],
+                        "k_steps_tf32": plan["nsteps"], "k_steps_bf16": plan["nsteps16"],
                         "peak_source": ("half of MEASURED_PEAKS.json bf16_tflops_sustained (kind::tf32 runs at half the "
                                         "bf16 rate; the kernel is timed inside a long step)" if bf16 else
                                         "half of the fallback 1.59 PFLOP/s bf16 figure of B200_PROFILING.md"),

@@ -129,11 +129,13 @@ int tnk_ksd_modeproduct(int n_latent, double length_scale, const void* q, int q_
                         double* u, double* ksd_part,
                         void* workspace, size_t workspace_bytes, int* n_launch, void* stream);
 
-/* Introspection of the tensor-core variant (TNK_PREC_TC32): padded score length, chunks (4 floats)
- * per state of the row and column operand tables, and the MMA K-step list - step k multiplies row
- * chunks {s[4k], s[4k]+s[4k+1]} with column chunks {s[4k+2], s[4k+2]+s[4k+3]}.  steps: host int32
- * [4*32] or NULL.  Used by the CPU tests to check that the steps cover the bracket exactly. */
-int tnk_tc_plan(int n_latent, int* np, int* ka, int* kb, int* nsteps, int32_t* steps);
+/* Introspection of the tensor-core variant (TNK_PREC_TC32): padded score length np, number of
+ * tf32 chunks (4 floats) per state k32, total 16-byte chunks per state of the column table kb
+ * (tf32 chunks followed by bf16 chunks), the tf32 MMA K-step list - step k multiplies row chunks
+ * {s[4k], s[4k]+s[4k+1]} with column chunks {s[4k+2], s[4k+2]+s[4k+3]} - and the number of bf16
+ * K-steps (K = 16; step k uses bf16 chunks 2k, 2k+1 on both sides).  steps: host int32 [4*32] or
+ * NULL.  Used by the CPU tests to check that the steps cover the bracket exactly. */
+int tnk_tc_plan(int n_latent, int* np, int* k32, int* kb, int* nsteps, int* nsteps16, int32_t* steps);
 
 /* Measurement hook: when both are non-NULL cudaEvent_t handles, every following tnk_ksd_rows call
  * on this host thread records them on its stream immediately before and after the pair kernel

@@ -108,7 +108,7 @@ def load():
                                         ctypes.POINTER(c_int), c_vp]
     lib.tnk_tc_plan.restype = c_int
     lib.tnk_tc_plan.argtypes = [c_int, ctypes.POINTER(c_int), ctypes.POINTER(c_int), ctypes.POINTER(c_int),
-                                ctypes.POINTER(c_int), ctypes.POINTER(ctypes.c_int32)]
+                                ctypes.POINTER(c_int), ctypes.POINTER(c_int), ctypes.POINTER(ctypes.c_int32)]
     lib.tnk_ksd_timing_events.restype = c_int
     lib.tnk_ksd_timing_events.argtypes = [c_vp, c_vp]
     lib.tnk_alu_peak.restype = c_int

@@ -36,13 +36,14 @@
 //             issues the MMAs and commits
 //   warps 2-9 epilogue: A -> TMEM once, then per tile TMEM -> registers, Hamming weights, row sums
 //             in fp32 per tile / compensated fp32 across tiles / one fp64 add at the end
+#include <cuda_bf16.h>
 #include "tnk_common.cuh"
 #include "tnk_tc.cuh"
 
 namespace {
 
 constexpr int kTcThreads = 320;
-constexpr int kMaxStages = 4;                 // B ring depth is 4 (NC <= 5) or 3 (NC = 6, shared-memory limit)
+constexpr int kMaxStages = 4;                 // B ring depth (NC = 6: 4 x 48 KB + tables = 213 KB of shared memory)
 constexpr int kQSlots = 8;                    // q-table ring depth >= kStages + 2 + 1 (see the producer comment)
 constexpr int kQTab = 5 * 8 * 16;             // floats per column tile: [Q0,Qb0..Qb3][8 groups][16 row variants]
 constexpr int kTile = TNK_TC_TILE;            // rows per CTA = columns per stage = 128
@@ -102,6 +103,14 @@ __device__ __forceinline__ void umma_tf32_ts(uint32_t tmem_d, uint32_t tmem_a, u
         "tcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], %2, %3, p;\n\t}"
         ::"r"(tmem_d), "r"(tmem_a), "l"(desc_b), "r"(idesc), "r"(accumulate) : "memory");
 }
+// same accumulator, kind::f16 with bf16 operands: one K-step of 16, A packed two per TMEM column
+__device__ __forceinline__ void umma_bf16_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t desc_b, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}"
+        ::"r"(tmem_d), "r"(tmem_a), "l"(desc_b), "r"(idesc), "r"(accumulate) : "memory");
+}
 __device__ __forceinline__ void umma_commit(uint64_t* bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
@@ -115,6 +124,7 @@ __device__ __forceinline__ uint64_t smem_desc(uint32_t byte_addr, uint32_t lbo_b
 }
 
 // instruction descriptor: D f32, A/B tf32, both K-major, M = 128, N = 128
+constexpr uint32_t kIdescBf16 = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(kTile >> 3) << 17) | ((uint32_t)(kTile >> 4) << 24);
 constexpr uint32_t kIdesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(kTile >> 3) << 17) | ((uint32_t)(kTile >> 4) << 24);
 
 struct TcParams {
@@ -130,49 +140,66 @@ struct TcParams {
 __device__ __forceinline__ float tf_hi(float x) { return __uint_as_float(__float_as_uint(x) & 0xFFFFE000u); }
 __device__ __forceinline__ float tf_lo(float x) { return x - tf_hi(x); }
 
-// ---- operand tables.  One thread = one float4 (4 consecutive k of one state).
-template <bool IS_B>
+__device__ __forceinline__ uint32_t bf16_bits(float x) {   // round to nearest even
+    return (uint32_t)__bfloat16_as_ushort(__float2bfloat16_rn(x));
+}
+__device__ __forceinline__ uint32_t bf16_pack(float lo, float hi) { return bf16_bits(lo) | (bf16_bits(hi) << 16); }
+
+// ---- column operand table.  One thread = one 16-byte chunk of one state: 4 floats (tf32 part) or
+// 8 bf16 (cross-term part).  Layout: tile t, chunk c, row r at 16-byte slot ((t*K + c)*128 + r).
 __global__ void __launch_bounds__(256)
-tc_pack_kernel(int n, int np, int64_t first_state, int64_t n_tiles, float gamma,
+tc_pack_kernel(int n, int np, int64_t n_tiles, float gamma,
                const float* __restrict__ ST, const float* __restrict__ Cst, const float* __restrict__ qT,
-               float4* __restrict__ out) {
+               uint4* __restrict__ out) {
     const int nc = np >> 2;
-    const int K = IS_B ? tnk_tc_kb(nc) : tnk_tc_ka(nc);
+    const int K32 = tnk_tc_k32(nc), K = tnk_tc_kb(nc);
     const int64_t idx = (int64_t)blockIdx.x * 256 + threadIdx.x;
     const int row = (int)(idx & (kTile - 1));
     const int64_t t = idx >> 7;
     const int chunk = (int)(t % K);
     const int64_t tile = t / K;
     if (tile >= n_tiles) return;
-    const int64_t z = first_state + tile * kTile + row;
-    const int nfield = IS_B ? 4 : 3;
-    float v[4] = {0.f, 0.f, 0.f, 0.f};
-    if (chunk < nfield * nc) {
+    const int64_t z = tile * kTile + row;
+    const float q = qT[z];
+    const float* srow = ST + z * np;
+    auto col_terms = [&](int p, float& ts, float& r) {   // t_p = q s_p, r_p = gamma q rho_p
+        const float sp = srow[p];
+        const bool bit = (z >> p) & 1;
+        ts = q * sp;
+        r = (p < n) ? (gamma * q) * (bit ? -(1.f - sp) : (1.f - sp)) : 0.f;
+    };
+    uint32_t w[4] = {0u, 0u, 0u, 0u};
+    if (chunk < 2 * nc) {                              // t_hi | r_hi
         const int f = chunk / nc, c = chunk - f * nc;
-        const float4 s4 = *reinterpret_cast<const float4*>(ST + z * np + 4 * c);
-        const float s[4] = {s4.x, s4.y, s4.z, s4.w};
-        const float q = IS_B ? qT[z] : 0.f;
 #pragma unroll
         for (int e = 0; e < 4; ++e) {
-            const int p = 4 * c + e;
-            const bool valid = p < n;
-            const bool bit = valid && ((z >> p) & 1);
-            float x;
-            if (!IS_B) {
-                x = f == 0 ? tf_hi(s[e]) : f == 1 ? tf_lo(s[e]) : (bit ? 1.f : 0.f);
-            } else {
-                const float rho = valid ? (bit ? -(1.f - s[e]) : (1.f - s[e])) : 0.f;
-                const float ts = q * s[e];
-                const float r = (gamma * q) * rho;
-                x = f == 0 ? tf_hi(ts) : f == 1 ? tf_lo(ts) : f == 2 ? tf_hi(r) : tf_lo(r);
-            }
-            v[e] = x;
+            float ts, r;
+            col_terms(4 * c + e, ts, r);
+            w[e] = __float_as_uint(tf_hi(f == 0 ? ts : r));
         }
-    } else if (chunk == nfield * nc) {
-        if (!IS_B) { v[0] = 1.f; v[1] = 1.f; }
-        else { const float qc = qT[z] * Cst[z]; v[0] = tf_hi(qc); v[1] = tf_lo(qc); }
-    }   // else: the zero chunk that pads an odd number of chunk products
-    out[idx] = make_float4(v[0], v[1], v[2], v[3]);
+    } else if (chunk == 2 * nc) {                      // [(qC)_hi, (qC)_lo, 0, 0]
+        const float qc = q * Cst[z];
+        w[0] = __float_as_uint(tf_hi(qc));
+        w[1] = __float_as_uint(tf_lo(qc));
+    } else if (chunk >= K32) {                         // bf16 region: bf(t_lo) | bf(t) | bf(r_lo) | 0
+        const int m = chunk - K32;
+        float v[8];
+#pragma unroll
+        for (int x = 0; x < 8; ++x) {
+            const int e = 8 * m + x;
+            const int f = e / np, p = e - f * np;
+            float val = 0.f;
+            if (f < 3) {
+                float ts, r;
+                col_terms(p, ts, r);
+                val = f == 0 ? tf_lo(ts) : f == 1 ? ts : tf_lo(r);
+            }
+            v[x] = val;
+        }
+#pragma unroll
+        for (int e = 0; e < 4; ++e) w[e] = bf16_pack(v[2 * e], v[2 * e + 1]);
+    }   // chunk == 2*nc + 1: the zero chunk that pads the odd tf32 product count
+    out[idx] = make_uint4(w[0], w[1], w[2], w[3]);
 }
 
 // ---- per-column-tile q tables of the ALU part.  For group g (16 columns) and row variant v = i & 15:
@@ -203,7 +230,7 @@ tc_qtab_kernel(const float* __restrict__ qT, float w1, float* __restrict__ out) 
 // ---- the tile kernel, NC = 4-float chunks per field (np / 4)
 template <int NC>
 struct TcSmem {
-    static constexpr int stages = NC <= 5 ? kMaxStages : 3;
+    static constexpr int stages = kMaxStages;
     static constexpr uint32_t b_bytes = (uint32_t)tnk_tc_kb(NC) * kChunkBytes;
     static constexpr uint32_t off_b = 0;
     static constexpr uint32_t off_q = off_b + stages * b_bytes;           // [kQSlots][kQTab] float
@@ -225,6 +252,7 @@ tc_rows_kernel(const __grid_constant__ TcParams prm, const float* __restrict__ B
     constexpr TnkTcSteps P = tnk_tc_steps(NC);
     static_assert(P.ok, "no K-step plan for this chunk count");
     constexpr int NP = 4 * NC;
+    constexpr int K32 = tnk_tc_k32(NC), S16 = tnk_tc_steps16(NC);
     constexpr int kStages = SM::stages;
     constexpr uint32_t b_bytes = SM::b_bytes;
     unsigned char* sB = smem + SM::off_b;
@@ -311,6 +339,12 @@ tc_rows_kernel(const __grid_constant__ TcParams prm, const float* __restrict__ B
                     const uint64_t db = b_desc + (uint64_t)((uint32_t)P.b0[ks] * cu + (((uint32_t)P.blb[ks] * cu) << 16));
                     umma_tf32_ts(d_addr, tmem_base + (uint32_t)(kTmemA + 8 * ks), db, kIdesc, ks > 0 ? 1u : 0u);
                 }
+#pragma unroll
+                for (int k = 0; k < S16; ++k) {               // cross terms in bf16: chunks 2k, 2k+1 of the bf16 region
+                    constexpr uint32_t cu = kChunkBytes >> 4;
+                    const uint64_t db = b_desc + (uint64_t)((uint32_t)(K32 + 2 * k) * cu + (cu << 16));
+                    umma_bf16_ts(d_addr, tmem_base + (uint32_t)(kTmemA + 8 * (P.nsteps + k)), db, kIdescBf16, 1u);
+                }
                 umma_commit(bar_empty + s);    // B stage free once these MMAs have read it
                 umma_commit(bar_tfull + ts);   // accumulator stage ready
                 }
@@ -334,23 +368,35 @@ tc_rows_kernel(const __grid_constant__ TcParams prm, const float* __restrict__ B
                 const float4 s4 = *reinterpret_cast<const float4*>(ST + i * NP + 4 * c);
                 sv[4 * c] = s4.x; sv[4 * c + 1] = s4.y; sv[4 * c + 2] = s4.z; sv[4 * c + 3] = s4.w;
             }
-            // A operand of this row -> TMEM: K-step ks occupies columns kTmemA + 8*ks .. +7 (its two
-            // chunks side by side); the two warps of a lane quarter write alternate steps.
-            // Chunk c of the row table: s_hi | s_lo | bits | [1,1,0,0] | 0  (see the file header).
-            auto a_val = [&](int chunk, int e) -> float {
+            // A operand of this row -> TMEM: every K-step occupies 8 columns from kTmemA (tf32: its two
+            // 4-float chunks side by side; bf16: 16 values packed two per column, low half = even k);
+            // the two warps of a lane quarter write alternate steps.
+            // A32 chunks: s_hi | bits | [1,1,0,0] | 0.   A16 vector: bf(s) | bf(s_lo) | bits | 0.
+            auto a32 = [&](int chunk, int e) -> float {
+                if (chunk >= 2 * NC) return (chunk == 2 * NC && e < 2) ? 1.f : 0.f;
                 const int f = chunk / NC, p = 4 * (chunk - f * NC) + e;
-                if (chunk >= 3 * NC) return (chunk == 3 * NC && e < 2) ? 1.f : 0.f;
-                const float x = sv[p < NP ? p : 0];
-                return f == 0 ? tf_hi(x) : f == 1 ? tf_lo(x) : ((p < n && ((i >> p) & 1)) ? 1.f : 0.f);
+                return f == 0 ? tf_hi(sv[p]) : ((p < n && ((i >> p) & 1)) ? 1.f : 0.f);
+            };
+            auto a16 = [&](int e) -> float {
+                const int f = e / NP, p = e - f * NP;
+                if (f >= 3) return 0.f;
+                const float x = sv[p];
+                return f == 0 ? x : f == 1 ? tf_lo(x) : ((p < n && ((i >> p) & 1)) ? 1.f : 0.f);
             };
 #pragma unroll
-            for (int ks = 0; ks < P.nsteps; ++ks) {
+            for (int ks = 0; ks < P.nsteps + S16; ++ks) {
                 if ((ks & 1) == half) {
                     uint32_t av[8];
+                    if (ks < P.nsteps) {
 #pragma unroll
-                    for (int e = 0; e < 4; ++e) {
-                        av[e] = __float_as_uint(a_val(P.a0[ks], e));
-                        av[4 + e] = __float_as_uint(a_val(P.a0[ks] + P.alb[ks], e));
+                        for (int e = 0; e < 4; ++e) {
+                            av[e] = __float_as_uint(a32(P.a0[ks < P.nsteps ? ks : 0], e));
+                            av[4 + e] = __float_as_uint(a32(P.a0[ks < P.nsteps ? ks : 0] + P.alb[ks < P.nsteps ? ks : 0], e));
+                        }
+                    } else {
+#pragma unroll
+                        for (int c = 0; c < 8; ++c)
+                            av[c] = bf16_pack(a16(16 * (ks - P.nsteps) + 2 * c), a16(16 * (ks - P.nsteps) + 2 * c + 1));
                     }
                     asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};"
                                  ::"r"(tmem_base + ((uint32_t)lq << 16) + (uint32_t)(kTmemA + 8 * ks)),
@@ -479,19 +525,20 @@ int tnk_tc_make_plan(int n, TnkTcPlan* p) {
     if (n < TNK_TC_MIN_LATENT || n > TNK_TC_MAX_LATENT) return 1;
     const int np = ((n + 3) / 4) * 4;
     const int nc = np / 4;
-    p->np = np; p->nc = nc; p->ka = tnk_tc_ka(nc); p->kb = tnk_tc_kb(nc);
+    p->np = np; p->nc = nc; p->k32 = tnk_tc_k32(nc); p->kb = tnk_tc_kb(nc); p->steps16 = tnk_tc_steps16(nc);
     p->s = tnk_tc_steps(nc);
     return p->s.ok ? 0 : 1;
 }
 
-extern "C" int tnk_tc_plan(int n_latent, int* np, int* ka, int* kb, int* nsteps, int32_t* steps) {
+extern "C" int tnk_tc_plan(int n_latent, int* np, int* k32, int* kb, int* nsteps, int* nsteps16, int32_t* steps) {
     TnkTcPlan p;
     TNK_REQUIRE(tnk_tc_make_plan(n_latent, &p) == 0, "tnk_tc_plan: no tensor-core plan for n=%d (supported %d..%d)",
                 n_latent, TNK_TC_MIN_LATENT, TNK_TC_MAX_LATENT);
     if (np) *np = p.np;
-    if (ka) *ka = p.ka;
+    if (k32) *k32 = p.k32;
     if (kb) *kb = p.kb;
     if (nsteps) *nsteps = p.s.nsteps;
+    if (nsteps16) *nsteps16 = p.steps16;
     if (steps)
         for (int ks = 0; ks < p.s.nsteps; ++ks) {
             steps[4 * ks + 0] = p.s.a0[ks]; steps[4 * ks + 1] = p.s.alb[ks];
@@ -530,8 +577,8 @@ int tnk_tc_launch(int n, double a, double gamma, const double* wl, const float* 
     const int64_t row_tiles = launch_rows / kTile, col_tiles = N / kTile;
     {
         const int64_t items = col_tiles * p.kb * kTile;
-        tc_pack_kernel<true><<<(unsigned)((items + 255) / 256), 256, 0, st>>>(n, p.np, 0, col_tiles, (float)gamma, ST, Cst, qT,
-                                                                             reinterpret_cast<float4*>(B_tab));
+        tc_pack_kernel<<<(unsigned)((items + 255) / 256), 256, 0, st>>>(n, p.np, col_tiles, (float)gamma, ST, Cst, qT,
+                                                                       reinterpret_cast<uint4*>(B_tab));
         TNK_CUDA_OK(cudaGetLastError());
     }
     tc_qtab_kernel<<<(unsigned)col_tiles, 128, 0, st>>>(qT, (float)wl[1], Qtab);

@@ -42,39 +42,46 @@ __host__ __device__ constexpr bool tnk_tc_match(const int* ia, const int* ib, in
     return false;
 }
 
-// Table widths in chunks.  A (rows): s_hi | s_lo | bits | [1,1,0,0] (| zero);
-// B (columns): t_hi | t_lo | r_hi | r_lo | [(qC)_hi,(qC)_lo,0,0] (| zero).  The zero chunks exist only
-// when the number of chunk products 5*nc+1 is odd (nc even) and pad the last K-step.
-__host__ __device__ constexpr int tnk_tc_ka(int nc) { return 3 * nc + 1 + (((5 * nc + 1) & 1) ? 1 : 0); }
-__host__ __device__ constexpr int tnk_tc_kb(int nc) { return 4 * nc + 1 + (((5 * nc + 1) & 1) ? 1 : 0); }
+// Operand structure (chunk = 16 bytes of one state).
+//   tf32 part (4 floats per chunk), products with the high parts:
+//     A32 (rows):    s_hi (nc) | bits (nc) | [1,1,0,0] | 0
+//     B32 (columns): t_hi (nc) | r_hi (nc) | [(qC)_hi,(qC)_lo,0,0] | 0          -> 2*nc+2 chunks, nc+1 K-steps
+//   bf16 part (8 bf16 per chunk), the second-order cross terms hi*lo + lo*hi, which tolerate 8-bit
+//   mantissas (error ~2^-20 of the product):
+//     A16 (rows):    bf(s) (np) | bf(s_lo) (np) | bits (np) | 0...
+//     B16 (columns): bf(t_lo)   | bf(t)         | bf(r_lo)  | 0...             -> ceil(3*np/16) K-steps of K = 16
+// The column table stores the B32 chunks followed by the B16 chunks of a tile.
+__host__ __device__ constexpr int tnk_tc_k32(int nc) { return 2 * nc + 2; }
+__host__ __device__ constexpr int tnk_tc_steps16(int nc) { return (3 * 4 * nc + 15) / 16; }
+__host__ __device__ constexpr int tnk_tc_k16(int nc) { return 2 * tnk_tc_steps16(nc); }
+__host__ __device__ constexpr int tnk_tc_kb(int nc) { return tnk_tc_k32(nc) + tnk_tc_k16(nc); }
 
+// tf32 K-steps: chunk indices inside A32 / B32
 __host__ __device__ constexpr TnkTcSteps tnk_tc_steps(int nc) {
     TnkTcSteps p{};
-    // field pairs: A {s_hi s_hi s_lo bits bits} x B {t_hi t_lo t_hi r_hi r_lo}
-    const int FA[5] = {0, 0, 1, 2, 2};
-    const int FB[5] = {0, 1, 0, 2, 3};
     int ra[16] = {}, rb[16] = {};
     int nrest = 0;
-    for (int f = 0; f < 5; ++f) {
+    for (int f = 0; f < 2; ++f) {            // s_hi x t_hi, bits x r_hi: same chunk index on both sides
         int c = 0;
         for (; c + 1 < nc; c += 2) {
             const int ks = p.nsteps++;
-            p.a0[ks] = FA[f] * nc + c; p.alb[ks] = 1;
-            p.b0[ks] = FB[f] * nc + c; p.blb[ks] = 1;
+            p.a0[ks] = f * nc + c; p.alb[ks] = 1;
+            p.b0[ks] = f * nc + c; p.blb[ks] = 1;
         }
-        if (c < nc) { ra[nrest] = FA[f] * nc + c; rb[nrest] = FB[f] * nc + c; ++nrest; }
+        if (c < nc) { ra[nrest] = f * nc + c; rb[nrest] = f * nc + c; ++nrest; }
     }
-    ra[nrest] = 3 * nc; rb[nrest] = 4 * nc; ++nrest;                   // [1,1,0,0] x [(qC)_hi,(qC)_lo,0,0]
-    if (nrest & 1) { ra[nrest] = 3 * nc + 1; rb[nrest] = 4 * nc + 1; ++nrest; }   // zero x zero
+    ra[nrest] = 2 * nc; rb[nrest] = 2 * nc; ++nrest;                      // [1,1,0,0] x [(qC)_hi,(qC)_lo,0,0]
+    if (nrest & 1) { ra[nrest] = 2 * nc + 1; rb[nrest] = 2 * nc + 1; ++nrest; }   // zero x zero
     bool used[16] = {};
-    p.ok = tnk_tc_match(ra, rb, nrest, used, p) && p.nsteps <= TNK_TC_MAX_STEPS;
+    p.ok = tnk_tc_match(ra, rb, nrest, used, p) && p.nsteps + tnk_tc_steps16(nc) <= TNK_TC_MAX_STEPS;
     return p;
 }
 
 struct TnkTcPlan {
     int np, nc;      // padded score length, 4-float chunks per field
-    int ka, kb;      // chunks per state in the A (row) and B (column) tables
-    TnkTcSteps s;
+    int k32, kb;     // tf32 chunks per state; total chunks per state of the column table (tf32 + bf16)
+    int steps16;     // bf16 K-steps (K = 16), chunks 2k, 2k+1 of the bf16 region on both sides
+    TnkTcSteps s;    // tf32 K-steps
 };
 
 int tnk_tc_make_plan(int n, TnkTcPlan* p);

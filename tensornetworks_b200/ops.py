@@ -346,10 +346,11 @@ def ksd_quadratic_form(q, tables, group=None, algorithm="pairs", exchange=None):
 def tc_plan(n):
     """K-step plan of the tensor-core variant for n latent bits (tnk_tc_plan)."""
     lib = _lib.load()
-    np_, ka, kb, ns = ctypes.c_int(), ctypes.c_int(), ctypes.c_int(), ctypes.c_int()
+    np_, k32, kb, ns, ns16 = ctypes.c_int(), ctypes.c_int(), ctypes.c_int(), ctypes.c_int(), ctypes.c_int()
     steps = (ctypes.c_int32 * 128)()
-    _lib.check(lib.tnk_tc_plan(n, ctypes.byref(np_), ctypes.byref(ka), ctypes.byref(kb), ctypes.byref(ns), steps), "tnk_tc_plan")
-    return {"np": np_.value, "ka": ka.value, "kb": kb.value, "nsteps": ns.value,
+    _lib.check(lib.tnk_tc_plan(n, ctypes.byref(np_), ctypes.byref(k32), ctypes.byref(kb), ctypes.byref(ns),
+                               ctypes.byref(ns16), steps), "tnk_tc_plan")
+    return {"np": np_.value, "k32": k32.value, "kb": kb.value, "nsteps": ns.value, "nsteps16": ns16.value,
             "steps": [tuple(steps[4 * k:4 * k + 4]) for k in range(ns.value)]}
 
 
