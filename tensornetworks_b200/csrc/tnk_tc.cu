@@ -3,10 +3,12 @@
 // With j the column state, the bracket of k_p splits into
 //   q_j * [ s(i).s(j) + g*T2(i,j) + C(j) ]           bilinear in per-state feature vectors -> tensor cores
 //   q_j * [ C(i) + g*T1(i,j) ],  T1 = sum_p rho_p(i) b_p(j)   depends on j only through its BITS -> ALU
-// A 128 x 128 tile of the first part is one GEMM tile: tcgen05.mma (kind::tf32), accumulator in
-// TMEM.  fp32-grade accuracy (the 1e-4 parity mode) comes from the 3xTF32 split x = hi + lo
-// (hi = top 10 mantissa bits, lo = x - hi exactly): a real product x*y is issued as
-// hi*hi + hi*lo + lo*hi; factors that are exact in tf32 (bits, 1) need no split.
+// A 128 x 128 tile of the first part is one GEMM tile: tcgen05.mma with the accumulator in TMEM.
+// fp32-grade accuracy (the 1e-4 parity mode) comes from a split x = hi + lo (hi = top 10 mantissa
+// bits, lo = x - hi exactly): a real product x*y is issued as hi*hi (kind::tf32) plus the
+// second-order cross terms hi*lo + lo*hi, which tolerate 8-bit mantissas and are issued as bf16
+// (kind::f16, K = 16 per step, half the tensor time per element) into the SAME accumulator;
+// factors that are exact (bits, 1) need no split.  Measured error against the fp64 kernel <= 2e-6.
 // The a^popc(i^j) weight does not factorise into a low-rank form, so it is applied per pair in
 // the epilogue: a thread owns one row (TMEM lane) and 64 of the tile's columns, pulls 32
 // accumulator columns at a time with tcgen05.ld and folds each group of 16 columns with a register
@@ -20,14 +22,15 @@
 // Column operand table B (built per call by tc_pack_kernel, K-major "interleaved" no-swizzle UMMA
 // layout, one 128-state tile contiguous so that a whole tile is one run of cp.async.bulk):
 //   tile t, chunk c, row r:  float4 at ((t*K + c)*128 + r)       (chunk = 4 consecutive k)
-//   t_hi | t_lo | r_hi | r_lo | [(qC)_hi,(qC)_lo,0,0] (| 0)
+//   tf32 chunks (4 floats): t_hi | r_hi | [(qC)_hi,(qC)_lo,0,0] | 0
+//   bf16 chunks (8 values): bf(t_lo) | bf(t) | bf(r_lo) | 0...
 //   t = q_j s(j),  r = gamma*q_j*rho(j),  rho_p = (1-s_p)(1-2b_p)
-// Row operand A: s_hi | s_lo | bits | [1,1,0,0] (| 0), written by the epilogue threads straight
-// into TMEM (tcgen05.st), 8 columns per K-step; the MMA is the TS form (A from TMEM, B from smem).
-// One MMA K-step (K = 8 tf32) consumes two (A-chunk, B-chunk) products; the constexpr planner
-// (tnk_tc.cuh) pairs the products so that the B chunk offsets increase inside a step (they become
-// the descriptor's leading-dimension byte offset) - shared chunks (t_hi) are stored once and
-// referenced by several steps.  n = 20: 26 products = 13 K-steps per tile.
+// Row operand A: tf32 s_hi | bits | [1,1,0,0] | 0 and bf16 bf(s) | bf(s_lo) | bits, written by the
+// epilogue threads straight into TMEM (tcgen05.st), 8 columns per K-step; the MMAs are the TS form
+// (A from TMEM, B from shared memory).  A tf32 K-step (K = 8) consumes two (A-chunk, B-chunk)
+// products of 4 floats, paired by the constexpr planner (tnk_tc.cuh) so that the B chunk offsets
+// increase inside a step (they become the descriptor's leading-dimension byte offset); a bf16
+// K-step (K = 16) consumes two consecutive 8-value chunks.  n = 20: 6 tf32 + 4 bf16 = 10 K-steps.
 //
 // Roles in a CTA of 320 threads (one CTA per SM):
 //   warp 0    producer: B column tiles and their q tables through a ring of shared-memory stages
