@@ -103,7 +103,7 @@ def run_reference(args):
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 # ------------------------------------------------------------------ clocks during the timed region
@@ -164,8 +164,8 @@ def run_ours(args):
     torch.cuda.set_device(local_rank)
     device = torch.device("cuda", local_rank)
     if world > 1:
-        if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
-            os.environ["NCCL_DEBUG"] = "WARN"      # keep NCCL's version banner off stdout (one JSON line only)
+        if os.environ.get("NCCL_DEBUG", "").upper() in ("VERSION", "WARN"):
+            os.environ.pop("NCCL_DEBUG")           # these levels print NCCL's version banner on stdout
         dist.init_process_group("nccl", device_id=device)
     n, N = args.n, 1 << args.n
     pairs = 4.0 ** n
@@ -303,8 +303,22 @@ def load_measured_peaks():
         return {}
 
 
+def emit(line):
+    """The one JSON line of the contract, written to the process's ORIGINAL stdout."""
+    os.write(_REAL_STDOUT, (json.dumps(line) + "\n").encode())
+
+
+_REAL_STDOUT = 1
+
+
 def main():
+    global _REAL_STDOUT
     args = parse_args()
+    # Library banners (NCCL, torchrun children) must not share stdout with the JSON line: keep a private
+    # copy of stdout for emit() and point fd 1 at stderr for everything else.
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
     if args.impl == "reference":
         run_reference(args)
         return
@@ -380,7 +394,7 @@ def main():
                                     "sample": f"{info['rows']} full rows x 2^{n} columns = {info['pairs']:.3g} ordered pairs "
                                               f"in {info['seconds']:.1f} s (oracle/ksd_oracle.c, literal four-term pair loop)",
                                     "gpu_vs_oracle_rows_max_rel_err": err}
-        print(json.dumps(line), flush=True)
+        emit(line)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
