@@ -436,7 +436,7 @@ struct Plan {
     int row_blocks, splits;
     bool tensor;          // TNK_PREC_TC32 with a tensor-core plan (7 <= n <= 24); else the ALU kernels
     TnkTcPlan tc;
-    size_t off_q, off_part, off_block, off_a, off_b, off_qtab, total;
+    size_t off_q, off_part, off_block, off_b, off_qtab, total;
 };
 
 int make_plan(int n, int precision, int64_t row_begin, int64_t row_end, Plan* p) {
@@ -457,7 +457,7 @@ int make_plan(int n, int precision, int64_t row_begin, int64_t row_end, Plan* p)
     }
     if (p->tensor) {
         // one split's slice of the column table should stay L2-resident (126 MB L2; 32 MB target)
-        const size_t b_bytes = tnk_tc_table_bytes(p->tc, p->N, true);
+        const size_t b_bytes = tnk_tc_table_bytes(p->tc, p->N);
         while ((b_bytes / splits) > ((size_t)32 << 20) && splits * 2 <= p->n_tiles) splits *= 2;
     }
     p->splits = splits;
@@ -466,11 +466,10 @@ int make_plan(int n, int precision, int64_t row_begin, int64_t row_end, Plan* p)
     p->off_q = off;      off += ((size_t)p->g.n_pad * p->g.elem + 255) / 256 * 256;
     p->off_part = off;   off += ((size_t)splits * p->launch_rows * sizeof(double) + 255) / 256 * 256;
     p->off_block = off;  off += ((size_t)(p->finish_blocks + 1) * sizeof(double) + 255) / 256 * 256;
-    p->off_a = p->off_b = p->off_qtab = off;
+    p->off_b = p->off_qtab = off;
     if (p->tensor) {
         p->off_qtab = off;  off += (tnk_tc_qtab_bytes(p->N) + 255) / 256 * 256;
-        p->off_a = off;  off += (tnk_tc_table_bytes(p->tc, p->launch_rows, false) + 255) / 256 * 256;
-        p->off_b = off;  off += (tnk_tc_table_bytes(p->tc, p->N, true) + 255) / 256 * 256;
+        p->off_b = off;  off += (tnk_tc_table_bytes(p->tc, p->N) + 255) / 256 * 256;
     }
     p->total = off;
     return 0;
@@ -584,7 +583,7 @@ static int ksd_rows_impl(int n_latent, double length_scale, int precision,
     int rc = 0;
     if (p.tensor) {
         rc = tnk_tc_launch(n, prm.a, prm.gamma, prm.wl, (const float*)ST, (const float*)Cst, (const float*)qT,
-                           p.row0, p.launch_rows, p.splits, (float*)(ws + p.off_a), (float*)(ws + p.off_b), (float*)(ws + p.off_qtab), part,
+                           p.row0, p.launch_rows, p.splits, (float*)(ws + p.off_b), (float*)(ws + p.off_qtab), part,
                            g_ev_start, g_ev_stop, &launches, st);
         if (rc) return rc;
         --launches;   // the common "++launches" below counts the pair kernel

@@ -550,9 +550,8 @@ extern "C" int tnk_tc_plan(int n_latent, int* np, int* k32, int* kb, int* nsteps
     return 0;
 }
 
-size_t tnk_tc_table_bytes(const TnkTcPlan& p, int64_t states, bool is_b) {
-    return is_b ? (size_t)states * (size_t)p.kb * 16 : 0;   // the row operand is built in TMEM by the kernel
-}
+// bytes of the column operand table (the row operand is built in TMEM by the kernel)
+size_t tnk_tc_table_bytes(const TnkTcPlan& p, int64_t states) { return (size_t)states * (size_t)p.kb * 16; }
 
 size_t tnk_tc_qtab_bytes(int64_t states) { return (size_t)(states / kTile) * kQTab * sizeof(float); }
 
@@ -571,9 +570,9 @@ int launch_tiles(const TcParams& prm, dim3 grid, const float* B_tab, const float
 
 // Builds both operand tables and launches the tile kernel.  qT: packed fp32 q [>= 2^n].
 int tnk_tc_launch(int n, double a, double gamma, const double* wl, const float* ST, const float* Cst, const float* qT,
-                  int64_t row0, int64_t launch_rows, int splits, float* A_tab, float* B_tab, float* Qtab, double* part,
+                  int64_t row0, int64_t launch_rows, int splits, float* B_tab, float* Qtab, double* part,
                   cudaEvent_t ev_start, cudaEvent_t ev_stop, int* launches, cudaStream_t st) {
-    (void)a; (void)A_tab;
+    (void)a;
     TnkTcPlan p;
     TNK_REQUIRE(tnk_tc_make_plan(n, &p) == 0, "tnk_ksd_rows: no tensor-core plan for n=%d", n);
     const int64_t N = (int64_t)1 << n;

@@ -85,8 +85,8 @@ struct TnkTcPlan {
 };
 
 int tnk_tc_make_plan(int n, TnkTcPlan* p);
-size_t tnk_tc_table_bytes(const TnkTcPlan& p, int64_t states, bool is_b);
+size_t tnk_tc_table_bytes(const TnkTcPlan& p, int64_t states);
 size_t tnk_tc_qtab_bytes(int64_t states);
 int tnk_tc_launch(int n, double a, double gamma, const double* wl, const float* ST, const float* Cst, const float* qT,
-                  int64_t row0, int64_t launch_rows, int splits, float* A_tab, float* B_tab, float* Qtab, double* part,
+                  int64_t row0, int64_t launch_rows, int splits, float* B_tab, float* Qtab, double* part,
                   cudaEvent_t ev_start, cudaEvent_t ev_stop, int* launches, cudaStream_t st);

@@ -53,3 +53,29 @@ def test_training_trajectory_matches_reference(train_golden, name, precision, rt
         xc = torch.tensor([1.0]) if run["config"]["conditioning_dim"] else None
         q = vi.born_machine.get_probabilities(x_condition=xc).squeeze().double().numpy()
     assert np.max(np.abs(q - g[f"{name}_final_q"])) <= rtol
+
+
+def test_quantum_trainer_runs_config2():
+    """BASELINE.json config #2 (run_sprinkler_quantum_ksd.py): Sprinkler KSD with q from a quantum Born
+    machine; the KSD part is the GPU drop-in.  PennyLane is not installed in this image, so the q supplier
+    is the torch state-vector simulator of the same ansatz; the first epoch's loss must equal the oracle's
+    sqrt(KSD^2) for the simulator's q, the history must have the reference's keys and the loss must fall."""
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    from oracle import ksd_oracle as orc
+    from tensornetworks_b200.ksd_vi_quantum import KSDVariationalInference as QuantumKSD
+    bn = get_sprinkler_network(random_cpts=False)
+    latent, observed, x = ["C", "S", "R"], ["W"], {"W": 1}
+    posterior, _ = bn.get_true_posterior(latent, x)
+    torch.manual_seed(7)
+    vi = QuantumKSD(bn, latent, observed, qbm_num_latent_vars=3, qbm_ansatz_layers=3, pytorch_device="cpu",
+                    precision="fp64", compute_device="cuda")
+    q0 = vi.born_machine.get_probabilities().detach().double().numpy()
+    P = orc.joint_table(bn, x, latent)
+    K0, _ = orc.ksd_dense(q0, orc.score_table(P, 3), 3)
+    hist = vi.train(x, num_epochs=40, lr_born_machine=0.05, verbose=False, true_posterior_for_tvd=posterior)
+    assert sorted(hist) == ["grad_norm", "loss_ksd", "tvd"]
+    assert len(hist["loss_ksd"]) == 40 and np.all(np.isfinite(hist["loss_ksd"]))
+    assert abs(hist["loss_ksd"][0] - np.sqrt(K0)) <= 1e-9 * np.sqrt(K0)
+    assert min(hist["loss_ksd"][-5:]) < 0.8 * hist["loss_ksd"][0]
+    assert hist["tvd"][-1] < hist["tvd"][0]
