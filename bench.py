@@ -308,6 +308,26 @@ def run_ours(args):
     return locals()
 
 
+def ncu_traffic(kernel_tag, n):
+    """dram__bytes_read.sum + dram__bytes_write.sum of the dominant kernel from the committed ncu --set full
+    summary of the same kernel and size (profiles/), or None when no capture exists for this n."""
+    import glob
+    import re
+    best = None
+    for path in sorted(glob.glob(os.path.join(REPO, "profiles", f"r*_ncu_full_{kernel_tag}_n{n}_v*.txt"))):
+        text = open(path).read()
+        unit = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+        tot = 0.0
+        for key in ("dram__bytes_read.sum", "dram__bytes_write.sum"):
+            m = re.search(rf"^{re.escape(key)} = ([0-9.,]+) (\w+)", text, re.M)
+            if not m:
+                break
+            tot += float(m.group(1).replace(",", "")) * unit.get(m.group(2), 1.0)
+        else:
+            best = (tot, os.path.basename(path))
+    return best
+
+
 def load_measured_peaks():
     try:
         with open(os.path.join(REPO, "MEASURED_PEAKS.json")) as f:
@@ -367,6 +387,9 @@ def main():
                                         "bf16 rate; the kernel is timed inside a long step)" if bf16 else
                                         "half of the fallback 1.59 PFLOP/s bf16 figure of B200_PROFILING.md"),
                         "alu_epilogue_lane_ops_per_pair": 1.5}
+        traffic = ncu_traffic("tc_rows" if args.precision == "tc32" else "ksd_rows", n) if world == 1 else None
+        if traffic:
+            roofline["traffic"], roofline["traffic_source"] = traffic[0], f"profiles/{traffic[1]} (bytes per launch)"
         line = {
             "metric": METRIC, "value": r["value"], "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": r["ms_per_step"], "higher_is_better": True,
