@@ -314,7 +314,8 @@ def ncu_traffic(kernel_tag, n):
     import glob
     import re
     best = None
-    for path in sorted(glob.glob(os.path.join(REPO, "profiles", f"r*_ncu_full_{kernel_tag}_n{n}_v*.txt"))):
+    paths = glob.glob(os.path.join(REPO, "profiles", f"r*_ncu_full_{kernel_tag}_n{n}_v*.txt"))
+    for path in sorted(paths, key=lambda f: int(re.search(r"_v(\d+)\.txt$", f).group(1))):   # newest capture last
         text = open(path).read()
         unit = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
         tot = 0.0
