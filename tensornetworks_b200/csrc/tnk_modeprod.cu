@@ -7,123 +7,384 @@
 //
 //   u[z] = sum_p [ -r_p(z) W_p[z] + W_p[z^e_p] + (r_p(z) + 1) (w[z] - w[z^e_p]) ]
 //
-// i.e. n+1 transforms by K (each n butterfly stages over a 2^n vector) and one gather pass.
-// This is the same number the O(4^n) pair kernel produces (tests compare both with the oracle);
-// it is HBM/L2-bound instead of ALU-bound.  All arithmetic is fp64.
+// Because X_p K = K X_p every flipped read can be moved in front of the transform or behind it.
+// With y_p = q.*s_p + X_p q, W'_p = K y_p and Rs = n + sum_p r_p the sum regroups into
 //
-// Kernels:  mp_pack (build the n_loc+1 input vectors), mp_transform (one pass = up to 12 bits
-// of butterflies on a shared-memory tile, radix-8 in registers), mp_combine (+ block partials
-// of q.u), mp_scalar (fixed-order final sum).
+//   u = - sum_p r_p .* W'_p  +  w .* Rs  -  sum_p X_p K (q .* r_p)
+//
+// and the last term is taken per bit on whichever side is local:
+//   "pre"  bits (below the last pass): folded into extra input vectors Y = -sum_pre X_p (q.*r_p),
+//          u += K Y;
+//   "post" bits (rows of the last pass tile): K(q.*r_p) = w - W'_p + X_p w, so
+//          u[z] += W'_p[z^e_p] - w[z^e_p] - w[z], both flipped elements being in the tile that is
+//          in shared memory at that moment.
+//
+// So the evaluation is n_loc + 1 + (#Y chunks) transforms by K and no gather pass: the first
+// pass builds its input on the fly from q and the column-major score table (never materialised),
+// the last pass folds every transformed vector into u while its tile is still in shared memory.
+// HBM traffic per evaluation (fp64, 2 passes): read S twice, write + read the V vectors once.
+// All arithmetic is fp64.
+//
+// Kernels:  mp_tables (one-off: column-major copy of the score table + row sums of r),
+// mp_first (build input tile, butterflies on the low bits, write V), mp_transform (middle passes,
+// only for n > 24), mp_last (butterflies on the high bits, fold into u, block partials of q.u),
+// mp_scalar (fixed-order final sum).
 #include "tnk_common.cuh"
 
 namespace {
 
-constexpr int kMpThreads = 256;
-constexpr int kTileLog = 12;               // elements per shared-memory tile (2^12 doubles + padding)
-constexpr int kMinLogW = 3;                // strided passes keep >= 8 contiguous doubles (64 B) per row
+constexpr int kMpThreads = 512;
+constexpr int kTileLog = 13;               // elements per shared-memory tile (2^13 doubles)
+constexpr int kMinLogW = 2;                // strided passes keep >= 4 contiguous doubles (one 32 B sector) per row
+constexpr int kMpPerThread = (1 << kTileLog) / kMpThreads;
+constexpr size_t kMpSmem = (size_t)(1 << kTileLog) * sizeof(double);
 
-__device__ __forceinline__ int pad_idx(int e) { return e + (e >> 3); }  // 1 pad per 8: conflict-free strides
+// Shared-memory swizzle of a tile index (8-byte elements, 16 per bank row): XOR-linear, so
+// swz(a | b) = swz(a) ^ swz(b) for disjoint bit fields.  Bits 4..6 are folded into bits 0..3 so that
+// the 16 lanes of a half-warp, which differ in the four lowest index bits outside the radix field
+// of the round ({0,1,2,3}, {0,1,2,6}, {0,1,5,6}, {0,4,5,6} or {3,4,5,6}), always hit 16 different
+// bank pairs - as do plain consecutive accesses.
+__device__ __forceinline__ int swz(int idx) { return idx ^ (((idx >> 4) & 7) << 1) ^ ((idx >> 6) & 1); }
 
-// ---- MP1: V[lv][z] = q[z] * s_p(z) for p = p0 + lv (lv < n_loc); V[n_loc][z] = q[z]
-template <typename Q>
-__global__ void __launch_bounds__(kMpThreads)
-mp_pack_kernel(int np, int64_t N, int p0, int n_loc, const Q* __restrict__ q,
-               const double* __restrict__ ST, double* __restrict__ V) {
-    const int64_t z = (int64_t)blockIdx.x * kMpThreads + threadIdx.x;
-    if (z >= N) return;
-    const double qz = (double)q[z];
-    const double* s = ST + z * np + p0;
-    for (int lv = 0; lv < n_loc; ++lv) V[(int64_t)lv * N + z] = qz * s[lv];
-    V[(int64_t)n_loc * N + z] = qz;
+// In-register butterflies of 2^RB values: x[j] <-> x[j ^ (1<<b)] for every bit b of j.
+template <int RB>
+__device__ __forceinline__ void reg_butterflies(double (&x)[1 << RB], double a) {
+#pragma unroll
+    for (int b = 0; b < RB; ++b) {
+#pragma unroll
+        for (int j = 0; j < (1 << RB); ++j) {
+            if (!(j & (1 << b))) {
+                const double lo = x[j], hi = x[j | (1 << b)];
+                x[j] = fma(a, hi, lo);
+                x[j | (1 << b)] = fma(a, lo, hi);
+            }
+        }
+    }
 }
 
-// ---- MP2: butterflies for bits [b0, b0+g) on tiles of 2^g rows x 2^logW contiguous elements.
-// Element (m, w) of tile (hi, lob) sits at  hi << (b0+g) | m << b0 | lob << logW | w.
-// b0 == 0 requires logW == 0 (the tile is one contiguous run).
-__global__ void __launch_bounds__(kMpThreads)
+// One round: butterflies of tile index bits [sh, sh + RB) of a 2^total_log element tile held in
+// swizzled shared memory, radix 2^RB in registers.  Ends with __syncthreads().
+template <int RB>
+__device__ __forceinline__ void smem_round(double* tile, int sh, int total_log, double a) {
+    constexpr int CNT = 1 << RB;
+    int cj[CNT];
+#pragma unroll
+    for (int j = 0; j < CNT; ++j) cj[j] = swz(j << sh);
+    const int units = 1 << (total_log - RB);
+    const int lowmask = (1 << sh) - 1;
+    for (int uidx = threadIdx.x; uidx < units; uidx += kMpThreads) {
+        const int pb = swz(((uidx & ~lowmask) << RB) | (uidx & lowmask));
+        double x[CNT];
+#pragma unroll
+        for (int j = 0; j < CNT; ++j) x[j] = tile[pb ^ cj[j]];
+        reg_butterflies<RB>(x, a);
+#pragma unroll
+        for (int j = 0; j < CNT; ++j) tile[pb ^ cj[j]] = x[j];
+    }
+    __syncthreads();
+}
+
+// Butterflies of tile index bits [sh0, sh0 + nbits), in rounds of at most 3 bits.
+__device__ __forceinline__ void tile_butterflies(double* tile, int sh0, int nbits, int total_log, double a) {
+    int k0 = 0;
+    while (nbits - k0 >= 3 && nbits - k0 != 4) { smem_round<3>(tile, sh0 + k0, total_log, a); k0 += 3; }
+    while (nbits - k0 >= 2) { smem_round<2>(tile, sh0 + k0, total_log, a); k0 += 2; }
+    if (nbits - k0 == 1) smem_round<1>(tile, sh0 + k0, total_log, a);
+}
+
+// Address of state z in the layout the last pass reads.  Two-pass plans (13 < n <= 24) store V, the
+// second score copy and r_sum "blocked": [z bits logW..12][z bits 13..n-1][z bits 0..logW-1], so that a
+// last-pass tile (2^g rows x 2^logW states) is one contiguous 64 KB run instead of 2^g runs of
+// 2^logW doubles 64 KB apart.  Other plans keep the natural order.
+__device__ __forceinline__ int64_t last_layout(int64_t z, int blocked, int logW) {
+    if (!blocked) return z;
+    const int64_t zl = z & ((1 << kTileLog) - 1), zh = z >> kTileLog;
+    return ((zl >> logW) << kTileLog) | (zh << logW) | (zl & ((1 << logW) - 1));
+}
+
+// ---- MP0 (one-off per table): S[lv][z] = s_p(z) for p = p0 + lv, the same in the last-pass layout
+// (S2), and Rs[last_layout(z)] = n_loc + sum_lv (1 - s_p(z))
+__global__ void __launch_bounds__(256)
+mp_tables_kernel(int np, int64_t N, int p0, int n_loc, int blocked, int logW, const double* __restrict__ ST,
+                 double* __restrict__ S, double* __restrict__ S2, double* __restrict__ Rs) {
+    const int64_t z = (int64_t)blockIdx.x * 256 + threadIdx.x;
+    if (z >= N) return;
+    const int64_t zb = last_layout(z, blocked, logW);
+    const double* s = ST + z * np + p0;
+    double rs = (double)n_loc;
+    for (int lv = 0; lv < n_loc; ++lv) {
+        const double v = s[lv];
+        S[(int64_t)lv * N + z] = v;
+        S2[(int64_t)lv * N + zb] = v;
+        rs += 1.0 - v;
+    }
+    Rs[zb] = rs;
+}
+
+// ---- MP1: first pass.  blockIdx.x = tile of 2^T contiguous states, blockIdx.y = input vector:
+//   y <  nchunk            Y_c[z] = -sum_{lv in chunk c, pre} q[z^e_p] r_p(z^e_p)      -> V slot n_loc+1+c
+//   y <  nchunk + n_loc    y_p[z] = q[z] s_p(z) + q[z^e_p],  p = p0 + (y - nchunk)      -> V slot lv
+//   y == nchunk + n_loc    q itself                                                    -> V slot n_loc
+// then the butterflies of bits [0,T) and the store.  (The heavy Y tiles are scheduled first.)
+template <typename Q>
+__global__ void __launch_bounds__(kMpThreads, 2)
+mp_first_kernel(int T, int64_t N, int p0, int n_loc, int pre_cnt, int chunk, int nchunk, int blocked, int logW, int group_log,
+                const Q* __restrict__ q, const double* __restrict__ S, double* __restrict__ V, double a) {
+    extern __shared__ double tile[];
+    const int tile_elems = 1 << T;
+    // block order: [tile group][vector][tile in group] - neighbouring tiles of one vector run together
+    // (their blocked stores fill whole lines in L2) and all vectors of a tile group reuse its q from L2
+    const int nvec = n_loc + 1 + nchunk;
+    const int64_t bid = blockIdx.x;
+    const int64_t tg = bid / ((int64_t)nvec << group_log);
+    const int rest = (int)(bid - tg * ((int64_t)nvec << group_log));
+    const int y = rest >> group_log;
+    const int64_t tile_id = (tg << group_log) | (rest & ((1 << group_log) - 1));
+    const int64_t z0 = tile_id << T;
+    const Q* qz = q + z0;
+    int slot, lv0 = 0, lv1 = 0;
+    if (y < nchunk) {
+        slot = n_loc + 1 + y;
+        lv0 = y * chunk;
+        lv1 = (lv0 + chunk < pre_cnt) ? lv0 + chunk : pre_cnt;
+    } else {
+        slot = y - nchunk;           // < n_loc: component lv = slot;  == n_loc: q itself
+    }
+    // input element e of this tile: flipped partners inside the tile are addressed by e ^ fl,
+    // partners in another tile by the same e from a shifted base
+    auto partner = [&](int p, int64_t& zb, int& fl) {
+        if (p < T) { zb = z0; fl = 1 << p; } else { zb = z0 ^ ((int64_t)1 << p); fl = 0; }
+    };
+
+    if (T == kTileLog) {
+        // bits 10..12 in registers straight from global memory (8 loads 8 KB apart per thread)
+#pragma unroll 1
+        for (int h = 0; h < 2; ++h) {
+            const int w = threadIdx.x + h * kMpThreads;
+            double x[8];
+            if (y < nchunk) {
+#pragma unroll
+                for (int j = 0; j < 8; ++j) x[j] = 0.0;
+                for (int lv = lv0; lv < lv1; ++lv) {
+                    int64_t zb; int fl;
+                    partner(p0 + lv, zb, fl);
+                    const Q* qf = q + zb;
+                    const double* Sf = S + (int64_t)lv * N + zb;
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) {
+                        const int ef = (w + (j << 10)) ^ fl;
+                        x[j] = fma(-(double)qf[ef], 1.0 - Sf[ef], x[j]);
+                    }
+                }
+            } else if (slot < n_loc) {
+                int64_t zb; int fl;
+                partner(p0 + slot, zb, fl);
+                const Q* qf = q + zb;
+                const double* Sp = S + (int64_t)slot * N + z0;
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    const int e = w + (j << 10);
+                    x[j] = fma((double)qz[e], Sp[e], (double)qf[e ^ fl]);
+                }
+            } else {
+#pragma unroll
+                for (int j = 0; j < 8; ++j) x[j] = (double)qz[w + (j << 10)];
+            }
+            reg_butterflies<3>(x, a);
+            const int pw = swz(w);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) tile[pw + (j << 10)] = x[j];
+        }
+        __syncthreads();
+        smem_round<3>(tile, 0, kTileLog, a);
+        smem_round<3>(tile, 3, kTileLog, a);
+        // bits 6..9 radix-16, straight to global memory (a warp stores 32 consecutive states per value)
+        const int base = ((threadIdx.x >> 6) << 10) | (threadIdx.x & 63);
+        const int pb = swz(base);
+        double x[16];
+#pragma unroll
+        for (int jj = 0; jj < 16; ++jj) x[jj] = tile[pb ^ ((jj << 6) ^ ((jj & 1) ? 9 : 0))];
+        reg_butterflies<4>(x, a);
+        double* out = V + (int64_t)slot * N;
+        if (blocked) {
+            out += tile_id << logW;
+            const int W = 1 << logW;
+#pragma unroll
+            for (int jj = 0; jj < 16; ++jj) {
+                const int e = base | (jj << 6);
+                out[((int64_t)(e >> logW) << kTileLog) | (e & (W - 1))] = x[jj];
+            }
+        } else {
+            out += z0;
+#pragma unroll
+            for (int jj = 0; jj < 16; ++jj) out[base | (jj << 6)] = x[jj];
+        }
+        return;
+    }
+
+    // n < 13: a single small tile, everything through shared memory
+    for (int e = threadIdx.x; e < tile_elems; e += kMpThreads) {
+        double val;
+        if (y < nchunk) {
+            val = 0.0;
+            for (int lv = lv0; lv < lv1; ++lv) {
+                int64_t zb; int fl;
+                partner(p0 + lv, zb, fl);
+                val = fma(-(double)q[zb + (e ^ fl)], 1.0 - S[(int64_t)lv * N + zb + (e ^ fl)], val);
+            }
+        } else if (slot < n_loc) {
+            int64_t zb; int fl;
+            partner(p0 + slot, zb, fl);
+            val = fma((double)qz[e], S[(int64_t)slot * N + z0 + e], (double)q[zb + (e ^ fl)]);
+        } else {
+            val = (double)qz[e];
+        }
+        tile[swz(e)] = val;
+    }
+    __syncthreads();
+    tile_butterflies(tile, 0, T, T, a);
+    double* out = V + (int64_t)slot * N + z0;      // never blocked: one pass only
+    for (int e = threadIdx.x; e < tile_elems; e += kMpThreads) out[e] = tile[swz(e)];
+}
+
+// ---- MP2: middle pass (n > kTileLog + 11 only): butterflies for bits [b0, b0+g) on tiles of
+// 2^g rows x 2^logW contiguous elements, in place.
+__global__ void __launch_bounds__(kMpThreads, 2)
 mp_transform_kernel(double* __restrict__ V, int64_t N, int b0, int g, int logW, double a) {
     extern __shared__ double tile[];
     const int tile_elems = 1 << (g + logW);
     const int W = 1 << logW;
-    const int64_t nlob = (b0 > logW) ? ((int64_t)1 << (b0 - logW)) : 1;
+    const int64_t nlob = (int64_t)1 << (b0 - logW);
     const int64_t t = blockIdx.x;
     const int64_t lob = t % nlob, hi = t / nlob;
     double* vec = V + (int64_t)blockIdx.y * N + ((hi << (b0 + g)) | (lob << logW));
-
     for (int e = threadIdx.x; e < tile_elems; e += kMpThreads) {
         const int m = e >> logW, w = e & (W - 1);
-        tile[pad_idx(e)] = vec[((int64_t)m << b0) + w];
+        tile[swz(e)] = vec[((int64_t)m << b0) + w];
     }
     __syncthreads();
-
-    for (int k0 = 0; k0 < g; k0 += 3) {
-        const int rb = (g - k0 < 3) ? (g - k0) : 3;      // bits handled in registers this round
-        const int cnt = 1 << rb;
-        const int units = tile_elems >> rb;
-        for (int uidx = threadIdx.x; uidx < units; uidx += kMpThreads) {
-            const int w = uidx & (W - 1), mm = uidx >> logW;
-            const int mlow = mm & ((1 << k0) - 1), mhigh = mm >> k0;
-            const int mbase = (mhigh << (k0 + rb)) | mlow;
-            double x[8];
-#pragma unroll
-            for (int j = 0; j < 8; ++j)
-                if (j < cnt) x[j] = tile[pad_idx(((mbase | (j << k0)) << logW) + w)];
-#pragma unroll
-            for (int b = 0; b < 3; ++b) {
-                if (b < rb) {
-#pragma unroll
-                    for (int j = 0; j < 8; ++j) {
-                        if (!(j & (1 << b)) && (j | (1 << b)) < cnt) {
-                            const double lo = x[j], hi2 = x[j | (1 << b)];
-                            x[j] = fma(a, hi2, lo);
-                            x[j | (1 << b)] = fma(a, lo, hi2);
-                        }
-                    }
-                }
-            }
-#pragma unroll
-            for (int j = 0; j < 8; ++j)
-                if (j < cnt) tile[pad_idx(((mbase | (j << k0)) << logW) + w)] = x[j];
-        }
-        __syncthreads();
-    }
-
+    tile_butterflies(tile, logW, g, g + logW, a);
     for (int e = threadIdx.x; e < tile_elems; e += kMpThreads) {
         const int m = e >> logW, w = e & (W - 1);
-        vec[((int64_t)m << b0) + w] = tile[pad_idx(e)];
+        vec[((int64_t)m << b0) + w] = tile[swz(e)];
     }
 }
 
-// ---- MP3: u[z] = sum_p [ -r_p W_p[z] + W_p[z^e_p] + (r_p + 1)(w[z] - w[z^e_p]) ],  block partials of q.u
-template <typename Q>
-__global__ void __launch_bounds__(kMpThreads)
-mp_combine_kernel(int np, int64_t N, int p0, int n_loc, const Q* __restrict__ q,
-                  const double* __restrict__ ST, const double* __restrict__ V,
-                  double* __restrict__ u, double* __restrict__ blockpart) {
-    __shared__ double red[kMpThreads];
-    const int64_t z = (int64_t)blockIdx.x * kMpThreads + threadIdx.x;
-    double contrib = 0.0;
-    if (z < N) {
-        const double* s = ST + z * np + p0;
-        const double* wq = V + (int64_t)n_loc * N;
-        const double wz = wq[z];
-        double acc = 0.0;
-        for (int lv = 0; lv < n_loc; ++lv) {
-            const int64_t zf = z ^ ((int64_t)1 << (p0 + lv));
-            const double* Wp = V + (int64_t)lv * N;
-            const double r = 1.0 - s[lv];
-            acc += fma(-r, Wp[z], Wp[zf]) + (r + 1.0) * (wz - wq[zf]);
+// ---- MP3: last pass.  One CTA per tile of 2^g rows (bits [b0,b0+g)) x 2^logW contiguous states;
+// it walks over all V vectors, finishes their butterflies in shared memory and folds each into
+// the u values its threads own (element e = tid + 512 k).  g == 0: nothing left to transform
+// (n <= kTileLog), the tile is a contiguous run and every bit is "pre".
+// FAST: the two-pass case with a full tile (blocked layout, g >= 3), specialised at compile time.
+template <typename Q, bool FAST>
+__global__ void __launch_bounds__(kMpThreads, 2)
+mp_last_kernel(int64_t N, int b0, int g, int logW, int p0, int n_loc, int nchunk, int flip_split, int blocked_arg,
+               const Q* __restrict__ q, const double* __restrict__ S, const double* __restrict__ Rs,
+               const double* __restrict__ V, double* __restrict__ u, double* __restrict__ blockpart, double a) {
+    extern __shared__ double tile[];
+    __shared__ double red[kMpThreads / 32];
+    const bool blocked = FAST || blocked_arg;
+    const int tile_elems = FAST ? (1 << kTileLog) : (1 << (g + logW));
+    const int W = 1 << logW;
+    const int64_t nlob = (int64_t)1 << (b0 - logW);
+    const int64_t t = blockIdx.x;
+    const int64_t base = ((t / nlob) << (b0 + g)) | ((t % nlob) << logW);
+    auto off = [&](int e) -> int64_t { return ((int64_t)(e >> logW) << b0) + (e & (W - 1)); };   // natural order
+    // V, S and Rs in the last-pass layout: a contiguous tile when blocked
+    const int64_t lbase = blocked ? (t << kTileLog) : base;
+    auto loff = [&](int e) -> int64_t { return blocked ? (int64_t)e : off(e); };
+    auto live = [&](int e) -> bool { return FAST || e < tile_elems; };
+    const int post0 = (flip_split > p0) ? flip_split - p0 : 0;       // local components >= post0 are "post"
+    const int n_post = (n_loc > post0) ? n_loc - post0 : 0;
+
+    double acc[kMpPerThread];
+#pragma unroll
+    for (int k = 0; k < kMpPerThread; ++k) acc[k] = 0.0;
+
+    const bool fused = FAST || ((g + logW == kTileLog) && g >= 3);   // full tile: top three row bits go through registers
+    const int64_t jstride = blocked ? 1024 : ((int64_t)(1024 >> logW) << b0);   // +1024 tile elements in V
+    const int ptid = swz(threadIdx.x);                     // swz(tid + 512 k) = ptid + 512 k
+    const int nvec = n_loc + 1 + nchunk;
+    for (int v = 0; v < nvec; ++v) {
+        const double* vec = V + (int64_t)v * N + lbase;
+        if (fused) {
+#pragma unroll 1
+            for (int h = 0; h < 2; ++h) {
+                const int w = threadIdx.x + h * kMpThreads;
+                const double* src = vec + loff(w);
+                double x[8];
+#pragma unroll
+                for (int j = 0; j < 8; ++j) x[j] = src[j * jstride];
+                reg_butterflies<3>(x, a);
+                const int pw = swz(w);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) tile[pw + (j << 10)] = x[j];
+            }
+            __syncthreads();
+            tile_butterflies(tile, logW, g - 3, kTileLog, a);
+        } else {
+#pragma unroll
+            for (int k = 0; k < kMpPerThread; ++k) {
+                const int e = threadIdx.x + k * kMpThreads;
+                if (live(e)) tile[ptid + k * kMpThreads] = vec[loff(e)];
+            }
+            __syncthreads();
+            tile_butterflies(tile, logW, g, g + logW, a);
         }
-        u[z] = acc;
-        contrib = (double)q[z] * acc;
-    }
-    red[threadIdx.x] = contrib;
-    __syncthreads();
-    for (int off = kMpThreads / 2; off > 0; off >>= 1) {
-        if (threadIdx.x < off) red[threadIdx.x] += red[threadIdx.x + off];
+        if (v < n_loc) {
+            const double* Sp = S + (int64_t)v * N + lbase;
+            const int fb = (v >= post0) ? swz(1 << (p0 + v - b0 + logW)) : 0;
+#pragma unroll
+            for (int k = 0; k < kMpPerThread; ++k) {
+                const int e = threadIdx.x + k * kMpThreads;
+                if (live(e)) {
+                    const int pe = ptid + k * kMpThreads;
+                    const double r = 1.0 - Sp[loff(e)];
+                    double x = fma(-r, tile[pe], acc[k]);
+                    if (fb) x += tile[pe ^ fb];
+                    acc[k] = x;
+                }
+            }
+        } else if (v == n_loc) {
+#pragma unroll
+            for (int k = 0; k < kMpPerThread; ++k) {
+                const int e = threadIdx.x + k * kMpThreads;
+                if (live(e)) {
+                    const int pe = ptid + k * kMpThreads;
+                    double x = tile[pe] * (Rs[lbase + loff(e)] - (double)n_post);
+                    for (int lv = post0; lv < n_loc; ++lv) x -= tile[pe ^ swz(1 << (p0 + lv - b0 + logW))];
+                    acc[k] += x;
+                }
+            }
+        } else {
+#pragma unroll
+            for (int k = 0; k < kMpPerThread; ++k) {
+                const int e = threadIdx.x + k * kMpThreads;
+                if (live(e)) acc[k] += tile[ptid + k * kMpThreads];
+            }
+        }
         __syncthreads();
     }
-    if (threadIdx.x == 0) blockpart[blockIdx.x] = red[0];
+
+    double contrib = 0.0;
+#pragma unroll
+    for (int k = 0; k < kMpPerThread; ++k) {
+        const int e = threadIdx.x + k * kMpThreads;
+        if (live(e)) {
+            const int64_t z = base + off(e);
+            u[z] = acc[k];
+            contrib = fma((double)q[z], acc[k], contrib);
+        }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) contrib += __shfl_xor_sync(0xffffffffu, contrib, o);
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = contrib;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double s = 0.0;
+#pragma unroll
+        for (int w2 = 0; w2 < kMpThreads / 32; ++w2) s += red[w2];
+        blockpart[blockIdx.x] = s;
+    }
 }
 
 __global__ void __launch_bounds__(256)
@@ -133,16 +394,19 @@ mp_scalar_kernel(const double* __restrict__ blockpart, int64_t nblocks, double* 
     for (int64_t b = threadIdx.x; b < nblocks; b += 256) acc += blockpart[b];
     red[threadIdx.x] = acc;
     __syncthreads();
-    for (int off = 128; off > 0; off >>= 1) {
-        if (threadIdx.x < off) red[threadIdx.x] += red[threadIdx.x + off];
+    for (int o = 128; o > 0; o >>= 1) {
+        if (threadIdx.x < o) red[threadIdx.x] += red[threadIdx.x + o];
         __syncthreads();
     }
     if (threadIdx.x == 0) out[0] = red[0];
 }
 
+struct MpPass { int b0, g, logW; };
+
 struct MpPlan {
-    int64_t N, blocks;
-    int n_loc;
+    int64_t N, tiles_first, tiles_last;
+    int n_loc, T, n_mid, pre_cnt, chunk, nchunk, nvec, flip_split, blocked, group_log;
+    MpPass mid[4], last;
     size_t off_v, off_block, total;
 };
 
@@ -150,10 +414,43 @@ int mp_plan(int n, int p_begin, int p_end, MpPlan* p) {
     if (n < 0 || n > TNK_MAX_LATENT || p_begin < 0 || p_end > n || p_begin > p_end) return 1;
     p->N = (int64_t)1 << n;
     p->n_loc = p_end - p_begin;
-    p->blocks = (p->N + kMpThreads - 1) / kMpThreads;
+    p->T = n < kTileLog ? n : kTileLog;
+    p->tiles_first = p->N >> p->T;
+    p->n_mid = 0;
+    const int rem = n - p->T;
+    if (rem == 0) {
+        p->last = MpPass{n, 0, n};
+        p->flip_split = n;
+    } else {
+        const int gmax = kTileLog - kMinLogW;
+        const int passes = (rem + gmax - 1) / gmax;
+        if (passes - 1 > 4) return 1;
+        int b0 = p->T, left = rem;
+        for (int ps = 0; ps < passes; ++ps) {
+            const int g = (left + (passes - ps) - 1) / (passes - ps);
+            int logW = kTileLog - g;
+            if (logW > b0) logW = b0;
+            const MpPass pass{b0, g, logW};
+            if (ps + 1 < passes) p->mid[p->n_mid++] = pass; else p->last = pass;
+            b0 += g;
+            left -= g;
+        }
+        p->flip_split = p->last.b0;
+    }
+    p->tiles_last = p->N >> (p->last.g + p->last.logW);
+    p->blocked = (rem > 0 && p->n_mid == 0) ? 1 : 0;        // two passes: V and the second score copy are blocked
+    p->group_log = 0;
+    while (p->group_log < 3 && ((int64_t)2 << p->group_log) <= p->tiles_first) ++p->group_log;
+    int pre = p->flip_split - p_begin;
+    if (pre < 0) pre = 0;
+    if (pre > p->n_loc) pre = p->n_loc;
+    p->pre_cnt = pre;
+    p->chunk = (p->tiles_first >= 1024 || pre <= 4) ? (pre > 0 ? pre : 1) : 4;   // few tiles: spread the Y work over more CTAs
+    p->nchunk = (pre + p->chunk - 1) / p->chunk;
+    p->nvec = p->n_loc + 1 + p->nchunk;
     size_t off = 0;
-    p->off_v = off;     off += ((size_t)(p->n_loc + 1) * p->N * sizeof(double) + 255) / 256 * 256;
-    p->off_block = off; off += ((size_t)(p->blocks + 1) * sizeof(double) + 255) / 256 * 256;
+    p->off_v = off;     off += ((size_t)p->nvec * p->N * sizeof(double) + 255) / 256 * 256;
+    p->off_block = off; off += ((size_t)(p->tiles_last + 1) * sizeof(double) + 255) / 256 * 256;
     p->total = off;
     return 0;
 }
@@ -166,14 +463,29 @@ extern "C" size_t tnk_ksd_modeproduct_workspace_bytes(int n_latent, int bit_begi
     return p.total;
 }
 
+extern "C" int tnk_modeproduct_tables(int n_latent, const double* ST64, int bit_begin, int bit_end,
+                                      double* S_cols, double* r_sum, void* stream) {
+    MpPlan p;
+    TNK_REQUIRE(mp_plan(n_latent, bit_begin, bit_end, &p) == 0, "tnk_modeproduct_tables: bad arguments n=%d bits=[%d,%d)",
+                n_latent, bit_begin, bit_end);
+    TNK_REQUIRE(ST64 && S_cols && r_sum, "tnk_modeproduct_tables: NULL pointer argument");
+    TnkGeom geo;
+    TNK_REQUIRE(tnk_geom(n_latent, TNK_PREC_FP64, &geo) == 0, "tnk_modeproduct_tables: unsupported n=%d", n_latent);
+    const unsigned blocks = (unsigned)((p.N + 255) / 256);
+    mp_tables_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(geo.np, p.N, bit_begin, p.n_loc, p.blocked, p.last.logW, ST64,
+                                                               S_cols, S_cols + (size_t)p.n_loc * p.N, r_sum);
+    TNK_CUDA_OK(cudaGetLastError());
+    return 0;
+}
+
 extern "C" int tnk_ksd_modeproduct(int n_latent, double length_scale, const void* q, int q_dtype,
-                                   const double* ST64, int bit_begin, int bit_end,
+                                   const double* S_cols, const double* r_sum, int bit_begin, int bit_end,
                                    double* u, double* ksd_part,
                                    void* workspace, size_t workspace_bytes, int* n_launch, void* stream) {
     MpPlan p;
     TNK_REQUIRE(mp_plan(n_latent, bit_begin, bit_end, &p) == 0, "tnk_ksd_modeproduct: bad arguments n=%d bits=[%d,%d)",
                 n_latent, bit_begin, bit_end);
-    TNK_REQUIRE(q && ST64 && u && ksd_part && workspace, "tnk_ksd_modeproduct: NULL pointer argument");
+    TNK_REQUIRE(q && S_cols && r_sum && u && ksd_part && workspace, "tnk_ksd_modeproduct: NULL pointer argument");
     TNK_REQUIRE(q_dtype == 0 || q_dtype == 1, "tnk_ksd_modeproduct: q_dtype must be 0 (double) or 1 (float)");
     TNK_REQUIRE(workspace_bytes >= p.total, "tnk_ksd_modeproduct: workspace %zu < required %zu", workspace_bytes, p.total);
     TNK_REQUIRE(((uintptr_t)workspace & 255) == 0, "tnk_ksd_modeproduct: workspace must be 256-byte aligned");
@@ -187,56 +499,60 @@ extern "C" int tnk_ksd_modeproduct(int n_latent, double length_scale, const void
         return 0;
     }
     TNK_REQUIRE((double)n * length_scale != 0.0, "tnk_ksd_modeproduct: num_vars*length_scale must be non-zero");
-    TnkGeom geo;
-    TNK_REQUIRE(tnk_geom(n, TNK_PREC_FP64, &geo) == 0, "tnk_ksd_modeproduct: unsupported n=%d", n);
     const double a = exp(-1.0 / ((double)n * length_scale));
     unsigned char* ws = (unsigned char*)workspace;
     double* V = (double*)(ws + p.off_v);
     double* blockpart = (double*)(ws + p.off_block);
-    const unsigned blocks = (unsigned)p.blocks;
-    const int nvec = p.n_loc + 1;
 
-    if (q_dtype == 0) mp_pack_kernel<double><<<blocks, kMpThreads, 0, st>>>(geo.np, p.N, bit_begin, p.n_loc, (const double*)q, ST64, V);
-    else mp_pack_kernel<float><<<blocks, kMpThreads, 0, st>>>(geo.np, p.N, bit_begin, p.n_loc, (const float*)q, ST64, V);
-    TNK_CUDA_OK(cudaGetLastError());
-    ++launches;
+    static bool attr_set = false;
+    if (!attr_set) {
+        TNK_CUDA_OK(cudaFuncSetAttribute(mp_first_kernel<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMpSmem));
+        TNK_CUDA_OK(cudaFuncSetAttribute(mp_first_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMpSmem));
+        TNK_CUDA_OK(cudaFuncSetAttribute(mp_last_kernel<double, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMpSmem));
+        TNK_CUDA_OK(cudaFuncSetAttribute(mp_last_kernel<float, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMpSmem));
+        TNK_CUDA_OK(cudaFuncSetAttribute(mp_last_kernel<double, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMpSmem));
+        TNK_CUDA_OK(cudaFuncSetAttribute(mp_last_kernel<float, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMpSmem));
+        TNK_CUDA_OK(cudaFuncSetAttribute(mp_transform_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMpSmem));
+        attr_set = true;
+    }
 
-    // pass plan: one contiguous pass of min(n,12) bits, then strided passes of <= 9 bits each
-    const size_t smem = ((size_t)(1 << kTileLog) * 9 / 8 + 8) * sizeof(double);
-    TNK_CUDA_OK(cudaFuncSetAttribute(mp_transform_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    int b0 = 0;
     {
-        const int g = n < kTileLog ? n : kTileLog;
-        dim3 grid((unsigned)(p.N >> g), (unsigned)nvec, 1);
-        mp_transform_kernel<<<grid, kMpThreads, smem, st>>>(V, p.N, 0, g, 0, a);
+        const unsigned grid = (unsigned)(p.tiles_first * p.nvec);
+        if (q_dtype == 0)
+            mp_first_kernel<double><<<grid, kMpThreads, kMpSmem, st>>>(p.T, p.N, bit_begin, p.n_loc, p.pre_cnt, p.chunk, p.nchunk,
+                                                                     p.blocked, p.last.logW, p.group_log,
+                                                                     (const double*)q, S_cols, V, a);
+        else
+            mp_first_kernel<float><<<grid, kMpThreads, kMpSmem, st>>>(p.T, p.N, bit_begin, p.n_loc, p.pre_cnt, p.chunk, p.nchunk,
+                                                                    p.blocked, p.last.logW, p.group_log,
+                                                                    (const float*)q, S_cols, V, a);
         TNK_CUDA_OK(cudaGetLastError());
         ++launches;
-        b0 = g;
     }
-    const int rem = n - b0;
-    if (rem > 0) {
-        const int gmax = kTileLog - kMinLogW;
-        const int passes = (rem + gmax - 1) / gmax;
-        int left = rem;
-        for (int ps = 0; ps < passes; ++ps) {
-            const int g = (left + (passes - ps) - 1) / (passes - ps);
-            int logW = kTileLog - g;
-            if (logW > b0) logW = b0;
-            dim3 grid((unsigned)(p.N >> (g + logW)), (unsigned)nvec, 1);
-            mp_transform_kernel<<<grid, kMpThreads, smem, st>>>(V, p.N, b0, g, logW, a);
-            TNK_CUDA_OK(cudaGetLastError());
-            ++launches;
-            b0 += g;
-            left -= g;
-        }
+    for (int m = 0; m < p.n_mid; ++m) {
+        const MpPass& ps = p.mid[m];
+        dim3 grid((unsigned)(p.N >> (ps.g + ps.logW)), (unsigned)p.nvec, 1);
+        mp_transform_kernel<<<grid, kMpThreads, kMpSmem, st>>>(V, p.N, ps.b0, ps.g, ps.logW, a);
+        TNK_CUDA_OK(cudaGetLastError());
+        ++launches;
     }
-
-    if (q_dtype == 0) mp_combine_kernel<double><<<blocks, kMpThreads, 0, st>>>(geo.np, p.N, bit_begin, p.n_loc, (const double*)q, ST64, V, u, blockpart);
-    else mp_combine_kernel<float><<<blocks, kMpThreads, 0, st>>>(geo.np, p.N, bit_begin, p.n_loc, (const float*)q, ST64, V, u, blockpart);
-    TNK_CUDA_OK(cudaGetLastError());
-    mp_scalar_kernel<<<1, 256, 0, st>>>(blockpart, p.blocks, ksd_part);
-    TNK_CUDA_OK(cudaGetLastError());
-    launches += 2;
+    {
+        const MpPass& ps = p.last;
+        const double* S2 = S_cols + (size_t)p.n_loc * p.N;       // the copy in the last-pass layout
+        const bool fast = p.blocked && ps.g >= 3;
+        const unsigned grid = (unsigned)p.tiles_last;
+#define TNK_MP_LAST(QT, FAST)                                                                          \
+        mp_last_kernel<QT, FAST><<<grid, kMpThreads, kMpSmem, st>>>(                                       \
+            p.N, ps.b0, ps.g, ps.logW, bit_begin, p.n_loc, p.nchunk, p.flip_split, p.blocked,              \
+            (const QT*)q, S2, r_sum, V, u, blockpart, a)
+        if (q_dtype == 0) { if (fast) TNK_MP_LAST(double, true); else TNK_MP_LAST(double, false); }
+        else              { if (fast) TNK_MP_LAST(float, true);  else TNK_MP_LAST(float, false); }
+#undef TNK_MP_LAST
+        TNK_CUDA_OK(cudaGetLastError());
+        mp_scalar_kernel<<<1, 256, 0, st>>>(blockpart, p.tiles_last, ksd_part);
+        TNK_CUDA_OK(cudaGetLastError());
+        launches += 2;
+    }
     if (n_launch) *n_launch = launches;
     return 0;
 }

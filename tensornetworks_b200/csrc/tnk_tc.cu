@@ -433,8 +433,21 @@ tc_rows_kernel(const __grid_constant__ TcParams prm, const float* __restrict__ B
             for (int b = 0; b < 3; ++b) v += ((g >> b) & 1) ? gp[4 + b] : 0.f;
             Gmid[gl] = v;
         }
-        const uint32_t imid = ((uint32_t)i >> 4) & 7u;
+        int pmid[4];                                       // Hamming distance on column bits 4..6
+#pragma unroll
+        for (int gl = 0; gl < 4; ++gl) pmid[gl] = __popc((((uint32_t)i >> 4) & 7u) ^ (uint32_t)(half * 4 + gl));
         const uint32_t ihi = (uint32_t)(i >> 7);
+        // Stepping to the next column tile flips tile bits 0..k-1 to 0 and sets bit k (k = ctz(J)):
+        // dE[k] is the change of sum_{p>=7} g_p b_p(J) for k < 4; every 16th tile recomputes exactly.
+        float dE[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            float v = (7 + k < NP) ? gp[(7 + k < NP) ? 7 + k : 0] : 0.f;
+#pragma unroll
+            for (int b = 0; b < k; ++b) v -= (7 + b < NP) ? gp[(7 + b < NP) ? 7 + b : 0] : 0.f;
+            dE[k] = v;
+        }
+        float Ehi = 0.f;                                   // C(i) + sum_{p>=7} g_p b_p(J)
         const int tab_off = (half * 4) * 16 + (int)(i & 15);   // [k][g][v] -> k*128 + g*16 + v
         // Row sum across tiles in compensated fp32 (Fast2Sum): the FP64 pipe stalls for hundreds of
         // cycles behind the tensor pipe (ncu: math-pipe throttle on a per-tile DADD), so fp64 is
@@ -447,9 +460,14 @@ tc_rows_kernel(const __grid_constant__ TcParams prm, const float* __restrict__ B
             const uint32_t qph = (uint32_t)((it / kQSlots) & 1);
             const int64_t J = j_first + it;
             const int xhi = __popc(ihi ^ (uint32_t)J);
-            float Ehi = Ci;                                // C(i) + sum_{p>=7} g_p b_p(J)
+            if (it == 0 || (J & 15) == 0) {
+                Ehi = Ci;
 #pragma unroll
-            for (int p = 7; p < NP; ++p) Ehi += ((J >> (p - 7)) & 1) ? gp[p] : 0.f;
+                for (int p = 7; p < NP; ++p) Ehi += ((J >> (p - 7)) & 1) ? gp[p] : 0.f;
+            } else {
+                const int k = __ffsll(J) - 1;
+                Ehi += (k == 0) ? dE[0] : (k == 1) ? dE[1] : (k == 2) ? dE[2] : dE[3];
+            }
             mbar_wait(bar_qfull + qs, qph);
             mbar_wait(bar_tfull + ts, tph);
             tc_fence_after();
@@ -482,7 +500,7 @@ tc_rows_kernel(const __grid_constant__ TcParams prm, const float* __restrict__ B
                 Q1 = fmaf(gp[2], tab[384 + gl * 16], Q1);
                 Q1 = fmaf(gp[3], tab[512 + gl * 16], Q1);
                 alu[gl] = fmaf(Ehi + Gmid[gl], Q0, Q1);
-                wg[gl] = sWl[xhi + __popc(imid ^ (uint32_t)(half * 4 + gl))];
+                wg[gl] = sWl[xhi + pmid[gl]];
             }
             asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
             tc_fence_before();

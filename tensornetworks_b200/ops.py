@@ -169,21 +169,29 @@ class SteinTables:
             raise ValueError("q must be float32 or float64")
         q = q.contiguous()
         lib = _lib.load()
-        st64 = self._st64()
         with torch.cuda.device(self.device):
             key = ("mp", bit_begin, bit_end)
             if key not in self._ws:
                 nbytes = lib.tnk_ksd_modeproduct_workspace_bytes(self.n, bit_begin, bit_end)
                 if nbytes == 0:
                     raise RuntimeError("tnk_ksd_modeproduct_workspace_bytes rejected the bit range")
-                self._ws[key] = torch.empty(nbytes, dtype=torch.uint8, device=self.device)
-            ws = self._ws[key]
+                # one-off per table and bit range: column-major score components and the row sums of r
+                s_cols = torch.empty((2, max(bit_end - bit_begin, 1), self.N), dtype=torch.float64, device=self.device)
+                r_sum = torch.empty(self.N, dtype=torch.float64, device=self.device)
+                _lib.check(lib.tnk_modeproduct_tables(self.n, _ptr(self._st64()), bit_begin, bit_end, _ptr(s_cols),
+                                                      _ptr(r_sum), _stream_ptr(self.device)), "tnk_modeproduct_tables")
+                launch_counter["kernels"] += 1
+                if self.dtype != torch.float64:
+                    self._ST64 = None        # the row-major fp64 copy was only needed for the transposition
+                self._ws[key] = (torch.empty(nbytes, dtype=torch.uint8, device=self.device), s_cols, r_sum)
+            ws, s_cols, r_sum = self._ws[key]
             u = torch.empty(self.N, dtype=torch.float64, device=self.device)
             part = torch.empty(1, dtype=torch.float64, device=self.device)
             launched = ctypes.c_int(0)
             _lib.check(lib.tnk_ksd_modeproduct(self.n, self.length_scale, _ptr(q), 0 if q.dtype == torch.float64 else 1,
-                                               _ptr(st64), bit_begin, bit_end, _ptr(u), _ptr(part), _ptr(ws), ws.numel(),
-                                               ctypes.byref(launched), _stream_ptr(self.device)), "tnk_ksd_modeproduct")
+                                               _ptr(s_cols), _ptr(r_sum), bit_begin, bit_end, _ptr(u), _ptr(part),
+                                               _ptr(ws), ws.numel(), ctypes.byref(launched), _stream_ptr(self.device)),
+                       "tnk_ksd_modeproduct")
             launch_counter["kernels"] += launched.value
         return u, part
 
