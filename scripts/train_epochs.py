@@ -23,6 +23,7 @@ def main():
     ap.add_argument("--epochs", type=int, default=2)
     ap.add_argument("--precision", default="tc32")
     ap.add_argument("--algorithm", default="pairs")
+    ap.add_argument("--profile", action="store_true", help="print the top CUDA ops of the timed epochs (torch.profiler)")
     args = ap.parse_args()
     world, rank, local = int(os.environ.get("WORLD_SIZE", "1")), int(os.environ.get("RANK", "0")), int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(local)
@@ -40,6 +41,12 @@ def main():
     hist = vi.train(x, num_epochs=1, lr_born_machine=0.05, verbose=False)      # warm-up epoch: tables, workspaces
     torch.cuda.synchronize()
     first_s = time.perf_counter() - t0
+    if args.profile and rank == 0:
+        from torch.profiler import profile, ProfilerActivity
+        with profile(activities=[ProfilerActivity.CPU, ProfilerActivity.CUDA]) as prof:
+            vi.train(x, num_epochs=args.epochs, lr_born_machine=0.05, verbose=False)
+            torch.cuda.synchronize()
+        print(prof.key_averages().table(sort_by="cuda_time_total", row_limit=25, max_name_column_width=60), file=sys.stderr)
     t0 = time.perf_counter()
     hist = vi.train(x, num_epochs=args.epochs, lr_born_machine=0.05, verbose=False)
     torch.cuda.synchronize()

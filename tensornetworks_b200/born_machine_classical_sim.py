@@ -79,7 +79,13 @@ class ClassicalBornMachine(nn.Module):
                 raise ValueError("x_condition provided but conditioning_dim is 0.")
             raw = self.params.unsqueeze(0)
         if self.use_logits:
-            return torch.softmax(raw - raw.max(dim=-1, keepdim=True)[0], dim=-1)
+            shifted = raw - raw.max(dim=-1, keepdim=True)[0]
+            if raw.is_cuda and raw.shape[0] == 1 and raw.shape[-1] >= (1 << 16):
+                # torch.softmax gives one thread block per row: a single row of 2^n logits would run on
+                # one SM (several ms at n = 24).  Same function from grid-wide elementwise ops and reductions.
+                e = torch.exp(shifted)
+                return e / e.sum(dim=-1, keepdim=True)
+            return torch.softmax(shifted, dim=-1)
         mag = raw.abs()
         return mag / mag.sum(dim=-1, keepdim=True)
 
