@@ -136,6 +136,24 @@ int tnk_ksd_modeproduct(int n_latent, double length_scale, const void* q, int q_
                         double* u, double* ksd_part,
                         void* workspace, size_t workspace_bytes, int* n_launch, void* stream);
 
+/* Classical Born machine over 2^n logits on the GPU (one unconditional distribution, fp32 like the
+ * reference's parameters): q = softmax(logits) and H = -sum q log clamp(q, 1e-10) in two streaming
+ * passes, and the backward pass of both in two more.  Replaces the tensor expressions of reference
+ * born_machine_classical_sim.py:74-99 (get_probabilities) and :177-181 (entropy) and their autograd
+ * graph.  Block partials are fp64 and folded in a fixed order.
+ *   tnk_born_blocks(N)   number of block partials (entropy_partial, scratch) for N states
+ *   max_logit            device float [1]: max over the logits (the shift of :97)
+ *   q                    device float [N] (out);  entropy_partial device double [blocks] (out): H = their sum
+ *   sum_exp              device double [1] (out): sum exp(logit - max)
+ *   grad_q               device double/float [N] or NULL (grad_dtype 0/1): dL/dq
+ *   grad_entropy         device double [1] or NULL: dL/dH
+ *   grad_logits          device float [N] (out): q (g - sum q g), g = grad_q + grad_entropy dH/dq */
+int tnk_born_blocks(int64_t num_states);
+int tnk_born_forward(const float* logits, int64_t num_states, const float* max_logit,
+                     float* q, double* entropy_partial, double* sum_exp, double* scratch, void* stream);
+int tnk_born_backward(const float* q, const void* grad_q, int grad_dtype, const double* grad_entropy,
+                      int64_t num_states, float* grad_logits, double* scratch, void* stream);
+
 /* Introspection of the tensor-core variant (TNK_PREC_TC32): padded score length np, number of
  * tf32 chunks (4 floats) per state k32, total 16-byte chunks per state of the column table kb
  * (tf32 chunks followed by bf16 chunks), the tf32 MMA K-step list - step k multiplies row chunks

@@ -16,7 +16,7 @@ REPO_DIR = os.path.dirname(PKG_DIR)
 CSRC = os.path.join(PKG_DIR, "csrc")
 INCLUDE = os.path.join(REPO_DIR, "include")
 LIB_PATH = os.path.join(PKG_DIR, "libtnk_b200.so")
-SOURCES = ["tnk_enum.cu", "tnk_ksd.cu", "tnk_peak.cu", "tnk_modeprod.cu", "tnk_tc.cu"]
+SOURCES = ["tnk_enum.cu", "tnk_ksd.cu", "tnk_peak.cu", "tnk_modeprod.cu", "tnk_tc.cu", "tnk_born.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC", "-I", INCLUDE]
 
@@ -26,7 +26,8 @@ MAX_PEERS = 8  # TNK_MAX_PEERS
 # every symbol include/tnk.h declares
 EXPORTS = ["tnk_last_error", "tnk_version", "tnk_bn_joint", "tnk_ksd_layout", "tnk_score",
            "tnk_ksd_workspace_bytes", "tnk_ksd_rows", "tnk_ksd_rows_peers", "tnk_ksd_timing_events", "tnk_alu_peak",
-           "tnk_ksd_modeproduct_workspace_bytes", "tnk_modeproduct_tables", "tnk_ksd_modeproduct", "tnk_tc_plan"]
+           "tnk_ksd_modeproduct_workspace_bytes", "tnk_modeproduct_tables", "tnk_ksd_modeproduct", "tnk_tc_plan",
+           "tnk_born_blocks", "tnk_born_forward", "tnk_born_backward"]
 
 
 def _nvcc():
@@ -111,6 +112,12 @@ def load():
     lib.tnk_tc_plan.restype = c_int
     lib.tnk_tc_plan.argtypes = [c_int, ctypes.POINTER(c_int), ctypes.POINTER(c_int), ctypes.POINTER(c_int),
                                 ctypes.POINTER(c_int), ctypes.POINTER(c_int), ctypes.POINTER(ctypes.c_int32)]
+    lib.tnk_born_blocks.restype = c_int
+    lib.tnk_born_blocks.argtypes = [ctypes.c_int64]
+    lib.tnk_born_forward.restype = c_int
+    lib.tnk_born_forward.argtypes = [c_vp, ctypes.c_int64, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp]
+    lib.tnk_born_backward.restype = c_int
+    lib.tnk_born_backward.argtypes = [c_vp, c_vp, c_int, c_vp, ctypes.c_int64, c_vp, c_vp, c_vp]
     lib.tnk_ksd_timing_events.restype = c_int
     lib.tnk_ksd_timing_events.argtypes = [c_vp, c_vp]
     lib.tnk_alu_peak.restype = c_int

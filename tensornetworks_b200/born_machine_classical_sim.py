@@ -24,6 +24,7 @@ class ClassicalBornMachine(nn.Module):
         self.use_layer_norm = use_layer_norm
         self._fixed_probs = None
         self._use_fixed_probs = False
+        self._pair_cache = None
 
         if conditioning_dim > 0:
             # MLP x -> logits (reference :24-48): Linear/[LayerNorm]/ReLU/Dropout(0.1) blocks,
@@ -79,15 +80,34 @@ class ClassicalBornMachine(nn.Module):
                 raise ValueError("x_condition provided but conditioning_dim is 0.")
             raw = self.params.unsqueeze(0)
         if self.use_logits:
+            if self._streaming(raw):
+                return self._probs_and_entropy("q_taken")[0].unsqueeze(0)
             shifted = raw - raw.max(dim=-1, keepdim=True)[0]
             if raw.is_cuda and raw.shape[0] == 1 and raw.shape[-1] >= (1 << 16):
-                # torch.softmax gives one thread block per row: a single row of 2^n logits would run on
-                # one SM (several ms at n = 24).  Same function from grid-wide elementwise ops and reductions.
-                e = torch.exp(shifted)
-                return e / e.sum(dim=-1, keepdim=True)
+                e = torch.exp(shifted)              # conditional net, one long row: same function from
+                return e / e.sum(dim=-1, keepdim=True)   # grid-wide ops (torch.softmax: one block per row)
             return torch.softmax(shifted, dim=-1)
         mag = raw.abs()
         return mag / mag.sum(dim=-1, keepdim=True)
+
+    def _streaming(self, raw):
+        """One unconditional row of >= 2^16 fp32 logits on the GPU goes through the streaming kernels
+        (ops.born_softmax_entropy); torch.softmax would run that single row on one SM."""
+        return (self.conditioning_dim == 0 and raw.is_cuda and raw.dtype == torch.float32
+                and raw.shape[-1] >= (1 << 16))
+
+    def _probs_and_entropy(self, which):
+        """(q, H) of the current parameters.  get_probabilities() and entropy() of the same training step
+        share one forward pass: the pair is cached per parameter version and grad mode, and each half is
+        handed out once (a second request recomputes, so no autograd graph is ever used twice)."""
+        from . import ops
+        key = (self.params._version, self.params.data_ptr(), torch.is_grad_enabled())
+        c = self._pair_cache
+        if c is None or c["key"] != key or c[which]:
+            q, H = ops.born_softmax_entropy(self.params)
+            c = self._pair_cache = {"key": key, "q": q, "H": H, "q_taken": False, "H_taken": False}
+        c[which] = True
+        return c["q"], c["H"]
 
     def _bits(self, indices, device):
         n = self.num_latent_vars
@@ -134,5 +154,8 @@ class ClassicalBornMachine(nn.Module):
 
     def entropy(self, x_condition=None):
         """H(q) = -sum q log clamp(q, 1e-10) (reference :177-181)."""
+        if (self.use_logits and self.conditioning_dim == 0 and x_condition is None
+                and not (self._use_fixed_probs and self._fixed_probs is not None) and self._streaming(self.params)):
+            return self._probs_and_entropy("H_taken")[1]
         probs = self.get_probabilities(x_condition).squeeze()
         return -(probs * torch.log(probs.clamp(min=1e-10))).sum()

@@ -351,6 +351,61 @@ def ksd_quadratic_form(q, tables, group=None, algorithm="pairs", exchange=None):
     return _KsdQuadraticForm.apply(q, tables, group, algorithm, exchange)
 
 
+class _BornSoftmaxEntropy(torch.autograd.Function):
+    """(q, H) = (softmax(logits), -sum q log clamp(q, 1e-10)) for one row of 2^n fp32 logits on the GPU:
+    tnk_born_forward / tnk_born_backward (four streaming passes per epoch instead of the autograd graph of
+    reference born_machine_classical_sim.py:74-99,177-181)."""
+
+    @staticmethod
+    def forward(ctx, logits):
+        ctx.set_materialize_grads(False)
+        lib = _lib.load()
+        logits = logits.contiguous()
+        N = logits.numel()
+        with torch.cuda.device(logits.device):
+            m = logits.max().reshape(1)
+            blocks = lib.tnk_born_blocks(N)
+            q = torch.empty_like(logits)
+            buf = torch.empty(2 * blocks + 1, dtype=torch.float64, device=logits.device)
+            _lib.check(lib.tnk_born_forward(_ptr(logits), N, _ptr(m), _ptr(q), _ptr(buf), _ptr(buf[2 * blocks:]),
+                                            _ptr(buf[blocks:]), _stream_ptr(logits.device)), "tnk_born_forward")
+            launch_counter["kernels"] += 2
+            H = buf[:blocks].sum().to(logits.dtype)
+        ctx.save_for_backward(q)
+        return q, H
+
+    @staticmethod
+    def backward(ctx, grad_q, grad_H):
+        (q,) = ctx.saved_tensors
+        if grad_q is None and grad_H is None:
+            return None
+        lib = _lib.load()
+        N = q.numel()
+        with torch.cuda.device(q.device):
+            if grad_q is not None:
+                if grad_q.dtype not in (torch.float32, torch.float64):
+                    grad_q = grad_q.to(torch.float32)
+                grad_q = grad_q.contiguous()
+            gH = None if grad_H is None else grad_H.detach().to(torch.float64).reshape(1)
+            blocks = lib.tnk_born_blocks(N)
+            scratch = torch.empty(blocks, dtype=torch.float64, device=q.device)
+            g_logits = torch.empty_like(q)
+            _lib.check(lib.tnk_born_backward(_ptr(q), None if grad_q is None else _ptr(grad_q),
+                                             1 if grad_q is None or grad_q.dtype == torch.float32 else 0,
+                                             None if gH is None else _ptr(gH), N, _ptr(g_logits), _ptr(scratch),
+                                             _stream_ptr(q.device)), "tnk_born_backward")
+            launch_counter["kernels"] += 2
+        return g_logits
+
+
+def born_softmax_entropy(logits):
+    """q [N] and H (0-dim) of one unconditional Born machine from its fp32 CUDA logits [N];
+    differentiable w.r.t. the logits through both outputs."""
+    if not (logits.is_cuda and logits.dtype == torch.float32 and logits.dim() == 1):
+        raise ValueError("born_softmax_entropy expects a 1-D float32 CUDA tensor of logits")
+    return _BornSoftmaxEntropy.apply(logits)
+
+
 def tc_plan(n):
     """K-step plan of the tensor-core variant for n latent bits (tnk_tc_plan)."""
     lib = _lib.load()
