@@ -129,6 +129,10 @@ int tnk_ksd_rows_peers(int n_latent, double length_scale, int precision,
  *   u        device double [2^n] (out, partial), ksd_part device double [1] (out, partial)
  *   workspace: tnk_ksd_modeproduct_workspace_bytes(n, bit_begin, bit_end) bytes, 256-byte aligned */
 size_t tnk_ksd_modeproduct_workspace_bytes(int n_latent, int bit_begin, int bit_end);
+/* Plan knob (tests): at most max_row_bits (1..11, default 11) high bits per strided pass, so that the
+ * three-and-more-pass plans of n > 24 can be exercised at small n.  Returns the previous value; tables and
+ * workspaces made under one setting must not be used under another. */
+int tnk_modeproduct_plan_limit(int max_row_bits);
 int tnk_modeproduct_tables(int n_latent, const double* ST64, int bit_begin, int bit_end,
                            double* S_cols, double* r_sum, void* stream);
 int tnk_ksd_modeproduct(int n_latent, double length_scale, const void* q, int q_dtype,

@@ -26,7 +26,7 @@ MAX_PEERS = 8  # TNK_MAX_PEERS
 # every symbol include/tnk.h declares
 EXPORTS = ["tnk_last_error", "tnk_version", "tnk_bn_joint", "tnk_ksd_layout", "tnk_score",
            "tnk_ksd_workspace_bytes", "tnk_ksd_rows", "tnk_ksd_rows_peers", "tnk_ksd_timing_events", "tnk_alu_peak",
-           "tnk_ksd_modeproduct_workspace_bytes", "tnk_modeproduct_tables", "tnk_ksd_modeproduct", "tnk_tc_plan",
+           "tnk_ksd_modeproduct_workspace_bytes", "tnk_modeproduct_tables", "tnk_modeproduct_plan_limit", "tnk_ksd_modeproduct", "tnk_tc_plan",
            "tnk_born_blocks", "tnk_born_forward", "tnk_born_backward"]
 
 
@@ -105,6 +105,8 @@ def load():
     lib.tnk_ksd_modeproduct_workspace_bytes.restype = c_sz
     lib.tnk_ksd_modeproduct_workspace_bytes.argtypes = [c_int, c_int, c_int]
     lib.tnk_ksd_modeproduct.restype = c_int
+    lib.tnk_modeproduct_plan_limit.restype = c_int
+    lib.tnk_modeproduct_plan_limit.argtypes = [c_int]
     lib.tnk_modeproduct_tables.restype = c_int
     lib.tnk_modeproduct_tables.argtypes = [c_int, c_vp, c_int, c_int, c_vp, c_vp, c_vp]
     lib.tnk_ksd_modeproduct.argtypes = [c_int, c_dbl, c_vp, c_int, c_vp, c_vp, c_int, c_int, c_vp, c_vp, c_vp, c_sz,

@@ -401,6 +401,10 @@ mp_scalar_kernel(const double* __restrict__ blockpart, int64_t nblocks, double* 
     if (threadIdx.x == 0) out[0] = red[0];
 }
 
+// Row bits one strided pass may take (2^g rows x 2^(13-g) states per tile).  The default lets two passes
+// reach n = 24; tnk_modeproduct_plan_limit lowers it so that tests reach the multi-pass plans at small n.
+int g_max_row_bits = kTileLog - kMinLogW;
+
 struct MpPass { int b0, g, logW; };
 
 struct MpPlan {
@@ -422,7 +426,7 @@ int mp_plan(int n, int p_begin, int p_end, MpPlan* p) {
         p->last = MpPass{n, 0, n};
         p->flip_split = n;
     } else {
-        const int gmax = kTileLog - kMinLogW;
+        const int gmax = g_max_row_bits;
         const int passes = (rem + gmax - 1) / gmax;
         if (passes - 1 > 4) return 1;
         int b0 = p->T, left = rem;
@@ -456,6 +460,12 @@ int mp_plan(int n, int p_begin, int p_end, MpPlan* p) {
 }
 
 }  // namespace
+
+extern "C" int tnk_modeproduct_plan_limit(int max_row_bits) {
+    const int prev = g_max_row_bits;
+    if (max_row_bits >= 1 && max_row_bits <= kTileLog - kMinLogW) g_max_row_bits = max_row_bits;
+    return prev;
+}
 
 extern "C" size_t tnk_ksd_modeproduct_workspace_bytes(int n_latent, int bit_begin, int bit_end) {
     MpPlan p;

@@ -204,6 +204,32 @@ def test_modeproduct_vs_oracle(ops, n, seed):
     _check(K, g, Kref, gref, 1e-9)
 
 
+@pytest.mark.parametrize("n,limit", [(15, 1), (17, 2), (18, 3), (19, 2), (20, 4)])
+def test_modeproduct_multi_pass_plans(ops, n, limit):
+    """The plans of n > 24 (in-place middle passes, natural V order, unblocked last pass) reached at small n by
+    limiting the row bits per strided pass; compared with the fp64 pair kernel and with bit-range partials."""
+    from tensornetworks_b200 import _lib
+    lib = _lib.load()
+    bn, lat, obs, x = random_binary_bn(n, seed=n)
+    q = random_q(1 << n, seed=n).cuda()
+    ref = _tables(ops, bn, x, lat, "fp64")
+    u0, K0 = ref.ksd_rows(q)
+    prev = lib.tnk_modeproduct_plan_limit(limit)
+    try:
+        tabs = _tables(ops, bn, x, lat, "fp64")          # fresh tables: the column copies follow the plan
+        u1, K1 = tabs.ksd_modeproduct(q)
+        ua, Ka = tabs.ksd_modeproduct(q, 0, n // 2)
+        ub, Kb = tabs.ksd_modeproduct(q, n // 2, n)
+        torch.cuda.synchronize()
+    finally:
+        lib.tnk_modeproduct_plan_limit(prev)
+    den = float(u0.abs().max())
+    assert float((u1 - u0).abs().max()) <= 1e-12 * den
+    assert float((ua + ub - u0).abs().max()) <= 1e-12 * den
+    assert abs(float(K1) - float(K0)) <= 1e-12 * abs(float(K0))
+    assert abs(float(Ka + Kb) - float(K0)) <= 1e-12 * abs(float(K0))
+
+
 def test_modeproduct_matches_pair_kernel_n20(ops):
     """Full size of BASELINE.json's metric: the two CUDA algorithms agree (no CPU oracle at this size
     in test time), plus the bit-range partials add up (the multi-GPU split)."""
