@@ -121,14 +121,17 @@ __global__ void __launch_bounds__(256)
 score_kernel(int n, int np, int64_t N, double alpha, double gamma,
              const double* __restrict__ P, double* __restrict__ S64,
              T* __restrict__ ST, T* __restrict__ Cst) {
+    // Rows are staged in shared memory with ODD strides (ns doubles, nps elements of T) so that the
+    // per-thread row writes are bank-conflict-free; the copy-out then walks the tile linearly.
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    double* sS = reinterpret_cast<double*>(smem_raw);                       // [256][n]
-    T* sT = reinterpret_cast<T*>(smem_raw + (size_t)256 * n * sizeof(double));  // [256][np]
+    const int ns = n | 1, nps = np + 1;
+    double* sS = reinterpret_cast<double*>(smem_raw);                                     // [256][ns], only if S64
+    T* sT = reinterpret_cast<T*>(smem_raw + (S64 ? (size_t)256 * ns * sizeof(double) : 0)); // [256][nps]
     const int tid = threadIdx.x;
     const int64_t base = (int64_t)blockIdx.x * 256;
     const int64_t i = base + tid;
     double Rsum = 0.0, rho0 = 0.0;
-    if (ST) for (int p = 0; p < np; ++p) sT[tid * np + p] = (T)0;
+    if (ST) for (int p = 0; p < np; ++p) sT[tid * nps + p] = (T)0;
     if (i < N) {
         const double p = P[i];
         const bool dead = fabs(p) < 1e-12;  // stein_utils.py:126
@@ -136,8 +139,8 @@ score_kernel(int n, int np, int64_t N, double alpha, double gamma,
             const int bit = n - 1 - k;
             double s = 0.0;
             if (!dead) s = __dsub_rn(1.0, __ddiv_rn(P[i ^ ((int64_t)1 << bit)], p));  // :134
-            if (S64) sS[tid * n + k] = s;
-            if (ST) sT[tid * np + bit] = (T)s;
+            if (S64) sS[tid * ns + k] = s;
+            if (ST) sT[tid * nps + bit] = (T)s;
             const double r = 1.0 - s;
             Rsum += r;
             if ((i >> bit) & 1) rho0 += r;
@@ -147,12 +150,24 @@ score_kernel(int n, int np, int64_t N, double alpha, double gamma,
         Cst[i] = (T)0;  // padding rows of the packed table
     }
     __syncthreads();
-    if (S64) {
-        const int64_t live = (N - base < 256 ? (N - base > 0 ? N - base : 0) : 256) * n;
-        for (int64_t t = tid; t < live; t += 256) S64[base * n + t] = sS[t];
+    if (S64 && n > 0) {
+        const int live = (int)(N - base < 256 ? (N - base > 0 ? N - base : 0) : 256) * n;
+        const int dq = 256 / n, dr = 256 % n;              // element t = tid + 256 j sits in row t / n, column t % n
+        int row = tid / n, col = tid % n;
+        for (int t = tid; t < live; t += 256) {
+            S64[base * n + t] = sS[row * ns + col];
+            row += dq; col += dr;
+            if (col >= n) { col -= n; ++row; }
+        }
     }
     if (ST) {
-        for (int t = tid; t < 256 * np; t += 256) ST[base * np + t] = sT[t];
+        const int dq = 256 / np, dr = 256 % np;
+        int row = tid / np, col = tid % np;
+        for (int t = tid; t < 256 * np; t += 256) {
+            ST[base * np + t] = sT[row * nps + col];
+            row += dq; col += dr;
+            if (col >= np) { col -= np; ++row; }
+        }
     }
 }
 
@@ -173,7 +188,7 @@ extern "C" int tnk_score(int n_latent, double length_scale, const double* P,
     }
     const int64_t rows = ST ? g.n_pad : N;
     const unsigned blocks = (unsigned)((rows + 255) / 256);
-    const size_t smem = (size_t)256 * ((size_t)n * sizeof(double) + (size_t)g.np * g.elem);
+    const size_t smem = (size_t)256 * ((S64 ? (size_t)(n | 1) * sizeof(double) : 0) + (size_t)(g.np + 1) * g.elem);
     cudaStream_t st = (cudaStream_t)stream;
     if (g.elem == 4) {
         TNK_CUDA_OK(cudaFuncSetAttribute(score_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
