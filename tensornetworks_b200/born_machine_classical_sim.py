@@ -90,6 +90,11 @@ class ClassicalBornMachine(nn.Module):
         mag = raw.abs()
         return mag / mag.sum(dim=-1, keepdim=True)
 
+    def __getstate__(self):
+        state = self.__dict__.copy()
+        state["_pair_cache"] = None          # cached (q, H) carry an autograd graph: never copied or pickled
+        return state
+
     def _streaming(self, raw):
         """One unconditional row of >= 2^16 fp32 logits on the GPU goes through the streaming kernels
         (ops.born_softmax_entropy); torch.softmax would run that single row on one SM."""

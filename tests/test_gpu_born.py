@@ -91,6 +91,10 @@ def test_born_machine_streaming_matches_tensor_path():
     H2 = -(p2 * torch.log(p2.clamp(min=1e-10))).sum()
     ((p2 * torch.arange(1 << 16, device="cuda", dtype=torch.float64)).sum() * 1e-4 - 0.01 * H2).backward()
     assert float((g1.double() - l.grad).abs().max() / l.grad.abs().max()) < 2e-5
+    import copy
+    bm.get_probabilities()
+    twin = copy.deepcopy(bm)                  # the cached pair (with its graph) is not copied
+    assert twin._pair_cache is None and torch.equal(twin.params, bm.params)
     # asking twice in one step never reuses a consumed graph
     a = bm.get_probabilities(); b = bm.get_probabilities()
     a.sum().backward(); b.sum().backward()
