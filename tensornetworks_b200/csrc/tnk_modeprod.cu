@@ -514,8 +514,10 @@ extern "C" int tnk_ksd_modeproduct(int n_latent, double length_scale, const void
     double* V = (double*)(ws + p.off_v);
     double* blockpart = (double*)(ws + p.off_block);
 
-    static bool attr_set = false;
-    if (!attr_set) {
+    static bool attr_set[64] = {};             // per device: function attributes belong to the device's context
+    int dev = 0;
+    TNK_CUDA_OK(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64 || !attr_set[dev]) {
         TNK_CUDA_OK(cudaFuncSetAttribute(mp_first_kernel<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMpSmem));
         TNK_CUDA_OK(cudaFuncSetAttribute(mp_first_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMpSmem));
         TNK_CUDA_OK(cudaFuncSetAttribute(mp_last_kernel<double, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMpSmem));
@@ -523,7 +525,7 @@ extern "C" int tnk_ksd_modeproduct(int n_latent, double length_scale, const void
         TNK_CUDA_OK(cudaFuncSetAttribute(mp_last_kernel<double, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMpSmem));
         TNK_CUDA_OK(cudaFuncSetAttribute(mp_last_kernel<float, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMpSmem));
         TNK_CUDA_OK(cudaFuncSetAttribute(mp_transform_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMpSmem));
-        attr_set = true;
+        if (dev >= 0 && dev < 64) attr_set[dev] = true;
     }
 
     {
