@@ -435,10 +435,14 @@ def main():
                                   "frac": alu_ach / r["peak_rate"], "lane_ops_per_pair": w_lane,
                                   "peak_source": "tnk_alu_peak FMA-chain probe measured in this run"}
         if r["mp_ms"] is not None:
-            mp_bytes = 8.0 * (1 << n) * (2 * n + 2 * (n + 2) + 4)    # S twice, n+2 vectors written and read once, q twice, r_sum, u
+            mp_storage = "fp64" if args.precision == "fp64" else "fp32"     # SteinTables.ksd_modeproduct's default for these tables
+            mp_elem = 8.0 if mp_storage == "fp64" else 4.0
+            # S twice, n+2 vectors written and read once (storage type); q twice, r_sum, u (fp64)
+            mp_bytes = mp_elem * (1 << n) * (2 * n + 2 * (n + 2)) + 8.0 * (1 << n) * 4
             hbm_peak = load_measured_peaks().get("hbm_gbs") or 6650.0
             mp_gbs = mp_bytes / (r["mp_ms"] * 1e-3) / 1e9
-            line["modeproduct"] = {"kernels": "mp_first_kernel + mp_last_kernel (fp64, O(n^2 2^n), same K and gradient)",
+            line["modeproduct"] = {"kernels": "mp_first_kernel + mp_last_kernel (fp64 arithmetic, O(n^2 2^n), same K and gradient)",
+                                   "storage": mp_storage,
                                    "ms": r["mp_ms"], "effective_value": pairs / (r["mp_ms"] * 1e-3), "unit": UNIT,
                                    "bound": "hbm", "algorithmic_bytes": mp_bytes, "achieved": mp_gbs, "peak": hbm_peak,
                                    "roofline_unit": "GB/s", "frac": mp_gbs / hbm_peak, "ksd_sq": r["mp_K"],

@@ -120,7 +120,7 @@ int tnk_ksd_rows_peers(int n_latent, double length_scale, int precision,
  * (ksd_vi.py:110-131,145).  Work is split by score component: the call handles bit positions
  * [bit_begin,bit_end) of [0,n) and writes that partial of u for ALL 2^n rows; partials of
  * disjoint bit ranges add up to u and K (sum-allreduce across ranks).
- *   S_cols   device double [2][bit_end-bit_begin][2^n]: column-major score components of the bit
+ *   S_cols   device double (or float, per `storage`) [2][bit_end-bit_begin][2^n]: column-major score components of the bit
  *            range, once in state order (read by the first pass) and once in the order the last
  *            pass walks (a private, plan-dependent permutation of the states);
  *   r_sum    device double [2^n] = sum over the range of (2 - s_p(z)), in the last-pass order;
@@ -128,15 +128,17 @@ int tnk_ksd_rows_peers(int n_latent, double length_scale, int precision,
  *   ST64     device double [n_pad][np]: the packed table tnk_score emits for TNK_PREC_FP64
  *   u        device double [2^n] (out, partial), ksd_part device double [1] (out, partial)
  *   workspace: tnk_ksd_modeproduct_workspace_bytes(n, bit_begin, bit_end) bytes, 256-byte aligned */
-size_t tnk_ksd_modeproduct_workspace_bytes(int n_latent, int bit_begin, int bit_end);
+#define TNK_MP_STORE_FP64 0   /* score columns and transformed vectors kept in fp64 (results to ~1e-15 of the fp64 pair kernel) */
+#define TNK_MP_STORE_FP32 1   /* kept in fp32 in HBM (half the traffic); arithmetic, r_sum, u and K stay fp64 */
+size_t tnk_ksd_modeproduct_workspace_bytes(int n_latent, int bit_begin, int bit_end, int storage);
 /* Plan knob (tests): at most max_row_bits (1..11, default 11) high bits per strided pass, so that the
  * three-and-more-pass plans of n > 24 can be exercised at small n.  Returns the previous value; tables and
  * workspaces made under one setting must not be used under another. */
 int tnk_modeproduct_plan_limit(int max_row_bits);
-int tnk_modeproduct_tables(int n_latent, const double* ST64, int bit_begin, int bit_end,
-                           double* S_cols, double* r_sum, void* stream);
-int tnk_ksd_modeproduct(int n_latent, double length_scale, const void* q, int q_dtype,
-                        const double* S_cols, const double* r_sum, int bit_begin, int bit_end,
+int tnk_modeproduct_tables(int n_latent, const double* ST64, int bit_begin, int bit_end, int storage,
+                           void* S_cols, double* r_sum, void* stream);
+int tnk_ksd_modeproduct(int n_latent, double length_scale, const void* q, int q_dtype, int storage,
+                        const void* S_cols, const double* r_sum, int bit_begin, int bit_end,
                         double* u, double* ksd_part,
                         void* workspace, size_t workspace_bytes, int* n_launch, void* stream);
 

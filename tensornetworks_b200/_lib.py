@@ -22,6 +22,7 @@ NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", 
 
 PREC_FP64, PREC_FP32, PREC_FP64_SIMPLE, PREC_TC32 = 0, 1, 2, 4
 MAX_PEERS = 8  # TNK_MAX_PEERS
+MP_STORE = {"fp64": 0, "fp32": 1}  # TNK_MP_STORE_*
 
 # every symbol include/tnk.h declares
 EXPORTS = ["tnk_last_error", "tnk_version", "tnk_bn_joint", "tnk_ksd_layout", "tnk_score",
@@ -103,13 +104,13 @@ def load():
                                        c_int, c_int, ctypes.POINTER(c_vp), ctypes.POINTER(c_vp), c_vp,
                                        c_vp, c_sz, ctypes.POINTER(c_int), c_vp]
     lib.tnk_ksd_modeproduct_workspace_bytes.restype = c_sz
-    lib.tnk_ksd_modeproduct_workspace_bytes.argtypes = [c_int, c_int, c_int]
+    lib.tnk_ksd_modeproduct_workspace_bytes.argtypes = [c_int, c_int, c_int, c_int]
     lib.tnk_ksd_modeproduct.restype = c_int
     lib.tnk_modeproduct_plan_limit.restype = c_int
     lib.tnk_modeproduct_plan_limit.argtypes = [c_int]
     lib.tnk_modeproduct_tables.restype = c_int
-    lib.tnk_modeproduct_tables.argtypes = [c_int, c_vp, c_int, c_int, c_vp, c_vp, c_vp]
-    lib.tnk_ksd_modeproduct.argtypes = [c_int, c_dbl, c_vp, c_int, c_vp, c_vp, c_int, c_int, c_vp, c_vp, c_vp, c_sz,
+    lib.tnk_modeproduct_tables.argtypes = [c_int, c_vp, c_int, c_int, c_int, c_vp, c_vp, c_vp]
+    lib.tnk_ksd_modeproduct.argtypes = [c_int, c_dbl, c_vp, c_int, c_int, c_vp, c_vp, c_int, c_int, c_vp, c_vp, c_vp, c_sz,
                                         ctypes.POINTER(c_int), c_vp]
     lib.tnk_tc_plan.restype = c_int
     lib.tnk_tc_plan.argtypes = [c_int, ctypes.POINTER(c_int), ctypes.POINTER(c_int), ctypes.POINTER(c_int),

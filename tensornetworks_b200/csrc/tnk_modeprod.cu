@@ -104,9 +104,10 @@ __device__ __forceinline__ int64_t last_layout(int64_t z, int blocked, int logW)
 
 // ---- MP0 (one-off per table): S[lv][z] = s_p(z) for p = p0 + lv, the same in the last-pass layout
 // (S2), and Rs[last_layout(z)] = n_loc + sum_lv (1 - s_p(z))
+template <typename T>
 __global__ void __launch_bounds__(256)
 mp_tables_kernel(int np, int64_t N, int p0, int n_loc, int blocked, int logW, const double* __restrict__ ST,
-                 double* __restrict__ S, double* __restrict__ S2, double* __restrict__ Rs) {
+                 T* __restrict__ S, T* __restrict__ S2, double* __restrict__ Rs) {
     const int64_t z = (int64_t)blockIdx.x * 256 + threadIdx.x;
     if (z >= N) return;
     const int64_t zb = last_layout(z, blocked, logW);
@@ -114,9 +115,9 @@ mp_tables_kernel(int np, int64_t N, int p0, int n_loc, int blocked, int logW, co
     double rs = (double)n_loc;
     for (int lv = 0; lv < n_loc; ++lv) {
         const double v = s[lv];
-        S[(int64_t)lv * N + z] = v;
-        S2[(int64_t)lv * N + zb] = v;
-        rs += 1.0 - v;
+        S[(int64_t)lv * N + z] = (T)v;
+        S2[(int64_t)lv * N + zb] = (T)v;
+        rs += 1.0 - (double)(T)v;            // the sum of the r_p the kernels will see
     }
     Rs[zb] = rs;
 }
@@ -126,10 +127,10 @@ mp_tables_kernel(int np, int64_t N, int p0, int n_loc, int blocked, int logW, co
 //   y <  nchunk + n_loc    y_p[z] = q[z] s_p(z) + q[z^e_p],  p = p0 + (y - nchunk)      -> V slot lv
 //   y == nchunk + n_loc    q itself                                                    -> V slot n_loc
 // then the butterflies of bits [0,T) and the store.  (The heavy Y tiles are scheduled first.)
-template <typename Q>
+template <typename Q, typename TS>
 __global__ void __launch_bounds__(kMpThreads, 2)
 mp_first_kernel(int T, int64_t N, int p0, int n_loc, int pre_cnt, int chunk, int nchunk, int blocked, int logW, int group_log,
-                const Q* __restrict__ q, const double* __restrict__ S, double* __restrict__ V, double a) {
+                const Q* __restrict__ q, const TS* __restrict__ S, TS* __restrict__ V, double a) {
     extern __shared__ double tile[];
     const int tile_elems = 1 << T;
     // block order: [tile group][vector][tile in group] - neighbouring tiles of one vector run together
@@ -169,22 +170,22 @@ mp_first_kernel(int T, int64_t N, int p0, int n_loc, int pre_cnt, int chunk, int
                     int64_t zb; int fl;
                     partner(p0 + lv, zb, fl);
                     const Q* qf = q + zb;
-                    const double* Sf = S + (int64_t)lv * N + zb;
+                    const TS* Sf = S + (int64_t)lv * N + zb;
 #pragma unroll
                     for (int j = 0; j < 8; ++j) {
                         const int ef = (w + (j << 10)) ^ fl;
-                        x[j] = fma(-(double)qf[ef], 1.0 - Sf[ef], x[j]);
+                        x[j] = fma(-(double)qf[ef], 1.0 - (double)Sf[ef], x[j]);
                     }
                 }
             } else if (slot < n_loc) {
                 int64_t zb; int fl;
                 partner(p0 + slot, zb, fl);
                 const Q* qf = q + zb;
-                const double* Sp = S + (int64_t)slot * N + z0;
+                const TS* Sp = S + (int64_t)slot * N + z0;
 #pragma unroll
                 for (int j = 0; j < 8; ++j) {
                     const int e = w + (j << 10);
-                    x[j] = fma((double)qz[e], Sp[e], (double)qf[e ^ fl]);
+                    x[j] = fma((double)qz[e], (double)Sp[e], (double)qf[e ^ fl]);
                 }
             } else {
 #pragma unroll
@@ -205,19 +206,19 @@ mp_first_kernel(int T, int64_t N, int p0, int n_loc, int pre_cnt, int chunk, int
 #pragma unroll
         for (int jj = 0; jj < 16; ++jj) x[jj] = tile[pb ^ ((jj << 6) ^ ((jj & 1) ? 9 : 0))];
         reg_butterflies<4>(x, a);
-        double* out = V + (int64_t)slot * N;
+        TS* out = V + (int64_t)slot * N;
         if (blocked) {
             out += tile_id << logW;
             const int W = 1 << logW;
 #pragma unroll
             for (int jj = 0; jj < 16; ++jj) {
                 const int e = base | (jj << 6);
-                out[((int64_t)(e >> logW) << kTileLog) | (e & (W - 1))] = x[jj];
+                out[((int64_t)(e >> logW) << kTileLog) | (e & (W - 1))] = (TS)x[jj];
             }
         } else {
             out += z0;
 #pragma unroll
-            for (int jj = 0; jj < 16; ++jj) out[base | (jj << 6)] = x[jj];
+            for (int jj = 0; jj < 16; ++jj) out[base | (jj << 6)] = (TS)x[jj];
         }
         return;
     }
@@ -230,12 +231,12 @@ mp_first_kernel(int T, int64_t N, int p0, int n_loc, int pre_cnt, int chunk, int
             for (int lv = lv0; lv < lv1; ++lv) {
                 int64_t zb; int fl;
                 partner(p0 + lv, zb, fl);
-                val = fma(-(double)q[zb + (e ^ fl)], 1.0 - S[(int64_t)lv * N + zb + (e ^ fl)], val);
+                val = fma(-(double)q[zb + (e ^ fl)], 1.0 - (double)S[(int64_t)lv * N + zb + (e ^ fl)], val);
             }
         } else if (slot < n_loc) {
             int64_t zb; int fl;
             partner(p0 + slot, zb, fl);
-            val = fma((double)qz[e], S[(int64_t)slot * N + z0 + e], (double)q[zb + (e ^ fl)]);
+            val = fma((double)qz[e], (double)S[(int64_t)slot * N + z0 + e], (double)q[zb + (e ^ fl)]);
         } else {
             val = (double)qz[e];
         }
@@ -243,30 +244,31 @@ mp_first_kernel(int T, int64_t N, int p0, int n_loc, int pre_cnt, int chunk, int
     }
     __syncthreads();
     tile_butterflies(tile, 0, T, T, a);
-    double* out = V + (int64_t)slot * N + z0;      // never blocked: one pass only
-    for (int e = threadIdx.x; e < tile_elems; e += kMpThreads) out[e] = tile[swz(e)];
+    TS* out = V + (int64_t)slot * N + z0;          // never blocked: one pass only
+    for (int e = threadIdx.x; e < tile_elems; e += kMpThreads) out[e] = (TS)tile[swz(e)];
 }
 
 // ---- MP2: middle pass (n > kTileLog + 11 only): butterflies for bits [b0, b0+g) on tiles of
 // 2^g rows x 2^logW contiguous elements, in place.
+template <typename TS>
 __global__ void __launch_bounds__(kMpThreads, 2)
-mp_transform_kernel(double* __restrict__ V, int64_t N, int b0, int g, int logW, double a) {
+mp_transform_kernel(TS* __restrict__ V, int64_t N, int b0, int g, int logW, double a) {
     extern __shared__ double tile[];
     const int tile_elems = 1 << (g + logW);
     const int W = 1 << logW;
     const int64_t nlob = (int64_t)1 << (b0 - logW);
     const int64_t t = blockIdx.x;
     const int64_t lob = t % nlob, hi = t / nlob;
-    double* vec = V + (int64_t)blockIdx.y * N + ((hi << (b0 + g)) | (lob << logW));
+    TS* vec = V + (int64_t)blockIdx.y * N + ((hi << (b0 + g)) | (lob << logW));
     for (int e = threadIdx.x; e < tile_elems; e += kMpThreads) {
         const int m = e >> logW, w = e & (W - 1);
-        tile[swz(e)] = vec[((int64_t)m << b0) + w];
+        tile[swz(e)] = (double)vec[((int64_t)m << b0) + w];
     }
     __syncthreads();
     tile_butterflies(tile, logW, g, g + logW, a);
     for (int e = threadIdx.x; e < tile_elems; e += kMpThreads) {
         const int m = e >> logW, w = e & (W - 1);
-        vec[((int64_t)m << b0) + w] = tile[swz(e)];
+        vec[((int64_t)m << b0) + w] = (TS)tile[swz(e)];
     }
 }
 
@@ -275,11 +277,11 @@ mp_transform_kernel(double* __restrict__ V, int64_t N, int b0, int g, int logW, 
 // the u values its threads own (element e = tid + 512 k).  g == 0: nothing left to transform
 // (n <= kTileLog), the tile is a contiguous run and every bit is "pre".
 // FAST: the two-pass case with a full tile (blocked layout, g >= 3), specialised at compile time.
-template <typename Q, bool FAST>
+template <typename Q, typename TS, bool FAST>
 __global__ void __launch_bounds__(kMpThreads, 2)
 mp_last_kernel(int64_t N, int b0, int g, int logW, int p0, int n_loc, int nchunk, int flip_split, int blocked_arg,
-               const Q* __restrict__ q, const double* __restrict__ S, const double* __restrict__ Rs,
-               const double* __restrict__ V, double* __restrict__ u, double* __restrict__ blockpart, double a) {
+               const Q* __restrict__ q, const TS* __restrict__ S, const double* __restrict__ Rs,
+               const TS* __restrict__ V, double* __restrict__ u, double* __restrict__ blockpart, double a) {
     extern __shared__ double tile[];
     __shared__ double red[kMpThreads / 32];
     const bool blocked = FAST || blocked_arg;
@@ -305,15 +307,15 @@ mp_last_kernel(int64_t N, int b0, int g, int logW, int p0, int n_loc, int nchunk
     const int ptid = swz(threadIdx.x);                     // swz(tid + 512 k) = ptid + 512 k
     const int nvec = n_loc + 1 + nchunk;
     for (int v = 0; v < nvec; ++v) {
-        const double* vec = V + (int64_t)v * N + lbase;
+        const TS* vec = V + (int64_t)v * N + lbase;
         if (fused) {
 #pragma unroll 1
             for (int h = 0; h < 2; ++h) {
                 const int w = threadIdx.x + h * kMpThreads;
-                const double* src = vec + loff(w);
+                const TS* src = vec + loff(w);
                 double x[8];
 #pragma unroll
-                for (int j = 0; j < 8; ++j) x[j] = src[j * jstride];
+                for (int j = 0; j < 8; ++j) x[j] = (double)src[j * jstride];
                 reg_butterflies<3>(x, a);
                 const int pw = swz(w);
 #pragma unroll
@@ -325,20 +327,20 @@ mp_last_kernel(int64_t N, int b0, int g, int logW, int p0, int n_loc, int nchunk
 #pragma unroll
             for (int k = 0; k < kMpPerThread; ++k) {
                 const int e = threadIdx.x + k * kMpThreads;
-                if (live(e)) tile[ptid + k * kMpThreads] = vec[loff(e)];
+                if (live(e)) tile[ptid + k * kMpThreads] = (double)vec[loff(e)];
             }
             __syncthreads();
             tile_butterflies(tile, logW, g, g + logW, a);
         }
         if (v < n_loc) {
-            const double* Sp = S + (int64_t)v * N + lbase;
+            const TS* Sp = S + (int64_t)v * N + lbase;
             const int fb = (v >= post0) ? swz(1 << (p0 + v - b0 + logW)) : 0;
 #pragma unroll
             for (int k = 0; k < kMpPerThread; ++k) {
                 const int e = threadIdx.x + k * kMpThreads;
                 if (live(e)) {
                     const int pe = ptid + k * kMpThreads;
-                    const double r = 1.0 - Sp[loff(e)];
+                    const double r = 1.0 - (double)Sp[loff(e)];
                     double x = fma(-r, tile[pe], acc[k]);
                     if (fb) x += tile[pe ^ fb];
                     acc[k] = x;
@@ -414,8 +416,10 @@ struct MpPlan {
     size_t off_v, off_block, total;
 };
 
-int mp_plan(int n, int p_begin, int p_end, MpPlan* p) {
+int mp_plan(int n, int p_begin, int p_end, int storage, MpPlan* p) {
     if (n < 0 || n > TNK_MAX_LATENT || p_begin < 0 || p_end > n || p_begin > p_end) return 1;
+    if (storage != TNK_MP_STORE_FP64 && storage != TNK_MP_STORE_FP32) return 1;
+    const size_t elem = storage == TNK_MP_STORE_FP32 ? sizeof(float) : sizeof(double);
     p->N = (int64_t)1 << n;
     p->n_loc = p_end - p_begin;
     p->T = n < kTileLog ? n : kTileLog;
@@ -453,9 +457,44 @@ int mp_plan(int n, int p_begin, int p_end, MpPlan* p) {
     p->nchunk = (pre + p->chunk - 1) / p->chunk;
     p->nvec = p->n_loc + 1 + p->nchunk;
     size_t off = 0;
-    p->off_v = off;     off += ((size_t)p->nvec * p->N * sizeof(double) + 255) / 256 * 256;
+    p->off_v = off;     off += ((size_t)p->nvec * p->N * elem + 255) / 256 * 256;
     p->off_block = off; off += ((size_t)(p->tiles_last + 1) * sizeof(double) + 255) / 256 * 256;
     p->total = off;
+    return 0;
+}
+
+// launches of one evaluation for q type Q and storage type TS
+template <typename Q, typename TS>
+int mp_run(const MpPlan& p, int bit_begin, double a, const Q* q, const TS* S_cols, const double* r_sum, TS* V,
+           double* u, double* blockpart, double* ksd_part, int* launches, cudaStream_t st) {
+    TNK_CUDA_OK(cudaFuncSetAttribute(mp_first_kernel<Q, TS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMpSmem));
+    TNK_CUDA_OK(cudaFuncSetAttribute(mp_last_kernel<Q, TS, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMpSmem));
+    TNK_CUDA_OK(cudaFuncSetAttribute(mp_last_kernel<Q, TS, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMpSmem));
+    TNK_CUDA_OK(cudaFuncSetAttribute(mp_transform_kernel<TS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMpSmem));
+    mp_first_kernel<Q, TS><<<(unsigned)(p.tiles_first * p.nvec), kMpThreads, kMpSmem, st>>>(
+        p.T, p.N, bit_begin, p.n_loc, p.pre_cnt, p.chunk, p.nchunk, p.blocked, p.last.logW, p.group_log, q, S_cols, V, a);
+    TNK_CUDA_OK(cudaGetLastError());
+    ++*launches;
+    for (int m = 0; m < p.n_mid; ++m) {
+        const MpPass& ps = p.mid[m];
+        dim3 grid((unsigned)(p.N >> (ps.g + ps.logW)), (unsigned)p.nvec, 1);
+        mp_transform_kernel<TS><<<grid, kMpThreads, kMpSmem, st>>>(V, p.N, ps.b0, ps.g, ps.logW, a);
+        TNK_CUDA_OK(cudaGetLastError());
+        ++*launches;
+    }
+    const MpPass& ps = p.last;
+    const TS* S2 = S_cols + (size_t)p.n_loc * p.N;       // the copy in the last-pass layout
+    const unsigned grid = (unsigned)p.tiles_last;
+    if (p.blocked && ps.g >= 3)
+        mp_last_kernel<Q, TS, true><<<grid, kMpThreads, kMpSmem, st>>>(p.N, ps.b0, ps.g, ps.logW, bit_begin, p.n_loc, p.nchunk,
+                                                                     p.flip_split, p.blocked, q, S2, r_sum, V, u, blockpart, a);
+    else
+        mp_last_kernel<Q, TS, false><<<grid, kMpThreads, kMpSmem, st>>>(p.N, ps.b0, ps.g, ps.logW, bit_begin, p.n_loc, p.nchunk,
+                                                                      p.flip_split, p.blocked, q, S2, r_sum, V, u, blockpart, a);
+    TNK_CUDA_OK(cudaGetLastError());
+    mp_scalar_kernel<<<1, 256, 0, st>>>(blockpart, p.tiles_last, ksd_part);
+    TNK_CUDA_OK(cudaGetLastError());
+    *launches += 2;
     return 0;
 }
 
@@ -467,34 +506,42 @@ extern "C" int tnk_modeproduct_plan_limit(int max_row_bits) {
     return prev;
 }
 
-extern "C" size_t tnk_ksd_modeproduct_workspace_bytes(int n_latent, int bit_begin, int bit_end) {
+extern "C" size_t tnk_ksd_modeproduct_workspace_bytes(int n_latent, int bit_begin, int bit_end, int storage) {
     MpPlan p;
-    if (mp_plan(n_latent, bit_begin, bit_end, &p)) return 0;
+    if (mp_plan(n_latent, bit_begin, bit_end, storage, &p)) return 0;
     return p.total;
 }
 
-extern "C" int tnk_modeproduct_tables(int n_latent, const double* ST64, int bit_begin, int bit_end,
-                                      double* S_cols, double* r_sum, void* stream) {
+extern "C" int tnk_modeproduct_tables(int n_latent, const double* ST64, int bit_begin, int bit_end, int storage,
+                                      void* S_cols, double* r_sum, void* stream) {
     MpPlan p;
-    TNK_REQUIRE(mp_plan(n_latent, bit_begin, bit_end, &p) == 0, "tnk_modeproduct_tables: bad arguments n=%d bits=[%d,%d)",
-                n_latent, bit_begin, bit_end);
+    TNK_REQUIRE(mp_plan(n_latent, bit_begin, bit_end, storage, &p) == 0,
+                "tnk_modeproduct_tables: bad arguments n=%d bits=[%d,%d) storage=%d", n_latent, bit_begin, bit_end, storage);
     TNK_REQUIRE(ST64 && S_cols && r_sum, "tnk_modeproduct_tables: NULL pointer argument");
     TnkGeom geo;
     TNK_REQUIRE(tnk_geom(n_latent, TNK_PREC_FP64, &geo) == 0, "tnk_modeproduct_tables: unsupported n=%d", n_latent);
     const unsigned blocks = (unsigned)((p.N + 255) / 256);
-    mp_tables_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(geo.np, p.N, bit_begin, p.n_loc, p.blocked, p.last.logW, ST64,
-                                                               S_cols, S_cols + (size_t)p.n_loc * p.N, r_sum);
+    cudaStream_t st = (cudaStream_t)stream;
+    if (storage == TNK_MP_STORE_FP32) {
+        float* S = (float*)S_cols;
+        mp_tables_kernel<float><<<blocks, 256, 0, st>>>(geo.np, p.N, bit_begin, p.n_loc, p.blocked, p.last.logW, ST64,
+                                                        S, S + (size_t)p.n_loc * p.N, r_sum);
+    } else {
+        double* S = (double*)S_cols;
+        mp_tables_kernel<double><<<blocks, 256, 0, st>>>(geo.np, p.N, bit_begin, p.n_loc, p.blocked, p.last.logW, ST64,
+                                                         S, S + (size_t)p.n_loc * p.N, r_sum);
+    }
     TNK_CUDA_OK(cudaGetLastError());
     return 0;
 }
 
-extern "C" int tnk_ksd_modeproduct(int n_latent, double length_scale, const void* q, int q_dtype,
-                                   const double* S_cols, const double* r_sum, int bit_begin, int bit_end,
+extern "C" int tnk_ksd_modeproduct(int n_latent, double length_scale, const void* q, int q_dtype, int storage,
+                                   const void* S_cols, const double* r_sum, int bit_begin, int bit_end,
                                    double* u, double* ksd_part,
                                    void* workspace, size_t workspace_bytes, int* n_launch, void* stream) {
     MpPlan p;
-    TNK_REQUIRE(mp_plan(n_latent, bit_begin, bit_end, &p) == 0, "tnk_ksd_modeproduct: bad arguments n=%d bits=[%d,%d)",
-                n_latent, bit_begin, bit_end);
+    TNK_REQUIRE(mp_plan(n_latent, bit_begin, bit_end, storage, &p) == 0,
+                "tnk_ksd_modeproduct: bad arguments n=%d bits=[%d,%d) storage=%d", n_latent, bit_begin, bit_end, storage);
     TNK_REQUIRE(q && S_cols && r_sum && u && ksd_part && workspace, "tnk_ksd_modeproduct: NULL pointer argument");
     TNK_REQUIRE(q_dtype == 0 || q_dtype == 1, "tnk_ksd_modeproduct: q_dtype must be 0 (double) or 1 (float)");
     TNK_REQUIRE(workspace_bytes >= p.total, "tnk_ksd_modeproduct: workspace %zu < required %zu", workspace_bytes, p.total);
@@ -511,60 +558,18 @@ extern "C" int tnk_ksd_modeproduct(int n_latent, double length_scale, const void
     TNK_REQUIRE((double)n * length_scale != 0.0, "tnk_ksd_modeproduct: num_vars*length_scale must be non-zero");
     const double a = exp(-1.0 / ((double)n * length_scale));
     unsigned char* ws = (unsigned char*)workspace;
-    double* V = (double*)(ws + p.off_v);
     double* blockpart = (double*)(ws + p.off_block);
-
-    static bool attr_set[64] = {};             // per device: function attributes belong to the device's context
-    int dev = 0;
-    TNK_CUDA_OK(cudaGetDevice(&dev));
-    if (dev < 0 || dev >= 64 || !attr_set[dev]) {
-        TNK_CUDA_OK(cudaFuncSetAttribute(mp_first_kernel<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMpSmem));
-        TNK_CUDA_OK(cudaFuncSetAttribute(mp_first_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMpSmem));
-        TNK_CUDA_OK(cudaFuncSetAttribute(mp_last_kernel<double, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMpSmem));
-        TNK_CUDA_OK(cudaFuncSetAttribute(mp_last_kernel<float, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMpSmem));
-        TNK_CUDA_OK(cudaFuncSetAttribute(mp_last_kernel<double, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMpSmem));
-        TNK_CUDA_OK(cudaFuncSetAttribute(mp_last_kernel<float, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMpSmem));
-        TNK_CUDA_OK(cudaFuncSetAttribute(mp_transform_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMpSmem));
-        if (dev >= 0 && dev < 64) attr_set[dev] = true;
+    int rc;
+    if (storage == TNK_MP_STORE_FP32) {
+        float* V = (float*)(ws + p.off_v);
+        rc = q_dtype == 0 ? mp_run<double, float>(p, bit_begin, a, (const double*)q, (const float*)S_cols, r_sum, V, u, blockpart, ksd_part, &launches, st)
+                          : mp_run<float, float>(p, bit_begin, a, (const float*)q, (const float*)S_cols, r_sum, V, u, blockpart, ksd_part, &launches, st);
+    } else {
+        double* V = (double*)(ws + p.off_v);
+        rc = q_dtype == 0 ? mp_run<double, double>(p, bit_begin, a, (const double*)q, (const double*)S_cols, r_sum, V, u, blockpart, ksd_part, &launches, st)
+                          : mp_run<float, double>(p, bit_begin, a, (const float*)q, (const double*)S_cols, r_sum, V, u, blockpart, ksd_part, &launches, st);
     }
-
-    {
-        const unsigned grid = (unsigned)(p.tiles_first * p.nvec);
-        if (q_dtype == 0)
-            mp_first_kernel<double><<<grid, kMpThreads, kMpSmem, st>>>(p.T, p.N, bit_begin, p.n_loc, p.pre_cnt, p.chunk, p.nchunk,
-                                                                     p.blocked, p.last.logW, p.group_log,
-                                                                     (const double*)q, S_cols, V, a);
-        else
-            mp_first_kernel<float><<<grid, kMpThreads, kMpSmem, st>>>(p.T, p.N, bit_begin, p.n_loc, p.pre_cnt, p.chunk, p.nchunk,
-                                                                    p.blocked, p.last.logW, p.group_log,
-                                                                    (const float*)q, S_cols, V, a);
-        TNK_CUDA_OK(cudaGetLastError());
-        ++launches;
-    }
-    for (int m = 0; m < p.n_mid; ++m) {
-        const MpPass& ps = p.mid[m];
-        dim3 grid((unsigned)(p.N >> (ps.g + ps.logW)), (unsigned)p.nvec, 1);
-        mp_transform_kernel<<<grid, kMpThreads, kMpSmem, st>>>(V, p.N, ps.b0, ps.g, ps.logW, a);
-        TNK_CUDA_OK(cudaGetLastError());
-        ++launches;
-    }
-    {
-        const MpPass& ps = p.last;
-        const double* S2 = S_cols + (size_t)p.n_loc * p.N;       // the copy in the last-pass layout
-        const bool fast = p.blocked && ps.g >= 3;
-        const unsigned grid = (unsigned)p.tiles_last;
-#define TNK_MP_LAST(QT, FAST)                                                                          \
-        mp_last_kernel<QT, FAST><<<grid, kMpThreads, kMpSmem, st>>>(                                       \
-            p.N, ps.b0, ps.g, ps.logW, bit_begin, p.n_loc, p.nchunk, p.flip_split, p.blocked,              \
-            (const QT*)q, S2, r_sum, V, u, blockpart, a)
-        if (q_dtype == 0) { if (fast) TNK_MP_LAST(double, true); else TNK_MP_LAST(double, false); }
-        else              { if (fast) TNK_MP_LAST(float, true);  else TNK_MP_LAST(float, false); }
-#undef TNK_MP_LAST
-        TNK_CUDA_OK(cudaGetLastError());
-        mp_scalar_kernel<<<1, 256, 0, st>>>(blockpart, p.tiles_last, ksd_part);
-        TNK_CUDA_OK(cudaGetLastError());
-        launches += 2;
-    }
+    if (rc) return rc;
     if (n_launch) *n_launch = launches;
     return 0;
 }

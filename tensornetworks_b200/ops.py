@@ -158,11 +158,19 @@ class SteinTables:
                 launch_counter["kernels"] += 1
         return self._ST64
 
-    def ksd_modeproduct(self, q, bit_begin=0, bit_end=None):
+    def ksd_modeproduct(self, q, bit_begin=0, bit_end=None, storage=None):
         """Partial of u = K_p q over score components (bit positions) [bit_begin, bit_end) for all rows,
-        and the matching partial of q.u, through the Kronecker factorisation (O(n^2 2^n), fp64).
-        Partials over disjoint bit ranges add up to the pair kernel's result."""
+        and the matching partial of q.u, through the Kronecker factorisation (O(n^2 2^n), fp64 arithmetic).
+        Partials over disjoint bit ranges add up to the pair kernel's result.
+        storage: "fp64" keeps the score columns and the transformed vectors in fp64 in HBM (results to ~1e-15
+        of the fp64 pair kernel), "fp32" in fp32 (half the traffic, errors of the fp32 pair kernel's size);
+        default: "fp64" for fp64-mode tables, "fp32" for fp32/tc32-mode tables."""
         bit_end = self.n if bit_end is None else bit_end
+        if storage is None:
+            storage = "fp64" if self.dtype == torch.float64 else "fp32"
+        if storage not in _lib.MP_STORE:
+            raise ValueError(f"storage must be one of {tuple(_lib.MP_STORE)}")
+        code = _lib.MP_STORE[storage]
         if q.device != self.device or q.dim() != 1 or q.numel() != self.N:
             raise ValueError(f"q must be a 1-D tensor of {self.N} entries on {self.device}")
         if q.dtype not in (torch.float32, torch.float64):
@@ -170,15 +178,16 @@ class SteinTables:
         q = q.contiguous()
         lib = _lib.load()
         with torch.cuda.device(self.device):
-            key = ("mp", bit_begin, bit_end)
+            key = ("mp", bit_begin, bit_end, storage)
             if key not in self._ws:
-                nbytes = lib.tnk_ksd_modeproduct_workspace_bytes(self.n, bit_begin, bit_end)
+                nbytes = lib.tnk_ksd_modeproduct_workspace_bytes(self.n, bit_begin, bit_end, code)
                 if nbytes == 0:
                     raise RuntimeError("tnk_ksd_modeproduct_workspace_bytes rejected the bit range")
                 # one-off per table and bit range: column-major score components and the row sums of r
-                s_cols = torch.empty((2, max(bit_end - bit_begin, 1), self.N), dtype=torch.float64, device=self.device)
+                s_cols = torch.empty((2, max(bit_end - bit_begin, 1), self.N), device=self.device,
+                                     dtype=torch.float64 if storage == "fp64" else torch.float32)
                 r_sum = torch.empty(self.N, dtype=torch.float64, device=self.device)
-                _lib.check(lib.tnk_modeproduct_tables(self.n, _ptr(self._st64()), bit_begin, bit_end, _ptr(s_cols),
+                _lib.check(lib.tnk_modeproduct_tables(self.n, _ptr(self._st64()), bit_begin, bit_end, code, _ptr(s_cols),
                                                       _ptr(r_sum), _stream_ptr(self.device)), "tnk_modeproduct_tables")
                 launch_counter["kernels"] += 1
                 if self.dtype != torch.float64:
@@ -188,7 +197,7 @@ class SteinTables:
             u = torch.empty(self.N, dtype=torch.float64, device=self.device)
             part = torch.empty(1, dtype=torch.float64, device=self.device)
             launched = ctypes.c_int(0)
-            _lib.check(lib.tnk_ksd_modeproduct(self.n, self.length_scale, _ptr(q), 0 if q.dtype == torch.float64 else 1,
+            _lib.check(lib.tnk_ksd_modeproduct(self.n, self.length_scale, _ptr(q), 0 if q.dtype == torch.float64 else 1, code,
                                                _ptr(s_cols), _ptr(r_sum), bit_begin, bit_end, _ptr(u), _ptr(part),
                                                _ptr(ws), ws.numel(), ctypes.byref(launched), _stream_ptr(self.device)),
                        "tnk_ksd_modeproduct")

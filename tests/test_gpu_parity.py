@@ -179,8 +179,10 @@ def test_modeproduct_sprinkler_golden(ops, golden):
         K, g = _eval_mp(ops, tabs, golden[f"spr_q_{name}"])
         _check(K, g, float(golden[f"spr_K_{name}"]), golden[f"spr_g_{name}"], 1e-9)
     t2 = _tables(ops, bn, {'W': 1}, ['C', 'S', 'R'], "fp32", length_scale=0.5)   # fp32 tables build ST64 lazily
-    K, g = _eval_mp(ops, t2, golden["spr_q_ramp"])
-    _check(K, g, float(golden["spr_K_ramp_ls0.5"]), golden["spr_g_ramp_ls0.5"], 1e-9)
+    K, g = _eval_mp(ops, t2, golden["spr_q_ramp"])                               # and default to fp32 storage
+    _check(K, g, float(golden["spr_K_ramp_ls0.5"]), golden["spr_g_ramp_ls0.5"], 1e-5)
+    u, part = t2.ksd_modeproduct(torch.as_tensor(golden["spr_q_ramp"], dtype=torch.float64, device="cuda"), storage="fp64")
+    _check(float(part), 2.0 * u.cpu().numpy(), float(golden["spr_K_ramp_ls0.5"]), golden["spr_g_ramp_ls0.5"], 1e-9)
 
 
 @pytest.mark.parametrize("n,seed,nh", RANDOM_CASES)
@@ -228,6 +230,29 @@ def test_modeproduct_multi_pass_plans(ops, n, limit):
     assert float((ua + ub - u0).abs().max()) <= 1e-12 * den
     assert abs(float(K1) - float(K0)) <= 1e-12 * abs(float(K0))
     assert abs(float(Ka + Kb) - float(K0)) <= 1e-12 * abs(float(K0))
+
+
+@pytest.mark.parametrize("n,seed", [(5, 1), (12, 0), (13, 2), (15, 0), (18, 1), (20, 0)])
+def test_modeproduct_fp32_storage(ops, n, seed):
+    """storage="fp32" (score columns and transformed vectors in fp32 in HBM, fp64 arithmetic) against the fp64
+    storage: the fp32-mode tolerance with a wide margin, for fp64 and fp32 q, full and split bit ranges."""
+    bn, lat, obs, x = random_binary_bn(n, seed=seed)
+    tabs = _tables(ops, bn, x, lat, "fp64")
+    q = random_q(1 << n, seed=seed).cuda()
+    u64, k64 = tabs.ksd_modeproduct(q)                      # fp64 tables default to fp64 storage
+    u32, k32 = tabs.ksd_modeproduct(q, storage="fp32")
+    ua, ka = tabs.ksd_modeproduct(q.float(), 0, n // 2, storage="fp32")
+    ub, kb = tabs.ksd_modeproduct(q.float(), n // 2, n, storage="fp32")
+    torch.cuda.synchronize()
+    den = u64.abs().max().item()
+    assert (u32 - u64).abs().max().item() <= 2e-6 * den
+    assert abs(k32.item() - k64.item()) <= 2e-6 * abs(k64.item())
+    assert (ua + ub - u64).abs().max().item() <= 2e-6 * den
+    t32 = _tables(ops, bn, x, lat, "fp32")                  # fp32 tables default to fp32 storage
+    ud, kd = t32.ksd_modeproduct(q)
+    assert (ud - u64).abs().max().item() <= 2e-6 * den
+    with pytest.raises(ValueError):
+        tabs.ksd_modeproduct(q, storage="bf16")
 
 
 def test_modeproduct_matches_pair_kernel_n20(ops):
