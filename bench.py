@@ -293,33 +293,41 @@ def run_ours(args):
     mp_ms = None
     if world == 1:
         m0, m1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        tables.ksd_modeproduct(q_dev)               # builds the column-major score copies once
-        times = []
-        for _ in range(5):
-            flush.zero_()
-            m0.record()
-            u_mp, part_mp = tables.ksd_modeproduct(q_dev)
-            m1.record()
-            torch.cuda.synchronize()
-            times.append(m0.elapsed_time(m1))
-        mp_ms = float(np.mean(times))
+        mp_times = {}
+        for mp_storage in ("fp32", "fp64"):
+            tables.ksd_modeproduct(q_dev, storage=mp_storage)   # builds the column-major score copies once
+            times = []
+            for _ in range(5):
+                flush.zero_()
+                m0.record()
+                u_mp, part_mp = tables.ksd_modeproduct(q_dev, storage=mp_storage)
+                m1.record()
+                torch.cuda.synchronize()
+                times.append(m0.elapsed_time(m1))
+            mp_times[mp_storage] = float(np.mean(times))
+        mp_ms = mp_times["fp64"]                                # the roofline line is the fp64-storage variant
         mp_K = float(part_mp.item())
         mp_err = float(((u_mp - u).abs().max() / u.abs().max()).item())
         tables._ws = {k: v for k, v in tables._ws.items() if not (isinstance(k, tuple) and k and k[0] == "mp")}
         del u_mp
     en0, en1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     enum_ms, joint_ms = [], []
-    enum_reps = 8       # back to back: one call is ~60 us of GPU work behind ~40 us of host launch path
+    enum_reps = 8       # back to back into the same buffers: one call is ~60 us of GPU work, less than its host path
+    from tensornetworks_b200 import _lib as tnk_lib
+    t_tmp = ops.SteinTables(tables.P, n, precision="fp32", keep_scores=True)             # K2 alone (score tables)
+    np_tmp = t_tmp.np
     for _ in range(3):
         flush.zero_()
         en0.record()
         for _ in range(enum_reps):
-            t_tmp = ops.SteinTables(tables.P, n, precision="fp32", keep_scores=True)     # K2 alone (score tables)
+            tnk_lib.check(tnk_lib.load().tnk_score(n, t_tmp.length_scale, t_tmp.P.data_ptr(), t_tmp.S.data_ptr(), t_tmp.prec_code,
+                                                   t_tmp.ST.data_ptr(), t_tmp.Cst.data_ptr(),
+                                                   torch.cuda.current_stream(device).cuda_stream), "tnk_score")
         en1.record()
         torch.cuda.synchronize()
         enum_ms.append(en0.elapsed_time(en1) / enum_reps)
-        np_tmp = t_tmp.np
-        del t_tmp
+    del t_tmp
+    for _ in range(3):
         t0 = time.perf_counter()
         ops.joint_table(bn, x, lat, device=device)                                  # K1 incl. host flattening + CPT upload
         torch.cuda.synchronize()
@@ -435,14 +443,12 @@ def main():
                                   "frac": alu_ach / r["peak_rate"], "lane_ops_per_pair": w_lane,
                                   "peak_source": "tnk_alu_peak FMA-chain probe measured in this run"}
         if r["mp_ms"] is not None:
-            mp_storage = "fp64" if args.precision == "fp64" else "fp32"     # SteinTables.ksd_modeproduct's default for these tables
-            mp_elem = 8.0 if mp_storage == "fp64" else 4.0
-            # S twice, n+2 vectors written and read once (storage type); q twice, r_sum, u (fp64)
-            mp_bytes = mp_elem * (1 << n) * (2 * n + 2 * (n + 2)) + 8.0 * (1 << n) * 4
+            # S twice, n+2 vectors written and read once, q twice, r_sum, u - all fp64 in this variant
+            mp_bytes = 8.0 * (1 << n) * (2 * n + 2 * (n + 2) + 4)
             hbm_peak = load_measured_peaks().get("hbm_gbs") or 6650.0
             mp_gbs = mp_bytes / (r["mp_ms"] * 1e-3) / 1e9
             line["modeproduct"] = {"kernels": "mp_first_kernel + mp_last_kernel (fp64 arithmetic, O(n^2 2^n), same K and gradient)",
-                                   "storage": mp_storage,
+                                   "storage": "fp64", "ms_fp32_storage": r["mp_times"]["fp32"],
                                    "ms": r["mp_ms"], "effective_value": pairs / (r["mp_ms"] * 1e-3), "unit": UNIT,
                                    "bound": "hbm", "algorithmic_bytes": mp_bytes, "achieved": mp_gbs, "peak": hbm_peak,
                                    "roofline_unit": "GB/s", "frac": mp_gbs / hbm_peak, "ksd_sq": r["mp_K"],
@@ -453,7 +459,7 @@ def main():
         line["enumeration"] = {"score_kernel_ms": r["enum_best"], "score_kernel_algorithmic_bytes": enum_bytes,
                                "score_kernel_GB/s": enum_bytes / (r["enum_best"] * 1e-3) / 1e9, "peak_GB/s": hbm,
                                "score_kernel_frac": enum_bytes / (r["enum_best"] * 1e-3) / 1e9 / hbm,
-                               "score_kernel_timing": f"{r['enum_reps']} back-to-back table builds between two events (outputs 256 MB > L2)",
+                               "score_kernel_timing": f"{r['enum_reps']} back-to-back tnk_score calls between two events (outputs 256 MB > L2)",
                                "joint_table_ms_incl_host_flatten_and_upload": r["joint_best"],
                                "joint_table_bytes": 8.0 * (1 << n)}
         if world == 1:

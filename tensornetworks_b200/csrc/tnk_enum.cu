@@ -116,6 +116,17 @@ extern "C" int tnk_bn_joint(int n_latent, int n_hidden, int n_nodes,
 // idx ^ (1 << (n-1-k)), so the n neighbour probabilities are gathers from P itself.
 // Each CTA computes 256 rows into shared memory and writes them out coalesced.
 // ------------------------------------------------------------------------------------
+// a / p, correctly rounded, from the correctly rounded reciprocal rp = RN(1/p) shared by the n divisions of a
+// state: q0 = a rp is faithful, and each residual step q += (a - q p) rp (exact residual by FMA) then returns
+// RN(a/p) (Markstein's theorem; two steps for margin).  Probabilities keep every intermediate in the normal
+// range (|p| >= 1e-12, 0 <= a <= 1).  The oracle divides with '/', the parity tests compare the tables with ==.
+__device__ __forceinline__ double div_by(double a, double p, double rp) {
+    double q = __dmul_rn(a, rp);
+    q = __fma_rn(__fma_rn(-q, p, a), rp, q);
+    q = __fma_rn(__fma_rn(-q, p, a), rp, q);
+    return q;
+}
+
 template <typename T>
 __global__ void __launch_bounds__(256)
 score_kernel(int n, int np, int64_t N, double alpha, double gamma,
@@ -135,15 +146,28 @@ score_kernel(int n, int np, int64_t N, double alpha, double gamma,
     if (i < N) {
         const double p = P[i];
         const bool dead = fabs(p) < 1e-12;  // stein_utils.py:126
-        for (int k = 0; k < n; ++k) {
-            const int bit = n - 1 - k;
-            double s = 0.0;
-            if (!dead) s = __dsub_rn(1.0, __ddiv_rn(P[i ^ ((int64_t)1 << bit)], p));  // :134
-            if (S64) sS[tid * ns + k] = s;
-            if (ST) sT[tid * nps + bit] = (T)s;
-            const double r = 1.0 - s;
-            Rsum += r;
-            if ((i >> bit) & 1) rho0 += r;
+        const double rp = dead ? 0.0 : __drcp_rn(p);
+        for (int k0 = 0; k0 < n; k0 += 4) {          // four flipped reads in flight; arithmetic in the original order
+            double pf[4];
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+                const int bit = n - 1 - (k0 + c);
+                pf[c] = (k0 + c < n && !dead) ? P[i ^ ((int64_t)1 << bit)] : 0.0;
+            }
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+                const int k = k0 + c;
+                if (k < n) {
+                    const int bit = n - 1 - k;
+                    double s = 0.0;
+                    if (!dead) s = __dsub_rn(1.0, div_by(pf[c], p, rp));  // :134
+                    if (S64) sS[tid * ns + k] = s;
+                    if (ST) sT[tid * nps + bit] = (T)s;
+                    const double r = 1.0 - s;
+                    Rsum += r;
+                    if ((i >> bit) & 1) rho0 += r;
+                }
+            }
         }
         if (Cst) Cst[i] = (T)(alpha * Rsum + gamma * rho0);
     } else if (Cst) {
