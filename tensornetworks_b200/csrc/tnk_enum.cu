@@ -127,32 +127,39 @@ __device__ __forceinline__ double div_by(double a, double p, double rp) {
     return q;
 }
 
-template <typename T>
+// NP = padded score length (compile time: the loops over score components unroll and the shared-memory
+// strides are constants), n <= NP at run time.
+template <typename T, int NP>
 __global__ void __launch_bounds__(256)
-score_kernel(int n, int np, int64_t N, double alpha, double gamma,
+score_kernel(int n, int64_t N, double alpha, double gamma,
              const double* __restrict__ P, double* __restrict__ S64,
              T* __restrict__ ST, T* __restrict__ Cst) {
-    // Rows are staged in shared memory with ODD strides (ns doubles, nps elements of T) so that the
-    // per-thread row writes are bank-conflict-free; the copy-out then walks the tile linearly.
+    // Rows are staged in shared memory with the ODD stride NP + 1 so that the per-thread row writes are
+    // bank-conflict-free; the copy-out then walks the tile linearly.
+    constexpr int kStride = NP + 1;
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    const int ns = n | 1, nps = np + 1;
-    double* sS = reinterpret_cast<double*>(smem_raw);                                     // [256][ns], only if S64
-    T* sT = reinterpret_cast<T*>(smem_raw + (S64 ? (size_t)256 * ns * sizeof(double) : 0)); // [256][nps]
+    double* sS = reinterpret_cast<double*>(smem_raw);                                          // [256][NP+1], only if S64
+    T* sT = reinterpret_cast<T*>(smem_raw + (S64 ? (size_t)256 * kStride * sizeof(double) : 0)); // [256][NP+1]
     const int tid = threadIdx.x;
     const int64_t base = (int64_t)blockIdx.x * 256;
     const int64_t i = base + tid;
     double Rsum = 0.0, rho0 = 0.0;
-    if (ST) for (int p = 0; p < np; ++p) sT[tid * nps + p] = (T)0;
+    if (ST) {
+#pragma unroll
+        for (int p = 0; p < NP; ++p) sT[tid * kStride + p] = (T)0;
+    }
     if (i < N) {
         const double p = P[i];
         const bool dead = fabs(p) < 1e-12;  // stein_utils.py:126
         const double rp = dead ? 0.0 : __drcp_rn(p);
-        for (int k0 = 0; k0 < n; k0 += 4) {          // four flipped reads in flight; arithmetic in the original order
+        const uint32_t iu = (uint32_t)i;     // n <= 30
+#pragma unroll
+        for (int k0 = 0; k0 < NP; k0 += 4) {         // four flipped reads in flight; arithmetic in the original order
             double pf[4];
 #pragma unroll
             for (int c = 0; c < 4; ++c) {
-                const int bit = n - 1 - (k0 + c);
-                pf[c] = (k0 + c < n && !dead) ? P[i ^ ((int64_t)1 << bit)] : 0.0;
+                const int k = k0 + c;
+                pf[c] = (k < n && !dead) ? P[iu ^ (1u << (n - 1 - k))] : 0.0;
             }
 #pragma unroll
             for (int c = 0; c < 4; ++c) {
@@ -161,11 +168,11 @@ score_kernel(int n, int np, int64_t N, double alpha, double gamma,
                     const int bit = n - 1 - k;
                     double s = 0.0;
                     if (!dead) s = __dsub_rn(1.0, div_by(pf[c], p, rp));  // :134
-                    if (S64) sS[tid * ns + k] = s;
-                    if (ST) sT[tid * nps + bit] = (T)s;
+                    if (S64) sS[tid * kStride + k] = s;
+                    if (ST) sT[tid * kStride + bit] = (T)s;
                     const double r = 1.0 - s;
                     Rsum += r;
-                    if ((i >> bit) & 1) rho0 += r;
+                    if ((iu >> bit) & 1u) rho0 += r;
                 }
             }
         }
@@ -178,20 +185,54 @@ score_kernel(int n, int np, int64_t N, double alpha, double gamma,
         const int live = (int)(N - base < 256 ? (N - base > 0 ? N - base : 0) : 256) * n;
         const int dq = 256 / n, dr = 256 % n;              // element t = tid + 256 j sits in row t / n, column t % n
         int row = tid / n, col = tid % n;
+        double* out = S64 + base * n;
         for (int t = tid; t < live; t += 256) {
-            S64[base * n + t] = sS[row * ns + col];
+            out[t] = sS[row * kStride + col];
             row += dq; col += dr;
             if (col >= n) { col -= n; ++row; }
         }
     }
     if (ST) {
-        const int dq = 256 / np, dr = 256 % np;
-        int row = tid / np, col = tid % np;
-        for (int t = tid; t < 256 * np; t += 256) {
-            ST[base * np + t] = sT[row * nps + col];
-            row += dq; col += dr;
-            if (col >= np) { col -= np; ++row; }
+        // 16-byte stores: a row of NP elements is NP*sizeof(T)/16 chunks
+        constexpr int kPer = 16 / (int)sizeof(T);           // elements per chunk
+        constexpr int kChunksPerRow = NP / kPer;
+        T* out = ST + base * NP;
+#pragma unroll
+        for (int c = 0; c < kChunksPerRow; ++c) {
+            const int ch = tid + 256 * c;                   // chunk index in the tile
+            const int row = ch / kChunksPerRow, col = (ch % kChunksPerRow) * kPer;
+            T v[kPer];
+#pragma unroll
+            for (int e = 0; e < kPer; ++e) v[e] = sT[row * kStride + col + e];
+            *reinterpret_cast<uint4*>(out + (size_t)ch * kPer) = *reinterpret_cast<const uint4*>(v);
         }
+    }
+}
+
+template <typename T, int NP>
+int launch_score(int n, int64_t N, int64_t rows, double alpha, double gamma, const double* P, double* S64,
+                 T* ST, T* Cst, cudaStream_t st) {
+    const unsigned blocks = (unsigned)((rows + 255) / 256);
+    const size_t smem = (size_t)256 * (NP + 1) * ((S64 ? sizeof(double) : 0) + sizeof(T));
+    TNK_CUDA_OK(cudaFuncSetAttribute(score_kernel<T, NP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    score_kernel<T, NP><<<blocks, 256, smem, st>>>(n, N, alpha, gamma, P, S64, ST, Cst);
+    TNK_CUDA_OK(cudaGetLastError());
+    return 0;
+}
+
+template <typename T>
+int dispatch_score(int np, int n, int64_t N, int64_t rows, double alpha, double gamma, const double* P, double* S64,
+                   T* ST, T* Cst, cudaStream_t st) {
+    switch (np) {
+        case 4:  return launch_score<T, 4>(n, N, rows, alpha, gamma, P, S64, ST, Cst, st);
+        case 8:  return launch_score<T, 8>(n, N, rows, alpha, gamma, P, S64, ST, Cst, st);
+        case 12: return launch_score<T, 12>(n, N, rows, alpha, gamma, P, S64, ST, Cst, st);
+        case 16: return launch_score<T, 16>(n, N, rows, alpha, gamma, P, S64, ST, Cst, st);
+        case 20: return launch_score<T, 20>(n, N, rows, alpha, gamma, P, S64, ST, Cst, st);
+        case 24: return launch_score<T, 24>(n, N, rows, alpha, gamma, P, S64, ST, Cst, st);
+        case 28: return launch_score<T, 28>(n, N, rows, alpha, gamma, P, S64, ST, Cst, st);
+        case 32: return launch_score<T, 32>(n, N, rows, alpha, gamma, P, S64, ST, Cst, st);
+        default: tnk_set_error("tnk_score: no kernel instance for padded length %d", np); return 2;
     }
 }
 
@@ -211,16 +252,11 @@ extern "C" int tnk_score(int n_latent, double length_scale, const double* P,
         gamma = a - 1.0 / a;
     }
     const int64_t rows = ST ? g.n_pad : N;
-    const unsigned blocks = (unsigned)((rows + 255) / 256);
-    const size_t smem = (size_t)256 * ((S64 ? (size_t)(n | 1) * sizeof(double) : 0) + (size_t)(g.np + 1) * g.elem);
     cudaStream_t st = (cudaStream_t)stream;
-    if (g.elem == 4) {
-        TNK_CUDA_OK(cudaFuncSetAttribute(score_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        score_kernel<float><<<blocks, 256, smem, st>>>(n, g.np, N, alpha, gamma, P, S64, (float*)ST, (float*)Cst);
-    } else {
-        TNK_CUDA_OK(cudaFuncSetAttribute(score_kernel<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        score_kernel<double><<<blocks, 256, smem, st>>>(n, g.np, N, alpha, gamma, P, S64, (double*)ST, (double*)Cst);
-    }
+    const int rc = g.elem == 4
+        ? dispatch_score<float>(g.np, n, N, rows, alpha, gamma, P, S64, (float*)ST, (float*)Cst, st)
+        : dispatch_score<double>(g.np, n, N, rows, alpha, gamma, P, S64, (double*)ST, (double*)Cst, st);
+    if (rc) return rc;
     TNK_CUDA_OK(cudaGetLastError());
     return 0;
 }
