@@ -126,6 +126,43 @@ def test_vs_modeproduct_oracle(ops, n, seed, precision):
     _check(K, g, Kref, gref, TOL[precision])
 
 
+def _deterministic_bn(n):
+    """Chain Z0 -> ... -> Z(n-1) in which Z3 copies Z2 and Z6 is the negation of Z5 (CPT entries exactly 0 and 1):
+    three quarters of the states have p(x,z) = 0 (zero score rows, stein_utils.py:126-128) and live states have
+    dead neighbours (ratio 0, score 1)."""
+    bn = BayesianNetwork()
+    bn.add_node('Z0', cpt={(): {0: 0.35, 1: 0.65}})
+    for k in range(1, n):
+        if k == 3:
+            cpt = {(0,): {0: 1.0, 1: 0.0}, (1,): {0: 0.0, 1: 1.0}}
+        elif k == 6:
+            cpt = {(0,): {0: 0.0, 1: 1.0}, (1,): {0: 1.0, 1: 0.0}}
+        else:
+            cpt = {(0,): {0: 0.2 + 0.05 * k, 1: 0.8 - 0.05 * k}, (1,): {0: 0.6 - 0.03 * k, 1: 0.4 + 0.03 * k}}
+        bn.add_node(f'Z{k}', cpt=cpt, parent_names=[f'Z{k-1}'])
+    bn.add_node('X', cpt={(0, 0): {0: 0.9, 1: 0.1}, (0, 1): {0: 0.5, 1: 0.5}, (1, 0): {0: 0.3, 1: 0.7},
+                          (1, 1): {0: 0.05, 1: 0.95}}, parent_names=['Z0', f'Z{n-1}'])
+    return bn, [f'Z{k}' for k in range(n)], {'X': 1}
+
+
+@pytest.mark.parametrize("precision", ["fp64", "fp32", "tc32"])
+def test_zero_probability_states(ops, precision):
+    n = 9
+    bn, lat, x = _deterministic_bn(n)
+    tabs = _tables(ops, bn, x, lat, precision)
+    P = orc.joint_table(bn, x, lat)
+    S = orc.score_table(P, n)
+    assert (P == 0).sum() == 3 * (1 << n) // 4 and np.all(S[P == 0] == 0) and np.any(S == 1.0)
+    assert np.array_equal(tabs.P.cpu().numpy(), P)
+    assert np.array_equal(tabs.S.cpu().numpy(), S)
+    q = random_q(1 << n, seed=4).numpy()
+    Kref, gref = orc.ksd_dense(q, S, n)
+    K, g = _eval(ops, tabs, q)
+    _check(K, g, Kref, gref, TOL[precision])
+    Km, gm = _eval_mp(ops, tabs, q)                      # mode-product, storage following the table precision
+    _check(Km, gm, Kref, gref, 1e-9 if precision == "fp64" else 1e-5)
+
+
 def test_row_ranges_add_up(ops):
     """Sharding property: disjoint row ranges reproduce the full u and K (incl. ranges that are
     not aligned to the kernel's row block)."""
