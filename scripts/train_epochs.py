@@ -23,6 +23,7 @@ def main():
     ap.add_argument("--epochs", type=int, default=2)
     ap.add_argument("--precision", default="tc32")
     ap.add_argument("--algorithm", default="pairs")
+    ap.add_argument("--cuda-graph", action="store_true", help="replay the epoch as CUDA graphs (single GPU, Adam)")
     ap.add_argument("--profile", action="store_true", help="print the top CUDA ops of the timed epochs (torch.profiler)")
     args = ap.parse_args()
     world, rank, local = int(os.environ.get("WORLD_SIZE", "1")), int(os.environ.get("RANK", "0")), int(os.environ.get("LOCAL_RANK", "0"))
@@ -35,7 +36,8 @@ def main():
     bn, lat, obs, x = random_binary_bn(args.n, seed=0)
     t0 = time.perf_counter()
     vi = KSDVariationalInference(bn, lat, obs, {"use_logits": True, "conditioning_dim": 0}, device=dev,
-                                 precision=args.precision, compute_device=dev, algorithm=args.algorithm)
+                                 precision=args.precision, compute_device=dev, algorithm=args.algorithm,
+                                 cuda_graph=args.cuda_graph)
     build_s = time.perf_counter() - t0
     t0 = time.perf_counter()
     hist = vi.train(x, num_epochs=1, lr_born_machine=0.05, verbose=False)      # warm-up epoch: tables, workspaces
@@ -57,7 +59,7 @@ def main():
         per_epoch = t.item()
     if rank == 0:
         print(json.dumps({"workload": f"KSDVariationalInference.train, synthetic random binary BN, {args.n} latent vars",
-                          "n_gpus": world, "precision": args.precision, "algorithm": args.algorithm,
+                          "n_gpus": world, "precision": args.precision, "algorithm": args.algorithm, "cuda_graph": args.cuda_graph,
                           "s_per_epoch": per_epoch, "pairs_per_s": 4.0 ** args.n / per_epoch if args.algorithm == "pairs" else None,
                           "epochs_timed": args.epochs, "first_train_call_s": first_s, "constructor_s": build_s,
                           "loss_ksd": hist["loss_ksd"][-1]}), flush=True)

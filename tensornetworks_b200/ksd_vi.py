@@ -79,13 +79,14 @@ def posterior_vector(true_posterior, num_latent_vars, device):
 class KSDVariationalInference:
     def __init__(self, bayesian_network, latent_vars_names, observed_vars_names,
                  born_machine_config, base_kernel_length_scale=1.0, device='cpu',
-                 *, precision="fp64", compute_device="cuda", algorithm="pairs"):
+                 *, precision="fp64", compute_device="cuda", algorithm="pairs", cuda_graph=False):
         self.bn = bayesian_network
         self.latent_vars_names = latent_vars_names
         self.observed_vars_names = observed_vars_names
         self.num_latent_vars = len(latent_vars_names)
         self.num_observed_vars = len(observed_vars_names)
         self.device = device
+        self.cuda_graph = cuda_graph
         # the reference overrides the caller's init_method (ksd_vi.py:30)
         born_machine_config = {**born_machine_config, 'init_method': 'small_random'}
         self.born_machine = ClassicalBornMachine(num_latent_vars=self.num_latent_vars,
@@ -136,6 +137,60 @@ class KSDVariationalInference:
                 self._exchange = False
         return self._exchange or None
 
+    def _graph_supported(self, params, optimizer_type):
+        """The epoch can be replayed as CUDA graphs when everything it launches is on one CUDA device and
+        fixed from epoch to epoch: unconditional Born machine (no dropout), Adam, a single process."""
+        import torch.distributed as dist
+        if not (self.cuda_graph and params and optimizer_type == "adam" and self.born_machine.conditioning_dim == 0):
+            return False
+        if dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1:
+            return False
+        return all(p.is_cuda and p.device == self.tables.device for p in params)
+
+    def _capture_epoch(self, params, optimizer, gradient_clip_norm, entropy_weight):
+        """Two CUDA graphs per epoch: A = forward, loss, backward, gradient clipping; B = optimizer step.
+        The host reads the three scalars between them (the reference's NaN/Inf guard decides whether B runs).
+        Returns (graph_a, graph_b, scalars [ksd, entropy, loss] fp64, grad_norm)."""
+        dev = params[0].device
+        scal = torch.zeros(3, dtype=torch.float64, device=dev)
+        gnorm = torch.zeros((), dtype=torch.float32, device=dev)
+
+        def forward_backward():
+            optimizer.zero_grad(set_to_none=True)
+            q = self.born_machine.get_probabilities().squeeze()
+            ksd_loss = torch.sqrt(self.ksd_squared(q).clamp(min=1e-12))
+            entropy = self.born_machine.entropy()
+            loss = ksd_loss - entropy_weight * entropy.to(ksd_loss.dtype)
+            scal.copy_(torch.stack([ksd_loss.detach().double(), entropy.detach().double(), loss.detach().double()]))
+            loss.backward()
+            gnorm.copy_(nn_utils.clip_grad_norm_(params, gradient_clip_norm).detach().float())
+
+        # warm-up on a side stream (workspaces, optimizer state), then put parameters and state back
+        snapshot = [p.detach().clone() for p in params]
+        side = torch.cuda.Stream(device=dev)
+        side.wait_stream(torch.cuda.current_stream(dev))
+        with torch.cuda.stream(side):
+            for _ in range(2):
+                self.born_machine._pair_cache = None
+                forward_backward()
+                optimizer.step()
+        torch.cuda.current_stream(dev).wait_stream(side)
+        with torch.no_grad():
+            for p, keep in zip(params, snapshot):
+                p.copy_(keep)
+            for state in optimizer.state.values():
+                for value in state.values():
+                    if torch.is_tensor(value):
+                        value.zero_()
+        self.born_machine._pair_cache = None
+        graph_a, graph_b = torch.cuda.CUDAGraph(), torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph_a, capture_error_mode="thread_local"):
+            forward_backward()
+        with torch.cuda.graph(graph_b, pool=graph_a.pool(), capture_error_mode="thread_local"):
+            optimizer.step()
+        self.born_machine._pair_cache = None
+        return graph_a, graph_b, scal, gnorm
+
     def train(self, x_observation_dict, num_epochs, lr_born_machine,
               verbose=True, true_posterior_for_tvd=None,
               use_lr_scheduler=True, gradient_clip_norm=10.0,
@@ -160,15 +215,25 @@ class KSDVariationalInference:
         self._precompute_all_s_p(x_observation_dict)
 
         params = list(self.born_machine.parameters())
-        if optimizer_type == "adam":
+        graphs = None
+        if self._graph_supported(params, optimizer_type):
+            # CUDA-graph epochs: the learning rate lives in a device scalar that the host
+            # refreshes from an ordinary scheduler on a stand-in optimizer, so the schedule is the reference's.
+            lr_device = torch.tensor(float(lr_born_machine), dtype=torch.float32, device=params[0].device)
+            optimizer = optim.Adam(params, lr=lr_device, betas=adam_betas, capturable=True, fused=True)
+            schedule_owner = optim.SGD([torch.zeros(1, requires_grad=True)], lr=lr_born_machine)
+            graphs = self._capture_epoch(params, optimizer, gradient_clip_norm, entropy_weight)
+        elif optimizer_type == "adam":
             # same update; on CUDA parameters one fused kernel instead of ~10 foreach passes over 2^n floats
             fused = bool(params) and all(p.is_cuda for p in params)
             optimizer = optim.Adam(params, lr=lr_born_machine, betas=adam_betas, fused=True if fused else None)
+            schedule_owner = optimizer
         else:
             optimizer = optim.SGD(params, lr=lr_born_machine, momentum=0.9)
+            schedule_owner = optimizer
         scheduler = None
         if use_lr_scheduler:
-            scheduler = optim.lr_scheduler.CosineAnnealingLR(optimizer, T_max=num_epochs, eta_min=lr_born_machine / 10)
+            scheduler = optim.lr_scheduler.CosineAnnealingLR(schedule_owner, T_max=num_epochs, eta_min=lr_born_machine / 10)
 
         history = {'loss_ksd': [], 'tvd': [], 'grad_norm': [], 'entropy': []}
         p_true, stray_mass = (None, 0.0)
@@ -187,27 +252,42 @@ class KSDVariationalInference:
         last_grad_norm, last_entropy = 0.0, 0.0
 
         for epoch in range(num_epochs):
-            optimizer.zero_grad()
-            q = self.born_machine.get_probabilities(x_condition=x_condition).squeeze()
-            if q.shape[0] != self.num_possible_latent_states:
-                raise ValueError(f"Probabilities shape mismatch: {q.shape}")
-
-            K = self.ksd_squared(q)                                   # ksd_vi.py:110-131
-            ksd_loss = torch.sqrt(K.clamp(min=1e-12))                 # :133-134
-            entropy = self.born_machine.entropy(x_condition=x_condition)
-            loss = ksd_loss - entropy_weight * entropy.to(ksd_loss.dtype)
-            # one device->host read for the three scalars the reference reads with three .item() calls
-            ksd_value, last_entropy, loss_value = torch.stack(
-                [ksd_loss.detach().double(), entropy.detach().double(), loss.detach().double()]).tolist()
-
-            if math.isnan(loss_value) or math.isinf(loss_value):
-                print(f"Warning: NaN or Inf loss: {loss_value}. Skipping update.")
+            if graphs is not None:
+                graph_a, graph_b, scalars, grad_norm_dev = graphs
+                graph_a.replay()                                      # forward, loss, backward, clipping
+                ksd_value, last_entropy, loss_value = scalars.tolist()
+                if math.isnan(loss_value) or math.isinf(loss_value):
+                    print(f"Warning: NaN or Inf loss: {loss_value}. Skipping update.")
+                else:
+                    last_grad_norm = grad_norm_dev.clone()
+                    graph_b.replay()                                  # optimizer step
+                    if scheduler is not None:
+                        schedule_owner.step()                         # stand-in optimizer: keeps the scheduler's call order
+                        scheduler.step()
+                        lr_device.fill_(scheduler.get_last_lr()[0])
+                self.born_machine._pair_cache = None                  # replays change the parameters in place
             else:
-                loss.backward()
-                last_grad_norm = nn_utils.clip_grad_norm_(params, gradient_clip_norm).detach()   # read after the loop
-                optimizer.step()
-                if scheduler is not None:
-                    scheduler.step()
+                optimizer.zero_grad()
+                q = self.born_machine.get_probabilities(x_condition=x_condition).squeeze()
+                if q.shape[0] != self.num_possible_latent_states:
+                    raise ValueError(f"Probabilities shape mismatch: {q.shape}")
+
+                K = self.ksd_squared(q)                                   # ksd_vi.py:110-131
+                ksd_loss = torch.sqrt(K.clamp(min=1e-12))                 # :133-134
+                entropy = self.born_machine.entropy(x_condition=x_condition)
+                loss = ksd_loss - entropy_weight * entropy.to(ksd_loss.dtype)
+                # one device->host read for the three scalars the reference reads with three .item() calls
+                ksd_value, last_entropy, loss_value = torch.stack(
+                    [ksd_loss.detach().double(), entropy.detach().double(), loss.detach().double()]).tolist()
+
+                if math.isnan(loss_value) or math.isinf(loss_value):
+                    print(f"Warning: NaN or Inf loss: {loss_value}. Skipping update.")
+                else:
+                    loss.backward()
+                    last_grad_norm = nn_utils.clip_grad_norm_(params, gradient_clip_norm).detach()   # read after the loop
+                    optimizer.step()
+                    if scheduler is not None:
+                        scheduler.step()
 
             history['loss_ksd'].append(ksd_value)
             history['grad_norm'].append(last_grad_norm)   # after a skipped step the previous value is re-logged (:156)
@@ -239,6 +319,12 @@ class KSDVariationalInference:
                 if p_true is not None and not np.isnan(history['tvd'][-1]):
                     msg += f" | TVD: {history['tvd'][-1]:.6f}"
                 print(msg)
+
+        if graphs is not None:
+            for p in params:                    # gradients live in the graphs' memory pool: hand out copies
+                if p.grad is not None:
+                    p.grad = p.grad.detach().clone()
+            graphs = None
 
         # gradient norms were kept on the device during the loop: one read for all epochs
         pending = [i for i, g in enumerate(history['grad_norm']) if torch.is_tensor(g)]

@@ -117,3 +117,28 @@ def test_trainer_epochs_with_and_without_streaming_kernels(monkeypatch):
     for key in ("loss_ksd", "entropy", "grad_norm"):
         a, b = np.array(hist[0][key], dtype=float), np.array(hist[1][key], dtype=float)
         assert np.max(np.abs(a - b) / np.maximum(np.abs(b), 1e-12)) < 1e-4, key
+
+
+@pytest.mark.parametrize("n,precision,algorithm", [(10, "fp64", "pairs"), (12, "tc32", "pairs"), (16, "fp64", "modeproduct")])
+def test_cuda_graph_epochs_match_eager(n, precision, algorithm):
+    """cuda_graph=True replays forward+backward+clipping and the Adam step as two CUDA graphs per epoch; the history
+    (with TVD tracking, cosine schedule, best-q restore) must be the eager one up to rounding."""
+    from tensornetworks_b200 import ops
+    from tensornetworks_b200.ksd_vi import KSDVariationalInference
+    from tensornetworks_b200.synthetic import random_binary_bn
+    bn, lat, obs, x = random_binary_bn(n, seed=5)
+    hist, final = [], []
+    for graph in (False, True):
+        torch.manual_seed(1)
+        vi = KSDVariationalInference(bn, lat, obs, {"use_logits": True, "conditioning_dim": 0}, device="cuda",
+                                     precision=precision, compute_device="cuda", algorithm=algorithm, cuda_graph=graph)
+        p_true = ops.SteinTables.from_network(bn, x, lat, precision="fp64").posterior()
+        hist.append(vi.train(x, num_epochs=12, lr_born_machine=0.05, verbose=False, true_posterior_for_tvd=p_true))
+        final.append(vi.born_machine.get_probabilities().squeeze().detach().double().cpu().numpy())
+        assert all(p.grad is not None for p in vi.born_machine.parameters())
+    tol = 1e-5 if precision == "fp64" else 2e-3
+    for key in ("loss_ksd", "entropy", "grad_norm", "tvd"):
+        a, b = np.array(hist[0][key], dtype=float), np.array(hist[1][key], dtype=float)
+        assert a.shape == b.shape == (12,), key
+        assert np.max(np.abs(a - b) / np.maximum(np.abs(a), 1e-12)) < tol, (key, a, b)
+    assert np.max(np.abs(final[0] - final[1])) <= tol * np.max(final[0])
