@@ -281,7 +281,10 @@ template <typename Q, typename TS, bool FAST>
 __global__ void __launch_bounds__(kMpThreads, 2)
 mp_last_kernel(int64_t N, int b0, int g, int logW, int p0, int n_loc, int nchunk, int flip_split, int blocked_arg,
                const Q* __restrict__ q, const TS* __restrict__ S, const double* __restrict__ Rs,
-               const TS* __restrict__ V, double* __restrict__ u, double* __restrict__ blockpart, double a) {
+               const TS* __restrict__ V, double* __restrict__ u, double* __restrict__ blockpart, double a,
+               double* __restrict__ upart) {
+    // gridDim.y > 1: the vectors are split over gridDim.y CTAs per tile (few tiles: small n); each writes its
+    // partial of u to upart[blockIdx.y][.] and mp_usum_kernel adds them in a fixed order.
     extern __shared__ double tile[];
     __shared__ double red[kMpThreads / 32];
     const bool blocked = FAST || blocked_arg;
@@ -306,7 +309,8 @@ mp_last_kernel(int64_t N, int b0, int g, int logW, int p0, int n_loc, int nchunk
     const int64_t jstride = blocked ? 1024 : ((int64_t)(1024 >> logW) << b0);   // +1024 tile elements in V
     const int ptid = swz(threadIdx.x);                     // swz(tid + 512 k) = ptid + 512 k
     const int nvec = n_loc + 1 + nchunk;
-    for (int v = 0; v < nvec; ++v) {
+    const int v_begin = (int)((int64_t)nvec * blockIdx.y / gridDim.y), v_end = (int)((int64_t)nvec * (blockIdx.y + 1) / gridDim.y);
+    for (int v = v_begin; v < v_end; ++v) {
         const TS* vec = V + (int64_t)v * N + lbase;
         if (fused) {
 #pragma unroll 1
@@ -367,6 +371,15 @@ mp_last_kernel(int64_t N, int b0, int g, int logW, int p0, int n_loc, int nchunk
         __syncthreads();
     }
 
+    if (gridDim.y > 1) {
+        double* out = upart + (int64_t)blockIdx.y * N;
+#pragma unroll
+        for (int k = 0; k < kMpPerThread; ++k) {
+            const int e = threadIdx.x + k * kMpThreads;
+            if (live(e)) out[base + off(e)] = acc[k];
+        }
+        return;
+    }
     double contrib = 0.0;
 #pragma unroll
     for (int k = 0; k < kMpPerThread; ++k) {
@@ -386,6 +399,32 @@ mp_last_kernel(int64_t N, int b0, int g, int logW, int p0, int n_loc, int nchunk
 #pragma unroll
         for (int w2 = 0; w2 < kMpThreads / 32; ++w2) s += red[w2];
         blockpart[blockIdx.x] = s;
+    }
+}
+
+// ---- MP3b (only when the vectors were split): u = sum_g upart[g] in group order, block partials of q.u
+template <typename Q>
+__global__ void __launch_bounds__(256)
+mp_usum_kernel(int64_t N, int groups, const Q* __restrict__ q, const double* __restrict__ upart,
+               double* __restrict__ u, double* __restrict__ blockpart) {
+    __shared__ double red[8];
+    const int64_t z = (int64_t)blockIdx.x * 256 + threadIdx.x;
+    double contrib = 0.0;
+    if (z < N) {
+        double acc = 0.0;
+        for (int gq = 0; gq < groups; ++gq) acc += upart[(int64_t)gq * N + z];
+        u[z] = acc;
+        contrib = (double)q[z] * acc;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) contrib += __shfl_xor_sync(0xffffffffu, contrib, o);
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = contrib;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double sum = 0.0;
+#pragma unroll
+        for (int w2 = 0; w2 < 8; ++w2) sum += red[w2];
+        blockpart[blockIdx.x] = sum;
     }
 }
 
@@ -411,9 +450,10 @@ struct MpPass { int b0, g, logW; };
 
 struct MpPlan {
     int64_t N, tiles_first, tiles_last;
-    int n_loc, T, n_mid, pre_cnt, chunk, nchunk, nvec, flip_split, blocked, group_log;
+    int n_loc, T, n_mid, pre_cnt, chunk, nchunk, nvec, flip_split, blocked, group_log, vgroups;
+    int64_t part_blocks;
     MpPass mid[4], last;
-    size_t off_v, off_block, total;
+    size_t off_v, off_block, off_upart, total;
 };
 
 int mp_plan(int n, int p_begin, int p_end, int storage, MpPlan* p) {
@@ -458,7 +498,12 @@ int mp_plan(int n, int p_begin, int p_end, int storage, MpPlan* p) {
     p->nvec = p->n_loc + 1 + p->nchunk;
     size_t off = 0;
     p->off_v = off;     off += ((size_t)p->nvec * p->N * elem + 255) / 256 * 256;
-    p->off_block = off; off += ((size_t)(p->tiles_last + 1) * sizeof(double) + 255) / 256 * 256;
+    // few last-pass tiles (small n): split the vectors of a tile over several CTAs to fill the SMs
+    p->vgroups = 1;
+    while (p->tiles_last * p->vgroups < 2 * 148 && p->vgroups * 2 <= p->nvec && p->vgroups < 8) p->vgroups *= 2;
+    p->part_blocks = p->vgroups > 1 ? (p->N + 255) / 256 : p->tiles_last;
+    p->off_block = off; off += ((size_t)(p->part_blocks + 1) * sizeof(double) + 255) / 256 * 256;
+    p->off_upart = off; off += p->vgroups > 1 ? ((size_t)p->vgroups * p->N * sizeof(double) + 255) / 256 * 256 : 0;
     p->total = off;
     return 0;
 }
@@ -466,7 +511,7 @@ int mp_plan(int n, int p_begin, int p_end, int storage, MpPlan* p) {
 // launches of one evaluation for q type Q and storage type TS
 template <typename Q, typename TS>
 int mp_run(const MpPlan& p, int bit_begin, double a, const Q* q, const TS* S_cols, const double* r_sum, TS* V,
-           double* u, double* blockpart, double* ksd_part, int* launches, cudaStream_t st) {
+           double* u, double* blockpart, double* upart, double* ksd_part, int* launches, cudaStream_t st) {
     TNK_CUDA_OK(cudaFuncSetAttribute(mp_first_kernel<Q, TS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMpSmem));
     TNK_CUDA_OK(cudaFuncSetAttribute(mp_last_kernel<Q, TS, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMpSmem));
     TNK_CUDA_OK(cudaFuncSetAttribute(mp_last_kernel<Q, TS, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMpSmem));
@@ -484,15 +529,20 @@ int mp_run(const MpPlan& p, int bit_begin, double a, const Q* q, const TS* S_col
     }
     const MpPass& ps = p.last;
     const TS* S2 = S_cols + (size_t)p.n_loc * p.N;       // the copy in the last-pass layout
-    const unsigned grid = (unsigned)p.tiles_last;
+    const dim3 grid((unsigned)p.tiles_last, (unsigned)p.vgroups, 1);
     if (p.blocked && ps.g >= 3)
         mp_last_kernel<Q, TS, true><<<grid, kMpThreads, kMpSmem, st>>>(p.N, ps.b0, ps.g, ps.logW, bit_begin, p.n_loc, p.nchunk,
-                                                                     p.flip_split, p.blocked, q, S2, r_sum, V, u, blockpart, a);
+                                                                     p.flip_split, p.blocked, q, S2, r_sum, V, u, blockpart, a, upart);
     else
         mp_last_kernel<Q, TS, false><<<grid, kMpThreads, kMpSmem, st>>>(p.N, ps.b0, ps.g, ps.logW, bit_begin, p.n_loc, p.nchunk,
-                                                                      p.flip_split, p.blocked, q, S2, r_sum, V, u, blockpart, a);
+                                                                      p.flip_split, p.blocked, q, S2, r_sum, V, u, blockpart, a, upart);
     TNK_CUDA_OK(cudaGetLastError());
-    mp_scalar_kernel<<<1, 256, 0, st>>>(blockpart, p.tiles_last, ksd_part);
+    if (p.vgroups > 1) {
+        mp_usum_kernel<Q><<<(unsigned)p.part_blocks, 256, 0, st>>>(p.N, p.vgroups, q, upart, u, blockpart);
+        TNK_CUDA_OK(cudaGetLastError());
+        ++*launches;
+    }
+    mp_scalar_kernel<<<1, 256, 0, st>>>(blockpart, p.part_blocks, ksd_part);
     TNK_CUDA_OK(cudaGetLastError());
     *launches += 2;
     return 0;
@@ -559,15 +609,16 @@ extern "C" int tnk_ksd_modeproduct(int n_latent, double length_scale, const void
     const double a = exp(-1.0 / ((double)n * length_scale));
     unsigned char* ws = (unsigned char*)workspace;
     double* blockpart = (double*)(ws + p.off_block);
+    double* upart = (double*)(ws + p.off_upart);
     int rc;
     if (storage == TNK_MP_STORE_FP32) {
         float* V = (float*)(ws + p.off_v);
-        rc = q_dtype == 0 ? mp_run<double, float>(p, bit_begin, a, (const double*)q, (const float*)S_cols, r_sum, V, u, blockpart, ksd_part, &launches, st)
-                          : mp_run<float, float>(p, bit_begin, a, (const float*)q, (const float*)S_cols, r_sum, V, u, blockpart, ksd_part, &launches, st);
+        rc = q_dtype == 0 ? mp_run<double, float>(p, bit_begin, a, (const double*)q, (const float*)S_cols, r_sum, V, u, blockpart, upart, ksd_part, &launches, st)
+                          : mp_run<float, float>(p, bit_begin, a, (const float*)q, (const float*)S_cols, r_sum, V, u, blockpart, upart, ksd_part, &launches, st);
     } else {
         double* V = (double*)(ws + p.off_v);
-        rc = q_dtype == 0 ? mp_run<double, double>(p, bit_begin, a, (const double*)q, (const double*)S_cols, r_sum, V, u, blockpart, ksd_part, &launches, st)
-                          : mp_run<float, double>(p, bit_begin, a, (const float*)q, (const double*)S_cols, r_sum, V, u, blockpart, ksd_part, &launches, st);
+        rc = q_dtype == 0 ? mp_run<double, double>(p, bit_begin, a, (const double*)q, (const double*)S_cols, r_sum, V, u, blockpart, upart, ksd_part, &launches, st)
+                          : mp_run<float, double>(p, bit_begin, a, (const float*)q, (const double*)S_cols, r_sum, V, u, blockpart, upart, ksd_part, &launches, st);
     }
     if (rc) return rc;
     if (n_launch) *n_launch = launches;
