@@ -168,8 +168,28 @@ int tnk_born_backward(const float* q, const void* grad_q, int grad_dtype, const 
  * NULL.  Used by the CPU tests to check that the steps cover the bracket exactly. */
 int tnk_tc_plan(int n_latent, int* np, int* k32, int* kb, int* nsteps, int* nsteps16, int32_t* steps);
 
-/* Measurement hook: when both are non-NULL cudaEvent_t handles, every following tnk_ksd_rows call
- * on this host thread records them on its stream immediately before and after the pair kernel
+/* Symmetric tensor-core evaluation of the same quadratic form (reference ksd_vi.py:110-131, whose k_p is
+ * symmetric, stein_utils.py:161-196): the pair space is cut into 128 x 128-state tiles and every
+ * UNORDERED pair of tiles is evaluated once - its values feed the rows of one tile and, mirrored, the
+ * rows of the other - so N(N+128)/2 of the 4^n ordered pairs are executed.  fp32-grade
+ * arithmetic as TNK_PREC_TC32 (1e-4 mode); 7 <= n <= 24.
+ *   q          device double/float [N];  ST, Cst: the fp32 tables tnk_score emits for TNK_PREC_TC32
+ *   tile_offset, tile_stride   this call owns row tiles tile_offset + k*tile_stride (k >= 0): rank g of G
+ *              passes (g, G); (0, 1) is the whole evaluation
+ *   reuse_table  non-zero: the workspace still holds the q-independent column table an earlier call built
+ *              for the same n, length_scale, ST, Cst (skips the packing pass)
+ *   u_partial  device double [N] (out): contributions of the owned tiles to u = K_p q, rows and mirrored
+ *              columns; the sum over all offsets of one stride is u
+ *   ksd_part   device double [1] (out): sum_z q_z u_partial[z]; the sum over all offsets is KSD^2
+ * The mirrored sums are accumulated with fp64 atomics: the last bits of u_partial depend on their order. */
+size_t tnk_ksd_sym_workspace_bytes(int n_latent, int tile_offset, int tile_stride);
+int tnk_ksd_sym(int n_latent, double length_scale, const void* q, int q_dtype,
+                const void* ST, const void* Cst, int tile_offset, int tile_stride, int reuse_table,
+                double* u_partial, double* ksd_part,
+                void* workspace, size_t workspace_bytes, int* n_launch, void* stream);
+
+/* Measurement hook: when both are non-NULL cudaEvent_t handles, every following tnk_ksd_rows or
+ * tnk_ksd_sym call on this host thread records them on its stream immediately before and after the pair kernel
  * (K3) alone, so a benchmark can time the dominant kernel live.  Pass NULL, NULL to switch off. */
 int tnk_ksd_timing_events(void* start_event, void* stop_event);
 

@@ -28,7 +28,8 @@ MP_STORE = {"fp64": 0, "fp32": 1}  # TNK_MP_STORE_*
 EXPORTS = ["tnk_last_error", "tnk_version", "tnk_bn_joint", "tnk_ksd_layout", "tnk_score",
            "tnk_ksd_workspace_bytes", "tnk_ksd_rows", "tnk_ksd_rows_peers", "tnk_ksd_timing_events", "tnk_alu_peak",
            "tnk_ksd_modeproduct_workspace_bytes", "tnk_modeproduct_tables", "tnk_modeproduct_plan_limit", "tnk_ksd_modeproduct", "tnk_tc_plan",
-           "tnk_born_blocks", "tnk_born_forward", "tnk_born_backward"]
+           "tnk_born_blocks", "tnk_born_forward", "tnk_born_backward",
+           "tnk_ksd_sym_workspace_bytes", "tnk_ksd_sym"]
 
 
 def _nvcc():
@@ -103,6 +104,11 @@ def load():
     lib.tnk_ksd_rows_peers.argtypes = [c_int, c_dbl, c_int, c_vp, c_int, c_vp, c_vp, c_i64, c_i64,
                                        c_int, c_int, ctypes.POINTER(c_vp), ctypes.POINTER(c_vp), c_vp,
                                        c_vp, c_sz, ctypes.POINTER(c_int), c_vp]
+    lib.tnk_ksd_sym_workspace_bytes.restype = c_sz
+    lib.tnk_ksd_sym_workspace_bytes.argtypes = [c_int, c_int, c_int]
+    lib.tnk_ksd_sym.restype = c_int
+    lib.tnk_ksd_sym.argtypes = [c_int, c_dbl, c_vp, c_int, c_vp, c_vp, c_int, c_int, c_int, c_vp, c_vp,
+                                c_vp, c_sz, ctypes.POINTER(c_int), c_vp]
     lib.tnk_ksd_modeproduct_workspace_bytes.restype = c_sz
     lib.tnk_ksd_modeproduct_workspace_bytes.argtypes = [c_int, c_int, c_int, c_int]
     lib.tnk_ksd_modeproduct.restype = c_int

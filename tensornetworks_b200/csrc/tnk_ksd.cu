@@ -655,3 +655,128 @@ extern "C" int tnk_ksd_rows_peers(int n_latent, double length_scale, int precisi
     return ksd_rows_impl(n_latent, length_scale, precision, q, q_dtype, ST, Cst, row_begin, row_end,
                          peers.u[my_rank], ksd_part, workspace, workspace_bytes, n_launch, stream, peers);
 }
+
+
+// ------------------------------------------------------------------------------------
+// Symmetric tensor-core evaluation (tnk_ksd_sym): every unordered pair of 128-state tiles is evaluated once.
+// ------------------------------------------------------------------------------------
+namespace {
+
+struct SymPlan {
+    int64_t N, T, finish_blocks;
+    int row_tiles, splits;
+    size_t off_q, off_part, off_col, off_block, off_b, total;
+};
+
+int make_sym_plan(int n, int tile_offset, int tile_stride, SymPlan* p) {
+    if (n < TNK_TC_MIN_LATENT || n > TNK_TC_MAX_LATENT || tile_stride < 1 || tile_offset < 0) return 1;
+    p->N = (int64_t)1 << n;
+    p->T = p->N / TNK_TC_TILE;
+    p->row_tiles = tile_offset < p->T ? (int)((p->T - tile_offset + tile_stride - 1) / tile_stride) : 0;
+    const size_t b_bytes = tnk_tcs_table_bytes(n, p->N);
+    int splits = 1;
+    while ((int64_t)p->row_tiles * splits < 8 * 148 && splits * 2 <= p->T) splits *= 2;
+    while ((b_bytes / splits) > ((size_t)32 << 20) && splits * 2 <= p->T) splits *= 2;
+    p->splits = splits;
+    p->finish_blocks = (p->N + 255) / 256;
+    size_t off = 0;
+    auto take = [&](size_t bytes) { const size_t at = off; off += (bytes + 255) / 256 * 256; return at; };
+    p->off_q = take((size_t)p->N * sizeof(float));
+    p->off_part = take((size_t)splits * (size_t)(p->row_tiles > 0 ? p->row_tiles : 1) * TNK_TC_TILE * sizeof(double));
+    p->off_col = take((size_t)p->N * sizeof(double));
+    p->off_block = take((size_t)(p->finish_blocks + 1) * sizeof(double));
+    p->off_b = take(b_bytes);
+    p->total = off;
+    return 0;
+}
+
+// u_partial[z] = mirrored column sums + (row sums over the column splits if this call owns z's row tile)
+template <typename Q>
+__global__ void __launch_bounds__(256)
+finish_sym_kernel(const double* __restrict__ part, int splits, int64_t part_stride, int tile_offset, int tile_stride,
+                  int row_tiles, const double* __restrict__ ucol, const Q* __restrict__ q, int64_t N,
+                  double* __restrict__ u, double* __restrict__ blockpart) {
+    __shared__ double red[256];
+    const int64_t z = (int64_t)blockIdx.x * 256 + threadIdx.x;
+    double contrib = 0.0;
+    if (z < N) {
+        double acc = ucol[z];
+        const int64_t d = (z / TNK_TC_TILE) - tile_offset;
+        if (d >= 0 && d % tile_stride == 0 && d / tile_stride < row_tiles) {
+            const int64_t r = (d / tile_stride) * TNK_TC_TILE + (z % TNK_TC_TILE);
+            double rows = 0.0;
+            for (int s = 0; s < splits; ++s) rows += part[(size_t)s * part_stride + r];
+            acc += rows;
+        }
+        u[z] = acc;
+        contrib = (double)q[z] * acc;
+    }
+    red[threadIdx.x] = contrib;
+    __syncthreads();
+    for (int off = 128; off > 0; off >>= 1) {
+        if (threadIdx.x < off) red[threadIdx.x] += red[threadIdx.x + off];
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) blockpart[blockIdx.x] = red[0];
+}
+
+}  // namespace
+
+extern "C" size_t tnk_ksd_sym_workspace_bytes(int n_latent, int tile_offset, int tile_stride) {
+    SymPlan p;
+    if (make_sym_plan(n_latent, tile_offset, tile_stride, &p)) return 0;
+    return p.total;
+}
+
+extern "C" int tnk_ksd_sym(int n_latent, double length_scale, const void* q, int q_dtype,
+                           const void* ST, const void* Cst, int tile_offset, int tile_stride, int reuse_table,
+                           double* u_partial, double* ksd_part,
+                           void* workspace, size_t workspace_bytes, int* n_launch, void* stream) {
+    SymPlan p;
+    TNK_REQUIRE(make_sym_plan(n_latent, tile_offset, tile_stride, &p) == 0,
+                "tnk_ksd_sym: bad arguments n=%d (supported %d..%d) tile_offset=%d tile_stride=%d", n_latent,
+                TNK_TC_MIN_LATENT, TNK_TC_MAX_LATENT, tile_offset, tile_stride);
+    TNK_REQUIRE(q && ST && Cst && u_partial && ksd_part && workspace, "tnk_ksd_sym: NULL pointer argument");
+    TNK_REQUIRE(q_dtype == 0 || q_dtype == 1, "tnk_ksd_sym: q_dtype must be 0 (double) or 1 (float)");
+    TNK_REQUIRE(workspace_bytes >= p.total, "tnk_ksd_sym: workspace %zu < required %zu", workspace_bytes, p.total);
+    TNK_REQUIRE(((uintptr_t)workspace & 255) == 0, "tnk_ksd_sym: workspace must be 256-byte aligned");
+    TNK_REQUIRE((double)n_latent * length_scale != 0.0, "tnk_ksd_sym: num_vars*length_scale must be non-zero");
+    cudaStream_t st = (cudaStream_t)stream;
+    const int n = n_latent;
+    unsigned char* ws = (unsigned char*)workspace;
+    float* qT = (float*)(ws + p.off_q);
+    double* part = (double*)(ws + p.off_part);
+    double* ucol = (double*)(ws + p.off_col);
+    double* blockpart = (double*)(ws + p.off_block);
+    int launches = 0;
+    const double a = exp(-1.0 / ((double)n * length_scale));
+    const double gamma = a - 1.0 / a;
+    double wl[32];
+    for (int h = 0; h < 32; ++h) wl[h] = (h <= n) ? exp(-(double)h / ((double)n * length_scale)) : 0.0;
+
+    const unsigned qblocks = (unsigned)((p.N + 255) / 256);
+    if (q_dtype == 0) q_pack_kernel<float, double><<<qblocks, 256, 0, st>>>((const double*)q, p.N, p.N, qT);
+    else q_pack_kernel<float, float><<<qblocks, 256, 0, st>>>((const float*)q, p.N, p.N, qT);
+    TNK_CUDA_OK(cudaGetLastError());
+    ++launches;
+    const int rc = tnk_tcs_launch(n, gamma, wl, (const float*)ST, (const float*)Cst, qT, tile_offset, tile_stride,
+                                  p.row_tiles, p.splits, (float*)(ws + p.off_b), reuse_table, part, ucol,
+                                  g_ev_start, g_ev_stop, &launches, st);
+    if (rc) return rc;
+    const int64_t part_stride = (int64_t)p.row_tiles * TNK_TC_TILE;
+    if (q_dtype == 0)
+        finish_sym_kernel<double><<<(unsigned)p.finish_blocks, 256, 0, st>>>(part, p.splits, part_stride, tile_offset, tile_stride,
+                                                                            p.row_tiles, ucol, (const double*)q, p.N, u_partial, blockpart);
+    else
+        finish_sym_kernel<float><<<(unsigned)p.finish_blocks, 256, 0, st>>>(part, p.splits, part_stride, tile_offset, tile_stride,
+                                                                           p.row_tiles, ucol, (const float*)q, p.N, u_partial, blockpart);
+    TNK_CUDA_OK(cudaGetLastError());
+    PeerSinks none;
+    none.n = 0;
+    none.rank = 0;
+    finish_scalar_kernel<<<1, 256, 0, st>>>(blockpart, p.finish_blocks, ksd_part, none);
+    TNK_CUDA_OK(cudaGetLastError());
+    launches += 2;
+    if (n_launch) *n_launch = launches;
+    return 0;
+}

@@ -539,6 +539,434 @@ tc_rows_kernel(const __grid_constant__ TcParams prm, const float* __restrict__ B
     }
 }
 
+
+// ======================================================================================================
+// K3-TCS: symmetric tile variant ("N(N+1)/2 if the symmetry k_p(z,z') = k_p(z',z)
+// is exploited").  A tile (I, J) of 128 x 128 states with I < J is evaluated ONCE and used twice:
+//   u_i += sum_j Y(i,j) q_j  (row part)       u_j += sum_i Y(i,j) q_i  (mirrored column part)
+// with Y = a^popc(i^j) * bracket(i,j); diagonal tiles (I = J) contribute their row part only.  The whole
+// bracket is bilinear in q-free feature vectors (App. A.4) and goes through the tensor cores:
+//   A32 (rows):    s_hi | (g rho)_hi | bits | [C_hi, C_lo, 1, 1] | 0      g rho_p = gamma (1-s_p)(1-2 b_p)
+//   B32 (columns): s_hi | bits | (g rho)_hi | [1, 1, C_hi, C_lo] | 0      -> chunk c of A meets chunk c of B
+//   A16 (rows):    bf(s) | bf(s_lo) | bf((g rho)_lo) | bits               bf16 cross terms, K = 16 per step
+//   B16 (columns): bf(s_lo) | bf(s) | bits | bf((g rho)_lo)
+// n = 20: 8 tf32 + 5 bf16 = 13 K-steps per tile, i.e. 6.5 per ordered tile pair.  The column table is
+// q-independent.  The epilogue reads the accumulator with tcgen05.ld.16x256b (the mma C-fragment
+// distribution: thread t of a warp holds rows t/4 + 8k, k = 0..3, and columns 8m + 2(t%4) + {0,1}, m = 0..7
+// of its warp's 32 x 64 block), so a thread owns a 4 x 16 patch: the mirrored column sums are reduced over
+// its 4 rows in registers and over the 8 row groups of the warp with a transposing exchange (14 SHFL),
+// then over the 4 lane quarters through shared memory and added to ucol[] with one fp64 RED per column and
+// tile.  The Hamming weight of the 7 in-tile bits factorises over the patch: per-thread constant x
+// (compile-time power of a from the unrolled row/column slots) -> 6 packed weights in registers.
+// Row sums: fp32 per tile, compensated fp32 across tiles, fp64 at the end (as in tc_rows_kernel).
+// Column sums arrive in ucol[] by atomics, so the last bits of u depend on the arrival order.
+// ======================================================================================================
+__host__ __device__ constexpr int tcs_k32(int nc) { return (3 * nc + 2) & ~1; }     // 3nc + 1 chunks, padded to even
+__host__ __device__ constexpr int tcs_steps32(int nc) { return tcs_k32(nc) / 2; }
+__host__ __device__ constexpr int tcs_steps16(int nc) { return nc; }                // 4 np bf16 values / 16
+__host__ __device__ constexpr int tcs_kb(int nc) { return tcs_k32(nc) + 2 * nc; }
+
+struct TcsParams {
+    int n;
+    int tile_offset, tile_stride;  // row tile of blockIdx.x = tile_offset + tile_stride * blockIdx.x
+    int64_t n_tiles;               // 2^n / 128
+    int col_splits;                // gridDim.y
+    int64_t part_stride;           // rows covered by the launch (gridDim.x * 128)
+    float gamma;
+    float wl[32];
+};
+
+// column operand table of the symmetric variant: q-independent, same slot layout as tc_pack_kernel
+__global__ void __launch_bounds__(256)
+tcs_pack_kernel(int n, int np, int64_t n_tiles, float gamma,
+                const float* __restrict__ ST, const float* __restrict__ Cst, uint4* __restrict__ out) {
+    const int nc = np >> 2;
+    const int K32 = tcs_k32(nc), K = tcs_kb(nc);
+    const int64_t idx = (int64_t)blockIdx.x * 256 + threadIdx.x;
+    const int row = (int)(idx & (kTile - 1));
+    const int64_t t = idx >> 7;
+    const int chunk = (int)(t % K);
+    const int64_t tile = t / K;
+    if (tile >= n_tiles) return;
+    const int64_t z = tile * kTile + row;
+    const float* srow = ST + z * np;
+    auto grho = [&](int p) -> float {
+        if (p >= n) return 0.f;
+        const float v = gamma * (1.f - srow[p]);
+        return ((z >> p) & 1) ? -v : v;
+    };
+    auto bit = [&](int p) -> float { return (p < n && ((z >> p) & 1)) ? 1.f : 0.f; };
+    uint32_t w[4] = {0u, 0u, 0u, 0u};
+    if (chunk < 3 * nc) {
+        const int f = chunk / nc, c = chunk - f * nc;
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+            const int p = 4 * c + e;
+            w[e] = __float_as_uint(f == 0 ? tf_hi(srow[p]) : f == 1 ? bit(p) : tf_hi(grho(p)));
+        }
+    } else if (chunk == 3 * nc) {
+        const float C = Cst[z];
+        w[0] = w[1] = __float_as_uint(1.f);
+        w[2] = __float_as_uint(tf_hi(C));
+        w[3] = __float_as_uint(tf_lo(C));
+    } else if (chunk >= K32) {
+        const int m = chunk - K32;
+        float v[8];
+#pragma unroll
+        for (int x = 0; x < 8; ++x) {
+            const int e = 8 * m + x;
+            const int f = e / np, p = e - f * np;
+            v[x] = f == 0 ? tf_lo(srow[p]) : f == 1 ? srow[p] : f == 2 ? bit(p) : tf_lo(grho(p));
+        }
+#pragma unroll
+        for (int e = 0; e < 4; ++e) w[e] = bf16_pack(v[2 * e], v[2 * e + 1]);
+    }   // 3nc < chunk < K32: zero padding chunk
+    out[idx] = make_uint4(w[0], w[1], w[2], w[3]);
+}
+
+template <int NC>
+struct TcsSmem {
+    static constexpr uint32_t b_bytes = (uint32_t)tcs_kb(NC) * kChunkBytes;
+    static constexpr int stages = (4u * b_bytes <= 216u * 1024u) ? 4 : 3;
+    static constexpr uint32_t off_b = 0;
+    static constexpr uint32_t off_q = off_b + stages * b_bytes;           // [kQSlots][128] float: q of the column tile
+    static constexpr uint32_t off_col = off_q + kQSlots * kTile * 4;      // [2][4][128] float: column sums per lane quarter
+    static constexpr uint32_t off_wl = off_col + 2 * 4 * kTile * 4;       // [32] float
+    static constexpr uint32_t off_red = off_wl + 32 * 4;                  // [128] double
+    static constexpr uint32_t off_bar = off_red + kTile * 8;              // mbarriers
+    static constexpr int n_bars = 1 + 2 * kMaxStages + 4 + kQSlots;
+    static constexpr uint32_t off_tmem = off_bar + n_bars * 8;
+    static constexpr uint32_t total = off_tmem + 16;
+    static_assert(total <= 227u * 1024u, "shared memory of the symmetric tile kernel");
+    static_assert(kQSlots >= stages + 3, "q ring depth");
+};
+
+#define TNK_LD_16x256b_x8(v, addr)                                                                              \
+    asm volatile(                                                                                               \
+        "tcgen05.ld.sync.aligned.16x256b.x8.b32 "                                                               \
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "                               \
+        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"               \
+        : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),       \
+          "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]), \
+          "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]), \
+          "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31]) \
+        : "r"(addr))
+
+template <int NC>
+__global__ void __launch_bounds__(kTcThreads, 1)
+tcs_tiles_kernel(const __grid_constant__ TcsParams prm, const float* __restrict__ B_tab,
+                 const float* __restrict__ ST, const float* __restrict__ Cst, const float* __restrict__ qT,
+                 double* __restrict__ part, double* __restrict__ ucol) {
+    extern __shared__ __align__(1024) unsigned char smem[];
+    using SM = TcsSmem<NC>;
+    constexpr int NP = 4 * NC;
+    constexpr int K32 = tcs_k32(NC), S32 = tcs_steps32(NC), S16 = tcs_steps16(NC);
+    constexpr int kStages = SM::stages;
+    constexpr uint32_t b_bytes = SM::b_bytes;
+    static_assert(2 * kTile + 8 * (S32 + S16) <= kTmemCols, "TMEM columns");
+
+    // Row tile I meets the column tiles J >= I of this column split; nothing to do when the split lies below I.
+    const int64_t I = (int64_t)prm.tile_offset + (int64_t)prm.tile_stride * blockIdx.x;
+    const int64_t n_per = prm.n_tiles / prm.col_splits;
+    const int64_t j_split = (int64_t)blockIdx.y * n_per;
+    const int64_t j_begin = j_split > I ? j_split : I;
+    const int64_t n_local = j_split + n_per - j_begin;
+    if (n_local <= 0) {
+        if (threadIdx.x < kTile)
+            part[(size_t)blockIdx.y * prm.part_stride + (size_t)blockIdx.x * kTile + threadIdx.x] = 0.0;
+        return;
+    }
+
+    unsigned char* sB = smem + SM::off_b;
+    float* sQ = reinterpret_cast<float*>(smem + SM::off_q);
+    float* sCol = reinterpret_cast<float*>(smem + SM::off_col);
+    float* sWl = reinterpret_cast<float*>(smem + SM::off_wl);
+    double* sRed = reinterpret_cast<double*>(smem + SM::off_red);
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + SM::off_bar);
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + SM::off_tmem);
+    uint64_t* bar_aready = bars;
+    uint64_t* bar_full = bars + 1;
+    uint64_t* bar_empty = bar_full + kMaxStages;
+    uint64_t* bar_tfull = bar_empty + kMaxStages;
+    uint64_t* bar_tempty = bar_tfull + 2;
+    uint64_t* bar_qfull = bar_tempty + 2;
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (threadIdx.x < 32) sWl[threadIdx.x] = prm.wl[threadIdx.x];
+    if (threadIdx.x == 0) {
+        mbar_init(bar_aready, 8);
+        for (int s = 0; s < kStages; ++s) { mbar_init(bar_full + s, 1); mbar_init(bar_empty + s, 1); }
+        for (int s = 0; s < 2; ++s) { mbar_init(bar_tfull + s, 1); mbar_init(bar_tempty + s, 8); }
+        for (int s = 0; s < kQSlots; ++s) mbar_init(bar_qfull + s, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 1) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(kTmemCols) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            // ===== producer: column tile of the operand table + its 128 q values (same ring protocol as tc_rows_kernel)
+            int s = 0;
+            uint32_t ph = 0;
+            for (int64_t it = 0; it < n_local; ++it) {
+                const int64_t J = j_begin + it;
+                mbar_wait(bar_empty + s, ph ^ 1u);
+                const int qs = (int)(it & (kQSlots - 1));
+                mbar_expect_tx(bar_qfull + qs, kTile * 4);
+                bulk_g2s(sQ + qs * kTile, qT + J * kTile, kTile * 4, bar_qfull + qs);
+                const unsigned char* srcB = reinterpret_cast<const unsigned char*>(B_tab) + (size_t)J * b_bytes;
+                unsigned char* dstB = sB + (size_t)s * b_bytes;
+                mbar_expect_tx(bar_full + s, b_bytes);
+                for (uint32_t off = 0; off < b_bytes; off += 8 * kChunkBytes) {
+                    const uint32_t len = min(b_bytes - off, (uint32_t)(8 * kChunkBytes));
+                    bulk_g2s(dstB + off, srcB + off, len, bar_full + s);
+                }
+                if (++s == kStages) { s = 0; ph ^= 1u; }
+            }
+        }
+    } else if (warp == 1) {
+        // ===== MMA issuer: K-step ks multiplies chunks (2ks, 2ks+1) of A (TMEM) and B (shared memory)
+        mbar_wait(bar_aready, 0);
+        tc_fence_after();
+        int s = 0;
+        uint32_t ph = 0;
+        for (int64_t it = 0; it < n_local; ++it) {
+            const int ts = (int)(it & 1);
+            const uint32_t tph = (uint32_t)((it >> 1) & 1);
+            mbar_wait(bar_tempty + ts, tph ^ 1u);
+            mbar_wait(bar_full + s, ph);
+            tc_fence_after();
+            const uint64_t b_desc = smem_desc(smem_u32(sB) + (uint32_t)s * b_bytes, 0);
+            const uint32_t d_addr = tmem_base + (uint32_t)(ts * kTile);
+            if (elect_one()) {
+                constexpr uint32_t cu = kChunkBytes >> 4;
+#pragma unroll
+                for (int ks = 0; ks < S32; ++ks) {
+                    const uint64_t db = b_desc + (uint64_t)((uint32_t)(2 * ks) * cu + (cu << 16));
+                    umma_tf32_ts(d_addr, tmem_base + (uint32_t)(kTmemA + 8 * ks), db, kIdesc, ks > 0 ? 1u : 0u);
+                }
+#pragma unroll
+                for (int k = 0; k < S16; ++k) {
+                    const uint64_t db = b_desc + (uint64_t)((uint32_t)(K32 + 2 * k) * cu + (cu << 16));
+                    umma_bf16_ts(d_addr, tmem_base + (uint32_t)(kTmemA + 8 * (S32 + k)), db, kIdescBf16, 1u);
+                }
+                umma_commit(bar_empty + s);
+                umma_commit(bar_tfull + ts);
+            }
+            __syncwarp();
+            if (++s == kStages) { s = 0; ph ^= 1u; }
+        }
+    } else {
+        // ===== epilogue warps 2..9: lane quarter lqi = warp & 3, column half of every tile = (warp - 2) >> 2
+        const int lqi = warp & 3;
+        const int lq = lqi * 32;
+        const int half = (warp - 2) >> 2;
+        const int n = prm.n;
+        {
+            // A operand: thread <-> TMEM lane <-> row L of the tile (32x32b stores), the two warps of a lane
+            // quarter write alternate K-steps
+            const int L = lq + lane;
+            const int64_t i = I * kTile + L;
+            float sv[NP], gr[NP];
+#pragma unroll
+            for (int c = 0; c < NC; ++c) {
+                const float4 s4 = *reinterpret_cast<const float4*>(ST + i * NP + 4 * c);
+                sv[4 * c] = s4.x; sv[4 * c + 1] = s4.y; sv[4 * c + 2] = s4.z; sv[4 * c + 3] = s4.w;
+            }
+#pragma unroll
+            for (int p = 0; p < NP; ++p) {
+                const float v = prm.gamma * (1.f - sv[p]);
+                gr[p] = (p < n) ? (((i >> p) & 1) ? -v : v) : 0.f;
+            }
+            const float Ci = Cst[i];
+            auto bitf = [&](int p) -> float { return (p < n && ((i >> p) & 1)) ? 1.f : 0.f; };
+            auto a32 = [&](int chunk, int e) -> float {
+                if (chunk > 3 * NC) return 0.f;
+                if (chunk == 3 * NC) return e == 0 ? tf_hi(Ci) : e == 1 ? tf_lo(Ci) : 1.f;
+                const int f = chunk / NC, p = 4 * (chunk - f * NC) + e;
+                return f == 0 ? tf_hi(sv[p]) : f == 1 ? tf_hi(gr[p]) : bitf(p);
+            };
+            auto a16 = [&](int e) -> float {
+                const int f = e / NP, p = e - f * NP;
+                return f == 0 ? sv[p] : f == 1 ? tf_lo(sv[p]) : f == 2 ? tf_lo(gr[p]) : bitf(p);
+            };
+#pragma unroll
+            for (int ks = 0; ks < S32 + S16; ++ks) {
+                if ((ks & 1) == half) {
+                    uint32_t av[8];
+                    if (ks < S32) {
+#pragma unroll
+                        for (int e = 0; e < 4; ++e) {
+                            av[e] = __float_as_uint(a32(2 * ks, e));
+                            av[4 + e] = __float_as_uint(a32(2 * ks + 1, e));
+                        }
+                    } else {
+#pragma unroll
+                        for (int c = 0; c < 8; ++c)
+                            av[c] = bf16_pack(a16(16 * (ks - S32) + 2 * c), a16(16 * (ks - S32) + 2 * c + 1));
+                    }
+                    asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};"
+                                 ::"r"(tmem_base + ((uint32_t)lq << 16) + (uint32_t)(kTmemA + 8 * ks)),
+                                   "r"(av[0]), "r"(av[1]), "r"(av[2]), "r"(av[3]), "r"(av[4]), "r"(av[5]), "r"(av[6]), "r"(av[7])
+                                 : "memory");
+                }
+            }
+            asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(bar_aready);
+        }
+        // Main loop: thread t owns rows rq + 8k (k = 0..3) of its lane quarter and columns 8m + 2(t&3) + {0,1}
+        // (m = 0..7) of its column half.  In-tile state bits: row bits 0-2 = t>>2, 3-4 = k, 5-6 = lqi;
+        // column bit 0 = e, bits 1-2 = t&3, bits 3-5 = m, bit 6 = half.
+        const int t = lane;
+        const int rq = lq + (t >> 2);
+        float2 T2[3][2];                                   // a^(in-tile Hamming distance), packed over e
+        {
+            const int i0 = (t >> 2) & 1;
+            const int c0 = __popc((unsigned)(((t >> 3) & 3) ^ (t & 3))) + (((lqi >> 1) ^ half) & 1);
+#pragma unroll
+            for (int h = 0; h < 3; ++h)
+#pragma unroll
+                for (int mh = 0; mh < 2; ++mh) {
+                    const int e0 = c0 + h + ((lqi & 1) ^ mh);
+                    T2[h][mh] = make_float2(sWl[e0 + i0], sWl[e0 + (i0 ^ 1)]);
+                }
+        }
+        float qi[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) qi[k] = qT[I * kTile + rq + 8 * k];
+        float uhi[4] = {0.f, 0.f, 0.f, 0.f}, ulo[4] = {0.f, 0.f, 0.f, 0.f};
+        const bool b4 = (t & 16) != 0, b3 = (t & 8) != 0, b2 = (t & 4) != 0;
+        for (int64_t it = 0; it < n_local; ++it) {
+            const int ts = (int)(it & 1);
+            const uint32_t tph = (uint32_t)((it >> 1) & 1);
+            const int qs = (int)(it & (kQSlots - 1));
+            const uint32_t qph = (uint32_t)((it / kQSlots) & 1);
+            const int64_t J = j_begin + it;
+            const float wg = sWl[__popc((uint32_t)I ^ (uint32_t)J)];
+            mbar_wait(bar_qfull + qs, qph);
+            mbar_wait(bar_tfull + ts, tph);
+            tc_fence_after();
+            const uint32_t taddr = tmem_base + ((uint32_t)lq << 16) + (uint32_t)(ts * kTile + half * 64);
+            uint32_t v0[32], v1[32];
+            TNK_LD_16x256b_x8(v0, taddr);
+            TNK_LD_16x256b_x8(v1, taddr + (16u << 16));
+            float2 qj[8];
+            {
+                const float2* q2 = reinterpret_cast<const float2*>(sQ + qs * kTile + half * 64 + 2 * (t & 3));
+#pragma unroll
+                for (int m = 0; m < 8; ++m) {
+                    const float2 x = q2[4 * m];
+                    qj[m] = make_float2(wg * x.x, wg * x.y);
+                }
+            }
+            float qiw[4];
+#pragma unroll
+            for (int k = 0; k < 4; ++k) qiw[k] = wg * qi[k];
+            asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(bar_tempty + ts);
+            float2 racc[4], cacc[8];
+#pragma unroll
+            for (int k = 0; k < 4; ++k) racc[k] = make_float2(0.f, 0.f);
+#pragma unroll
+            for (int m = 0; m < 8; ++m) cacc[m] = make_float2(0.f, 0.f);
+            auto fold = [&](const uint32_t (&v)[32], const int hr) {
+#pragma unroll
+                for (int m = 0; m < 8; ++m)
+#pragma unroll
+                    for (int r = 0; r < 2; ++r) {
+                        const int k = 2 * hr + r;
+                        const int d = (k ^ m) & 3;            // row bits 3-4 against column bits 3-4
+                        const float2 acc = make_float2(__uint_as_float(v[4 * m + 2 * r]), __uint_as_float(v[4 * m + 2 * r + 1]));
+                        const float2 p = __fmul2_rn(T2[(d & 1) + (d >> 1)][m >> 2], acc);
+                        racc[k] = __ffma2_rn(p, qj[m], racc[k]);
+                        cacc[m] = __ffma2_rn(p, make_float2(qiw[k], qiw[k]), cacc[m]);
+                    }
+            };
+            fold(v0, 0);
+            fold(v1, 1);
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const float utile = racc[k].x + racc[k].y;
+                const float sum = uhi[k] + utile;           // TwoSum
+                const float bb = sum - uhi[k];
+                ulo[k] += (uhi[k] - (sum - bb)) + (utile - bb);
+                uhi[k] = sum;
+            }
+            if (J != I) {
+                // mirrored part: sum over the warp's 32 rows, exchanging halves of the column set per level
+                float2 c1[4], c2[2], c3;
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    const float2 send = b4 ? cacc[k] : cacc[k + 4], keep = b4 ? cacc[k + 4] : cacc[k];
+                    c1[k].x = keep.x + __shfl_xor_sync(0xffffffffu, send.x, 16);
+                    c1[k].y = keep.y + __shfl_xor_sync(0xffffffffu, send.y, 16);
+                }
+#pragma unroll
+                for (int k = 0; k < 2; ++k) {
+                    const float2 send = b3 ? c1[k] : c1[k + 2], keep = b3 ? c1[k + 2] : c1[k];
+                    c2[k].x = keep.x + __shfl_xor_sync(0xffffffffu, send.x, 8);
+                    c2[k].y = keep.y + __shfl_xor_sync(0xffffffffu, send.y, 8);
+                }
+                {
+                    const float2 send = b2 ? c2[0] : c2[1], keep = b2 ? c2[1] : c2[0];
+                    c3.x = keep.x + __shfl_xor_sync(0xffffffffu, send.x, 4);
+                    c3.y = keep.y + __shfl_xor_sync(0xffffffffu, send.y, 4);
+                }
+                // thread t now holds columns 2t, 2t+1 of the half; add the 4 lane quarters through shared memory
+                float* col = sCol + (ts * 4) * kTile + half * 64;
+                *reinterpret_cast<float2*>(col + lqi * kTile + 2 * t) = c3;
+                if (half == 0) asm volatile("bar.sync 2, 128;" ::: "memory");
+                else asm volatile("bar.sync 3, 128;" ::: "memory");
+                if (lqi == 0) {
+                    const float2 x0 = *reinterpret_cast<const float2*>(col + 2 * t);
+                    const float2 x1 = *reinterpret_cast<const float2*>(col + kTile + 2 * t);
+                    const float2 x2 = *reinterpret_cast<const float2*>(col + 2 * kTile + 2 * t);
+                    const float2 x3 = *reinterpret_cast<const float2*>(col + 3 * kTile + 2 * t);
+                    double* dst = ucol + J * kTile + half * 64 + 2 * t;
+                    atomicAdd(dst, (double)((x0.x + x1.x) + (x2.x + x3.x)));
+                    atomicAdd(dst + 1, (double)((x0.y + x1.y) + (x2.y + x3.y)));
+                }
+            }
+        }
+        // row sums: over the 4 threads sharing a row, then over the two column halves
+        double ud[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            double x = (double)uhi[k] + (double)ulo[k];
+            x += __shfl_xor_sync(0xffffffffu, x, 1);
+            x += __shfl_xor_sync(0xffffffffu, x, 2);
+            ud[k] = x;
+        }
+        if (half == 1 && (t & 3) == 0) {
+#pragma unroll
+            for (int k = 0; k < 4; ++k) sRed[rq + 8 * k] = ud[k];
+        }
+        asm volatile("bar.sync 1, 256;" ::: "memory");
+        if (half == 0 && (t & 3) == 0) {
+#pragma unroll
+            for (int k = 0; k < 4; ++k)
+                part[(size_t)blockIdx.y * prm.part_stride + (size_t)blockIdx.x * kTile + rq + 8 * k] = ud[k] + sRed[rq + 8 * k];
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        __syncwarp();
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(kTmemCols) : "memory");
+    }
+}
+
 }  // namespace
 
 // Host planner: chunk products (A-chunk x B-chunk) of the bracket, two per MMA K-step.
@@ -621,5 +1049,65 @@ int tnk_tc_launch(int n, double a, double gamma, const double* wl, const float* 
     if (rc) return rc;
     if (ev_stop) TNK_CUDA_OK(cudaEventRecord(ev_stop, st));
     if (launches) *launches += 3;
+    return 0;
+}
+
+// ---- symmetric variant: host side
+size_t tnk_tcs_table_bytes(int n, int64_t states) {
+    const int nc = ((n + 3) / 4);
+    return (size_t)states * (size_t)tcs_kb(nc) * 16;
+}
+
+namespace {
+template <int NC>
+int launch_sym(const TcsParams& prm, dim3 grid, const float* B_tab, const float* ST, const float* Cst,
+               const float* qT, double* part, double* ucol, cudaStream_t st) {
+    const size_t smem = TcsSmem<NC>::total;
+    auto kern = tcs_tiles_kernel<NC>;
+    TNK_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    kern<<<grid, kTcThreads, smem, st>>>(prm, B_tab, ST, Cst, qT, part, ucol);
+    TNK_CUDA_OK(cudaGetLastError());
+    return 0;
+}
+}  // namespace
+
+// Builds the (q-independent) column table unless the caller vouches for the one in B_tab, zeroes ucol and
+// launches the symmetric tile kernel for row tiles tile_offset + k*tile_stride, k < row_tiles.
+int tnk_tcs_launch(int n, double gamma, const double* wl, const float* ST, const float* Cst, const float* qT,
+                   int tile_offset, int tile_stride, int row_tiles, int splits, float* B_tab, int reuse_table,
+                   double* part, double* ucol, cudaEvent_t ev_start, cudaEvent_t ev_stop, int* launches,
+                   cudaStream_t st) {
+    TNK_REQUIRE(n >= TNK_TC_MIN_LATENT && n <= TNK_TC_MAX_LATENT, "tnk_ksd_sym: n=%d outside %d..%d", n,
+                TNK_TC_MIN_LATENT, TNK_TC_MAX_LATENT);
+    const int np = ((n + 3) / 4) * 4, nc = np / 4;
+    const int64_t N = (int64_t)1 << n;
+    const int64_t col_tiles = N / kTile;
+    if (!reuse_table) {
+        const int64_t items = col_tiles * tcs_kb(nc) * kTile;
+        tcs_pack_kernel<<<(unsigned)((items + 255) / 256), 256, 0, st>>>(n, np, col_tiles, (float)gamma, ST, Cst,
+                                                                        reinterpret_cast<uint4*>(B_tab));
+        TNK_CUDA_OK(cudaGetLastError());
+        if (launches) *launches += 1;
+    }
+    TNK_CUDA_OK(cudaMemsetAsync(ucol, 0, (size_t)N * sizeof(double), st));
+    if (row_tiles <= 0) return 0;
+    TcsParams prm;
+    prm.n = n; prm.tile_offset = tile_offset; prm.tile_stride = tile_stride; prm.n_tiles = col_tiles;
+    prm.col_splits = splits; prm.part_stride = (int64_t)row_tiles * kTile; prm.gamma = (float)gamma;
+    for (int h = 0; h < 32; ++h) prm.wl[h] = (float)wl[h];
+    if (ev_start) TNK_CUDA_OK(cudaEventRecord(ev_start, st));
+    dim3 grid((unsigned)row_tiles, (unsigned)splits, 1);
+    int rc = 2;
+    switch (nc) {
+        case 2: rc = launch_sym<2>(prm, grid, B_tab, ST, Cst, qT, part, ucol, st); break;
+        case 3: rc = launch_sym<3>(prm, grid, B_tab, ST, Cst, qT, part, ucol, st); break;
+        case 4: rc = launch_sym<4>(prm, grid, B_tab, ST, Cst, qT, part, ucol, st); break;
+        case 5: rc = launch_sym<5>(prm, grid, B_tab, ST, Cst, qT, part, ucol, st); break;
+        case 6: rc = launch_sym<6>(prm, grid, B_tab, ST, Cst, qT, part, ucol, st); break;
+        default: tnk_set_error("tnk_ksd_sym: no kernel instance for %d chunks", nc); break;
+    }
+    if (rc) return rc;
+    if (ev_stop) TNK_CUDA_OK(cudaEventRecord(ev_stop, st));
+    if (launches) *launches += 1;
     return 0;
 }

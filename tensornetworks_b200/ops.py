@@ -143,6 +143,38 @@ class SteinTables:
         return u, part
 
 
+    def ksd_sym(self, q, tile_offset=0, tile_stride=1):
+        """Symmetric tensor-core evaluation (tnk_ksd_sym): every unordered pair of 128-state tiles is evaluated
+        once and feeds both its row tile and, mirrored, its column tile.  This call owns the row tiles
+        tile_offset + k*tile_stride; returns (u_partial [N] fp64, part [1] fp64) whose sums over all offsets of
+        one stride are u = K_p q and KSD^2.  Needs the fp32 tables (precision "tc32" or "fp32"), 7 <= n <= 24."""
+        if self.dtype != torch.float32:
+            raise ValueError('the symmetric tile kernel reads the fp32 tables: build SteinTables with precision "tc32"')
+        if q.device != self.device or q.dim() != 1 or q.numel() != self.N:
+            raise ValueError(f"q must be a 1-D tensor of {self.N} entries on {self.device}")
+        if q.dtype not in (torch.float32, torch.float64):
+            raise ValueError("q must be float32 or float64")
+        q = q.contiguous()
+        lib = _lib.load()
+        with torch.cuda.device(self.device):
+            key = ("sym", tile_offset, tile_stride)
+            reuse = key in self._ws
+            if not reuse:
+                nbytes = lib.tnk_ksd_sym_workspace_bytes(self.n, tile_offset, tile_stride)
+                if nbytes == 0:
+                    raise RuntimeError(f"tnk_ksd_sym_workspace_bytes rejected n={self.n}, tiles ({tile_offset}, {tile_stride})")
+                self._ws[key] = torch.empty(nbytes, dtype=torch.uint8, device=self.device)
+            ws = self._ws[key]
+            u = torch.empty(self.N, dtype=torch.float64, device=self.device)
+            part = torch.empty(1, dtype=torch.float64, device=self.device)
+            launched = ctypes.c_int(0)
+            _lib.check(lib.tnk_ksd_sym(self.n, self.length_scale, _ptr(q), 0 if q.dtype == torch.float64 else 1,
+                                       _ptr(self.ST), _ptr(self.Cst), tile_offset, tile_stride, 1 if reuse else 0,
+                                       _ptr(u), _ptr(part), _ptr(ws), ws.numel(), ctypes.byref(launched),
+                                       _stream_ptr(self.device)), "tnk_ksd_sym")
+            launch_counter["kernels"] += launched.value
+        return u, part
+
     def _st64(self):
         """fp64 packed score table [n_pad, np] (bit order) for the mode-product path; the fp64-mode
         tables already hold it, fp32-mode tables build it on first use."""
@@ -320,6 +352,12 @@ class _KsdQuadraticForm(torch.autograd.Function):
                 buf = torch.cat([u, part])
                 dist.all_reduce(buf, op=dist.ReduceOp.SUM, group=group)
                 u, part = buf[:-1], buf[-1:].clone()
+        elif algorithm == "pairs_sym":
+            u, part = tables.ksd_sym(q_dev, rank, world)    # row tiles dealt round-robin: equal triangle shares
+            if world > 1:
+                buf = torch.cat([u, part])
+                dist.all_reduce(buf, op=dist.ReduceOp.SUM, group=group)
+                u, part = buf[:-1], buf[-1:].clone()
         elif exchange is not None and world > 1:
             u, part = ksd_rows_fused(tables, q_dev, exchange)
             u = u.clone()     # the symmetric buffer is rewritten two evaluations later
@@ -340,7 +378,7 @@ class _KsdQuadraticForm(torch.autograd.Function):
         return grad.to(device=device, dtype=dtype), None, None, None, None
 
 
-ALGORITHMS = ("pairs", "modeproduct")
+ALGORITHMS = ("pairs", "pairs_sym", "modeproduct")
 
 
 def ksd_quadratic_form(q, tables, group=None, algorithm="pairs", exchange=None):
@@ -349,6 +387,9 @@ def ksd_quadratic_form(q, tables, group=None, algorithm="pairs", exchange=None):
     loop of reference ksd_vi.py:110-131 / ksd_vi_quantum.py:122-142.  When torch.distributed is
     initialised the rows of the pair space are sharded over the ranks of `group`.
     algorithm="pairs" evaluates all 4^n pairs on the fly (the reference's loop, tiled);
+    algorithm="pairs_sym" evaluates every unordered pair of 128-state tiles once on the tensor cores and uses
+    k_p(z,z') = k_p(z',z) for the mirrored half (fp32-grade, tables of precision "tc32"; row tiles are dealt
+    round-robin over the ranks and u is sum-all-reduced);
     algorithm="modeproduct" returns the same value through the Kronecker factorisation of the
     Hamming kernel in O(n^2 2^n) (fp64), with the score components sharded over the ranks.
     exchange: a PeerExchange makes the sharded "pairs" evaluation store its rows straight into every
