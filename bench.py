@@ -32,6 +32,9 @@ def parse_args():
     ap.add_argument("--n", "--latent-bits", dest="n", type=int, default=20, help="latent bits (BASELINE.json quotes the metric at n=20)")
     ap.add_argument("--precision", default="tc32", choices=["fp32", "fp64", "tc32"],
                     help="pair-kernel arithmetic: fp32/fp64 ALU kernels or tc32 = tcgen05 tf32 tiles with 3xTF32 split")
+    ap.add_argument("--algorithm", default="auto", choices=["auto", "pairs", "pairs_sym"],
+                    help="tc32 only: pairs_sym evaluates every unordered pair of 128-state tiles once (tnk_ksd_sym); "
+                         "pairs evaluates all 4^n ordered pairs (tnk_ksd_rows); auto = pairs_sym where it exists (7 <= n <= 24)")
     ap.add_argument("--seed", type=int, default=0)
     ap.add_argument("--exchange", default="fused", choices=["fused", "nccl"],
                     help="N>1: rows stored into every rank's buffer by the reduction kernel over NVLink (fused) "
@@ -187,8 +190,13 @@ def run_ours(args):
     q_dev = q_host.to(device)
     flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=device)  # > 126 MB L2
     r0, r1 = ops.shard_rows(N, rank, world)
+    sym = args.precision == "tc32" and args.algorithm in ("auto", "pairs_sym") and 7 <= n <= 24
+    if args.algorithm == "pairs_sym" and not sym:
+        raise SystemExit("--algorithm pairs_sym needs --precision tc32 and 7 <= n <= 24")
     exchange, exchange_name = None, args.exchange
-    if world > 1 and args.exchange == "fused":
+    if sym:
+        exchange_name = "sum-all-reduce of u (NCCL)"
+    if world > 1 and args.exchange == "fused" and not sym:
         try:
             exchange = ops.PeerExchange(N, device)
         except Exception as exc:      # no P2P mapping between these GPUs: keep the NCCL exchange, say so
@@ -201,6 +209,13 @@ def run_ours(args):
             torch.cuda.synchronize()
 
     def device_step():
+        if sym:
+            u, part = tables.ksd_sym(q_dev, rank, world)          # row tiles rank, rank + world, ...
+            if world > 1:
+                buf = torch.cat([u, part])
+                dist.all_reduce(buf, op=dist.ReduceOp.SUM)
+                u, part = buf[:-1], buf[-1:]
+            return u, part
         if exchange is not None:
             return ops.ksd_rows_fused(tables, q_dev, exchange)   # K3 + K4 with peer stores + barrier
         u, part = tables.ksd_rows(q_dev, r0, r1)
@@ -211,7 +226,8 @@ def run_ours(args):
     def e2e_step():
         qh = q_host.requires_grad_(True)
         qh.grad = None
-        K = ops.ksd_quadratic_form(qh, tables, exchange=exchange)   # H2D of q inside, public differentiable op
+        K = ops.ksd_quadratic_form(qh, tables, exchange=exchange,   # H2D of q inside, public differentiable op
+                                   algorithm="pairs_sym" if sym else "pairs")
         K.backward()                               # D2H of dK/dq inside
         return float(K.item()), qh.grad
 
@@ -270,6 +286,27 @@ def run_ours(args):
 
     # ---- context lines (not the headline): the fp32 ALU pair kernel on the same rows, and the
     # enumeration kernels K1+K2 (joint + score tables) as GB/s
+    full_ms = None
+    if sym:
+        # context: the tile kernel that executes all 4^n ordered pairs (tnk_ksd_rows, precision tc32) on this rank's rows
+        f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        f0.record(); f1.record()
+        tables.ksd_rows(q_dev, r0, r1)
+        times = []
+        for _ in range(2):
+            flush.zero_()
+            ops.time_pair_kernel(f0, f1)
+            u_full, _ = tables.ksd_rows(q_dev, r0, r1)
+            torch.cuda.synchronize()
+            times.append(f0.elapsed_time(f1))
+        ops.time_pair_kernel(None, None)
+        full_t = torch.tensor([float(np.mean(times))], dtype=torch.float64, device=device)
+        if world > 1:
+            dist.all_reduce(full_t, op=dist.ReduceOp.MAX)
+        full_ms = full_t.item()
+        full_err = float(((u_full[r0:r1] - u[r0:r1]).abs().max() / u.abs().max()).item())
+        del u_full
+        tables._ws = {k: v for k, v in tables._ws.items() if not (isinstance(k, tuple) and len(k) == 2 and k == (r0, r1))}
     alu = None
     if args.precision == "tc32":
         t_alu = ops.SteinTables(tables.P, n, precision="fp32")
@@ -398,7 +435,27 @@ def main():
                     "kernel": "ksd_rows_kernel", "kernel_ms": r["kmean_ms"].item(),
                     "lane_ops_per_pair": w_lane,
                     "peak_source": "tnk_alu_peak FMA-chain probe measured in this run (MEASURED_PEAKS.json has no ALU peak)"}
-        if args.precision == "tc32":
+        if r["sym"]:
+            # symmetric tile kernel: rank 0 owns row tiles 0, world, 2 world, ...; row tile I meets column tiles I..T-1
+            T = (1 << n) // 128
+            tiles = sum(T - I for I in range(0, T, world))
+            nc = (n + 3) // 4
+            s32, s16 = ((3 * nc + 2) & ~1) // 2, nc
+            flops_tile = 128 * 128 * 2 * 8 * (s32 + s16)
+            peaks = load_measured_peaks()
+            bf16 = peaks.get("bf16_tflops_sustained") or peaks.get("bf16_tflops")
+            peak_tf = (bf16 / 2.0) if bf16 else 1590.0 / 2.0
+            ach_tf = tiles * flops_tile / kernel_s / 1e12
+            roofline = {"bound": "tensor", "achieved": ach_tf, "peak": peak_tf, "unit": "TFLOP/s",
+                        "frac": ach_tf / peak_tf, "traffic": None, "kernel": "tcs_tiles_kernel",
+                        "kernel_ms": r["kmean_ms"].item(), "executed_tiles_128x128": tiles,
+                        "ordered_pairs_per_executed_pair": (pairs / world) / (tiles * 16384.0),
+                        "k_steps_tf32": s32, "k_steps_bf16": s16,
+                        "peak_source": ("half of MEASURED_PEAKS.json bf16_tflops_sustained (kind::tf32 runs at half the "
+                                        "bf16 rate; the kernel is timed inside a long step)" if bf16 else
+                                        "half of the fallback 1.59 PFLOP/s bf16 figure of B200_PROFILING.md"),
+                        "alu_epilogue_lane_ops_per_executed_pair": 4.5}
+        elif args.precision == "tc32":
             from tensornetworks_b200 import ops as _ops
             plan = _ops.tc_plan(n)
             # tf32-equivalent MMA flops issued per pair: a tf32 K-step (K = 8) and a bf16 K-step (K = 16) occupy
@@ -416,7 +473,7 @@ def main():
                                         "bf16 rate; the kernel is timed inside a long step)" if bf16 else
                                         "half of the fallback 1.59 PFLOP/s bf16 figure of B200_PROFILING.md"),
                         "alu_epilogue_lane_ops_per_pair": 1.5}
-        traffic = ncu_traffic("tc_rows" if args.precision == "tc32" else "ksd_rows", n) if world == 1 else None
+        traffic = ncu_traffic("tcs_tiles" if r["sym"] else "tc_rows" if args.precision == "tc32" else "ksd_rows", n) if world == 1 else None
         if traffic:
             roofline["traffic"], roofline["traffic_source"] = traffic[0], f"profiles/{traffic[1]} (bytes per launch)"
         line = {
@@ -427,13 +484,21 @@ def main():
             "config": {"workload": workload_name(n), "n_latent": n, "pairs_per_step": pairs,
                        "precision_mode": {"fp32": "fp32-compute/fp64-accumulate", "fp64": "fp64",
                                           "tc32": "3xTF32 tensor-core tiles (fp32 accumulate per tile, fp64 across tiles)"}[args.precision],
-                       "parallelism": (f"row-sharded x{world}, exchange={r['exchange_name']}" if world > 1 else "single GPU"),
-                       "l2": "256 MB flush written between timed steps", "executed_pairs": "4^n (symmetry not exploited)"},
+                       "parallelism": ((f"row tiles dealt round-robin x{world}, {r['exchange_name']}" if r["sym"] else
+                                        f"row-sharded x{world}, exchange={r['exchange_name']}") if world > 1 else "single GPU"),
+                       "l2": "256 MB flush written between timed steps",
+                       "executed_pairs": ("N(N+128)/2: every unordered pair of 128-state tiles evaluated once, the symmetry "
+                                          "k_p(z,z') = k_p(z',z) supplies the mirrored half (SURVEY.md 8d); value = 4^n / t"
+                                          if r["sym"] else "4^n (symmetry not exploited)")},
             "roofline": roofline,
             "e2e": {"value": r["e2e_value"], "unit": UNIT, "h2d_bytes_per_step": 8 * (1 << n) * world,
                     "d2h_bytes_per_step": (8 * (1 << n) + 8) * world},
             "gpu_launches": r["launches"], "clocks": r["clocks"], "ksd_sq": r["K_value"],
         }
+        if r["full_ms"] is not None:
+            line["full_tile_kernel"] = {"kernel": "tc_rows_kernel (all 4^n ordered pairs, tnk_ksd_rows precision tc32)",
+                                        "kernel_ms": r["full_ms"], "value": pairs / (r["full_ms"] * 1e-3), "unit": UNIT,
+                                        "u_vs_headline_kernel_max_rel": r["full_err"]}
         if r["alu"] is not None:
             alu_s = r["alu"] * 1e-3
             alu_ach = executed * w_lane / alu_s

@@ -555,8 +555,7 @@ tc_rows_kernel(const __grid_constant__ TcParams prm, const float* __restrict__ B
 // distribution: thread t of a warp holds rows t/4 + 8k, k = 0..3, and columns 8m + 2(t%4) + {0,1}, m = 0..7
 // of its warp's 32 x 64 block), so a thread owns a 4 x 16 patch: the mirrored column sums are reduced over
 // its 4 rows in registers and over the 8 row groups of the warp with a transposing exchange (14 SHFL),
-// then over the 4 lane quarters through shared memory and added to ucol[] with one fp64 RED per column and
-// tile.  The Hamming weight of the 7 in-tile bits factorises over the patch: per-thread constant x
+// then added to ucol[] with one fp64 RED per column, warp and tile (the 4 lane quarters meet in L2).  The Hamming weight of the 7 in-tile bits factorises over the patch: per-thread constant x
 // (compile-time power of a from the unrolled row/column slots) -> 6 packed weights in registers.
 // Row sums: fp32 per tile, compensated fp32 across tiles, fp64 at the end (as in tc_rows_kernel).
 // Column sums arrive in ucol[] by atomics, so the last bits of u depend on the arrival order.
@@ -630,8 +629,7 @@ struct TcsSmem {
     static constexpr int stages = (4u * b_bytes <= 216u * 1024u) ? 4 : 3;
     static constexpr uint32_t off_b = 0;
     static constexpr uint32_t off_q = off_b + stages * b_bytes;           // [kQSlots][128] float: q of the column tile
-    static constexpr uint32_t off_col = off_q + kQSlots * kTile * 4;      // [2][4][128] float: column sums per lane quarter
-    static constexpr uint32_t off_wl = off_col + 2 * 4 * kTile * 4;       // [32] float
+    static constexpr uint32_t off_wl = off_q + kQSlots * kTile * 4;       // [32] float
     static constexpr uint32_t off_red = off_wl + 32 * 4;                  // [128] double
     static constexpr uint32_t off_bar = off_red + kTile * 8;              // mbarriers
     static constexpr int n_bars = 1 + 2 * kMaxStages + 4 + kQSlots;
@@ -679,7 +677,6 @@ tcs_tiles_kernel(const __grid_constant__ TcsParams prm, const float* __restrict_
 
     unsigned char* sB = smem + SM::off_b;
     float* sQ = reinterpret_cast<float*>(smem + SM::off_q);
-    float* sCol = reinterpret_cast<float*>(smem + SM::off_col);
     float* sWl = reinterpret_cast<float*>(smem + SM::off_wl);
     double* sRed = reinterpret_cast<double*>(smem + SM::off_red);
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + SM::off_bar);
@@ -862,14 +859,8 @@ tcs_tiles_kernel(const __grid_constant__ TcsParams prm, const float* __restrict_
             {
                 const float2* q2 = reinterpret_cast<const float2*>(sQ + qs * kTile + half * 64 + 2 * (t & 3));
 #pragma unroll
-                for (int m = 0; m < 8; ++m) {
-                    const float2 x = q2[4 * m];
-                    qj[m] = make_float2(wg * x.x, wg * x.y);
-                }
+                for (int m = 0; m < 8; ++m) qj[m] = q2[4 * m];
             }
-            float qiw[4];
-#pragma unroll
-            for (int k = 0; k < 4; ++k) qiw[k] = wg * qi[k];
             asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
             tc_fence_before();
             __syncwarp();
@@ -889,14 +880,14 @@ tcs_tiles_kernel(const __grid_constant__ TcsParams prm, const float* __restrict_
                         const float2 acc = make_float2(__uint_as_float(v[4 * m + 2 * r]), __uint_as_float(v[4 * m + 2 * r + 1]));
                         const float2 p = __fmul2_rn(T2[(d & 1) + (d >> 1)][m >> 2], acc);
                         racc[k] = __ffma2_rn(p, qj[m], racc[k]);
-                        cacc[m] = __ffma2_rn(p, make_float2(qiw[k], qiw[k]), cacc[m]);
+                        cacc[m] = __ffma2_rn(p, make_float2(qi[k], qi[k]), cacc[m]);
                     }
             };
             fold(v0, 0);
             fold(v1, 1);
 #pragma unroll
             for (int k = 0; k < 4; ++k) {
-                const float utile = racc[k].x + racc[k].y;
+                const float utile = wg * (racc[k].x + racc[k].y);
                 const float sum = uhi[k] + utile;           // TwoSum
                 const float bb = sum - uhi[k];
                 ulo[k] += (uhi[k] - (sum - bb)) + (utile - bb);
@@ -922,20 +913,12 @@ tcs_tiles_kernel(const __grid_constant__ TcsParams prm, const float* __restrict_
                     c3.x = keep.x + __shfl_xor_sync(0xffffffffu, send.x, 4);
                     c3.y = keep.y + __shfl_xor_sync(0xffffffffu, send.y, 4);
                 }
-                // thread t now holds columns 2t, 2t+1 of the half; add the 4 lane quarters through shared memory
-                float* col = sCol + (ts * 4) * kTile + half * 64;
-                *reinterpret_cast<float2*>(col + lqi * kTile + 2 * t) = c3;
-                if (half == 0) asm volatile("bar.sync 2, 128;" ::: "memory");
-                else asm volatile("bar.sync 3, 128;" ::: "memory");
-                if (lqi == 0) {
-                    const float2 x0 = *reinterpret_cast<const float2*>(col + 2 * t);
-                    const float2 x1 = *reinterpret_cast<const float2*>(col + kTile + 2 * t);
-                    const float2 x2 = *reinterpret_cast<const float2*>(col + 2 * kTile + 2 * t);
-                    const float2 x3 = *reinterpret_cast<const float2*>(col + 3 * kTile + 2 * t);
-                    double* dst = ucol + J * kTile + half * 64 + 2 * t;
-                    atomicAdd(dst, (double)((x0.x + x1.x) + (x2.x + x3.x)));
-                    atomicAdd(dst + 1, (double)((x0.y + x1.y) + (x2.y + x3.y)));
-                }
+                // thread t now holds columns 2t, 2t+1 of the half summed over the warp's 32 rows: one fp64 RED each
+                // (fire and forget; the four lane quarters meet in L2 - measured faster than combining them in
+                // shared memory behind a named barrier)
+                double* dst = ucol + J * kTile + half * 64 + 2 * t;
+                atomicAdd(dst, (double)(wg * c3.x));
+                atomicAdd(dst + 1, (double)(wg * c3.y));
             }
         }
         // row sums: over the 4 threads sharing a row, then over the two column halves
