@@ -12,7 +12,8 @@ changes is where the work happens:
 
 Extra keyword-only arguments (defaults keep reference behaviour): `precision` ("fp64" |
 "fp32" | "tc32") selects the pair-kernel arithmetic, `algorithm` ("pairs" = all 4^n pairs on the
-fly, "modeproduct" = the Kronecker form, O(n^2 2^n)), `compute_device` the CUDA device of the KSD
+fly, "pairs_sym" = every unordered pair of 128-state tiles once on the tensor cores (precision "tc32",
+7 <= n <= 24), "modeproduct" = the Kronecker form, O(n^2 2^n)), `compute_device` the CUDA device of the KSD
 kernels (the Born machine itself stays on `device`, as in the reference).
 """
 import math

@@ -157,3 +157,24 @@ def test_sym_matches_modeproduct_n20(ops):
     assert abs(k_sy.item() - k_mp.item()) <= TOL * abs(k_mp.item())
     assert (u_sy - u_mp).abs().max().item() <= TOL * scale
     assert (u_sy - u_tc).abs().max().item() <= TOL * scale
+
+
+def test_trainer_epochs_pairs_sym_match_fp64(ops):
+    """KSDVariationalInference.train with algorithm="pairs_sym" (eager and CUDA-graph epochs) follows the fp64
+    pair-kernel trajectory within the fp32-mode tolerance."""
+    from tensornetworks_b200.ksd_vi import KSDVariationalInference
+    n = 9
+    bn, lat, obs, x = random_binary_bn(n, seed=5)
+    hist = {}
+    for name, kw in (("fp64", dict(precision="fp64", algorithm="pairs")),
+                     ("sym", dict(precision="tc32", algorithm="pairs_sym")),
+                     ("sym_graph", dict(precision="tc32", algorithm="pairs_sym", cuda_graph=True))):
+        torch.manual_seed(1)
+        vi = KSDVariationalInference(bn, lat, obs, {"use_logits": True, "conditioning_dim": 0}, device="cuda",
+                                     compute_device="cuda", **kw)
+        hist[name] = vi.train(x, num_epochs=10, lr_born_machine=0.05, verbose=False)
+    for name in ("sym", "sym_graph"):
+        for key in ("loss_ksd", "entropy", "grad_norm"):
+            a, b = np.array(hist["fp64"][key], dtype=float), np.array(hist[name][key], dtype=float)
+            assert a.shape == b.shape == (10,), key
+            assert np.max(np.abs(a - b) / np.maximum(np.abs(a), 1e-12)) < 2e-3, (name, key, a, b)
