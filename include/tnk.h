@@ -172,18 +172,24 @@ int tnk_tc_plan(int n_latent, int* np, int* k32, int* kb, int* nsteps, int* nste
  * symmetric, stein_utils.py:161-196): the pair space is cut into 128 x 128-state tiles and every
  * UNORDERED pair of tiles is evaluated once - its values feed the rows of one tile and, mirrored, the
  * rows of the other - so N(N+128)/2 of the 4^n ordered pairs are executed.  fp32-grade
- * arithmetic as TNK_PREC_TC32 (1e-4 mode); 7 <= n <= 24.
+ * arithmetic (1e-4 mode); 7 <= n <= 24.
+ *   split      operand split of the tensor-core products:
+ *              TNK_SYM_SPLIT_TF32   tf32 high parts + bf16 cross terms (as TNK_PREC_TC32; ~2^-19 per product)
+ *              TNK_SYM_SPLIT_BF16X2 every real factor as two bf16 pieces (~2^-17 per product, 10 instead of 13
+ *                                   MMA K-steps per tile at n = 20)
  *   q          device double/float [N];  ST, Cst: the fp32 tables tnk_score emits for TNK_PREC_TC32
  *   tile_offset, tile_stride   this call owns row tiles tile_offset + k*tile_stride (k >= 0): rank g of G
  *              passes (g, G); (0, 1) is the whole evaluation
  *   reuse_table  non-zero: the workspace still holds the q-independent column table an earlier call built
- *              for the same n, length_scale, ST, Cst (skips the packing pass)
+ *              for the same n, length_scale, split, ST, Cst (skips the packing pass)
  *   u_partial  device double [N] (out): contributions of the owned tiles to u = K_p q, rows and mirrored
  *              columns; the sum over all offsets of one stride is u
  *   ksd_part   device double [1] (out): sum_z q_z u_partial[z]; the sum over all offsets is KSD^2
  * The mirrored sums are accumulated with fp64 atomics: the last bits of u_partial depend on their order. */
-size_t tnk_ksd_sym_workspace_bytes(int n_latent, int tile_offset, int tile_stride);
-int tnk_ksd_sym(int n_latent, double length_scale, const void* q, int q_dtype,
+#define TNK_SYM_SPLIT_TF32 0
+#define TNK_SYM_SPLIT_BF16X2 1
+size_t tnk_ksd_sym_workspace_bytes(int n_latent, int split, int tile_offset, int tile_stride);
+int tnk_ksd_sym(int n_latent, double length_scale, int split, const void* q, int q_dtype,
                 const void* ST, const void* Cst, int tile_offset, int tile_stride, int reuse_table,
                 double* u_partial, double* ksd_part,
                 void* workspace, size_t workspace_bytes, int* n_launch, void* stream);

@@ -23,6 +23,7 @@ NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", 
 PREC_FP64, PREC_FP32, PREC_FP64_SIMPLE, PREC_TC32 = 0, 1, 2, 4
 MAX_PEERS = 8  # TNK_MAX_PEERS
 MP_STORE = {"fp64": 0, "fp32": 1}  # TNK_MP_STORE_*
+SYM_SPLIT = {"tf32": 0, "bf16x2": 1}  # TNK_SYM_SPLIT_*
 
 # every symbol include/tnk.h declares
 EXPORTS = ["tnk_last_error", "tnk_version", "tnk_bn_joint", "tnk_ksd_layout", "tnk_score",
@@ -105,9 +106,9 @@ def load():
                                        c_int, c_int, ctypes.POINTER(c_vp), ctypes.POINTER(c_vp), c_vp,
                                        c_vp, c_sz, ctypes.POINTER(c_int), c_vp]
     lib.tnk_ksd_sym_workspace_bytes.restype = c_sz
-    lib.tnk_ksd_sym_workspace_bytes.argtypes = [c_int, c_int, c_int]
+    lib.tnk_ksd_sym_workspace_bytes.argtypes = [c_int, c_int, c_int, c_int]
     lib.tnk_ksd_sym.restype = c_int
-    lib.tnk_ksd_sym.argtypes = [c_int, c_dbl, c_vp, c_int, c_vp, c_vp, c_int, c_int, c_int, c_vp, c_vp,
+    lib.tnk_ksd_sym.argtypes = [c_int, c_dbl, c_int, c_vp, c_int, c_vp, c_vp, c_int, c_int, c_int, c_vp, c_vp,
                                 c_vp, c_sz, ctypes.POINTER(c_int), c_vp]
     lib.tnk_ksd_modeproduct_workspace_bytes.restype = c_sz
     lib.tnk_ksd_modeproduct_workspace_bytes.argtypes = [c_int, c_int, c_int, c_int]

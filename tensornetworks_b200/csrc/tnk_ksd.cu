@@ -668,12 +668,13 @@ struct SymPlan {
     size_t off_q, off_part, off_col, off_block, off_b, total;
 };
 
-int make_sym_plan(int n, int tile_offset, int tile_stride, SymPlan* p) {
+int make_sym_plan(int n, int split, int tile_offset, int tile_stride, SymPlan* p) {
     if (n < TNK_TC_MIN_LATENT || n > TNK_TC_MAX_LATENT || tile_stride < 1 || tile_offset < 0) return 1;
+    if (split != TNK_SYM_SPLIT_TF32 && split != TNK_SYM_SPLIT_BF16X2) return 1;
     p->N = (int64_t)1 << n;
     p->T = p->N / TNK_TC_TILE;
     p->row_tiles = tile_offset < p->T ? (int)((p->T - tile_offset + tile_stride - 1) / tile_stride) : 0;
-    const size_t b_bytes = tnk_tcs_table_bytes(n, p->N);
+    const size_t b_bytes = tnk_tcs_table_bytes(n, split, p->N);
     int splits = 1;
     while ((int64_t)p->row_tiles * splits < 8 * 148 && splits * 2 <= p->T) splits *= 2;
     while ((b_bytes / splits) > ((size_t)32 << 20) && splits * 2 <= p->T) splits *= 2;
@@ -722,20 +723,20 @@ finish_sym_kernel(const double* __restrict__ part, int splits, int64_t part_stri
 
 }  // namespace
 
-extern "C" size_t tnk_ksd_sym_workspace_bytes(int n_latent, int tile_offset, int tile_stride) {
+extern "C" size_t tnk_ksd_sym_workspace_bytes(int n_latent, int split, int tile_offset, int tile_stride) {
     SymPlan p;
-    if (make_sym_plan(n_latent, tile_offset, tile_stride, &p)) return 0;
+    if (make_sym_plan(n_latent, split, tile_offset, tile_stride, &p)) return 0;
     return p.total;
 }
 
-extern "C" int tnk_ksd_sym(int n_latent, double length_scale, const void* q, int q_dtype,
+extern "C" int tnk_ksd_sym(int n_latent, double length_scale, int split, const void* q, int q_dtype,
                            const void* ST, const void* Cst, int tile_offset, int tile_stride, int reuse_table,
                            double* u_partial, double* ksd_part,
                            void* workspace, size_t workspace_bytes, int* n_launch, void* stream) {
     SymPlan p;
-    TNK_REQUIRE(make_sym_plan(n_latent, tile_offset, tile_stride, &p) == 0,
-                "tnk_ksd_sym: bad arguments n=%d (supported %d..%d) tile_offset=%d tile_stride=%d", n_latent,
-                TNK_TC_MIN_LATENT, TNK_TC_MAX_LATENT, tile_offset, tile_stride);
+    TNK_REQUIRE(make_sym_plan(n_latent, split, tile_offset, tile_stride, &p) == 0,
+                "tnk_ksd_sym: bad arguments n=%d (supported %d..%d) split=%d tile_offset=%d tile_stride=%d", n_latent,
+                TNK_TC_MIN_LATENT, TNK_TC_MAX_LATENT, split, tile_offset, tile_stride);
     TNK_REQUIRE(q && ST && Cst && u_partial && ksd_part && workspace, "tnk_ksd_sym: NULL pointer argument");
     TNK_REQUIRE(q_dtype == 0 || q_dtype == 1, "tnk_ksd_sym: q_dtype must be 0 (double) or 1 (float)");
     TNK_REQUIRE(workspace_bytes >= p.total, "tnk_ksd_sym: workspace %zu < required %zu", workspace_bytes, p.total);
@@ -759,7 +760,7 @@ extern "C" int tnk_ksd_sym(int n_latent, double length_scale, const void* q, int
     else q_pack_kernel<float, float><<<qblocks, 256, 0, st>>>((const float*)q, p.N, p.N, qT);
     TNK_CUDA_OK(cudaGetLastError());
     ++launches;
-    const int rc = tnk_tcs_launch(n, gamma, wl, (const float*)ST, (const float*)Cst, qT, tile_offset, tile_stride,
+    const int rc = tnk_tcs_launch(n, split, gamma, wl, (const float*)ST, (const float*)Cst, qT, tile_offset, tile_stride,
                                   p.row_tiles, p.splits, (float*)(ws + p.off_b), reuse_table, part, ucol,
                                   g_ev_start, g_ev_stop, &launches, st);
     if (rc) return rc;

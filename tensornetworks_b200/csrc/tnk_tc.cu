@@ -560,10 +560,17 @@ tc_rows_kernel(const __grid_constant__ TcParams prm, const float* __restrict__ B
 // Row sums: fp32 per tile, compensated fp32 across tiles, fp64 at the end (as in tc_rows_kernel).
 // Column sums arrive in ucol[] by atomics, so the last bits of u depend on the arrival order.
 // ======================================================================================================
-__host__ __device__ constexpr int tcs_k32(int nc) { return (3 * nc + 2) & ~1; }     // 3nc + 1 chunks, padded to even
-__host__ __device__ constexpr int tcs_steps32(int nc) { return tcs_k32(nc) / 2; }
-__host__ __device__ constexpr int tcs_steps16(int nc) { return nc; }                // 4 np bf16 values / 16
-__host__ __device__ constexpr int tcs_kb(int nc) { return tcs_k32(nc) + 2 * nc; }
+// Operand format 0 (above): tf32 high parts + bf16 cross terms, ~2^-19 per product.  Format 1: every real factor
+// as TWO bf16 pieces x = x1 + x2 (x1 = bf(x), x2 = bf(x - x1), residual <= 2^-18 |x|), all K-steps kind::f16:
+//   A16 (rows):    s1 | s1 | s2 | g1 | g2 | bits | bits | c1 c2 c3 1 1 1        (g = gamma rho, c = C in three pieces)
+//   B16 (columns): s1 | s2 | s1 | bits | bits | g1 | g2 | 1 1 1 c1 c2 c3
+// 7 np + 6 values: 10 K-steps at n = 20 instead of 13, 320 instead of 416 table bytes per state, ~2^-17 per product.
+__host__ __device__ constexpr int tcs_k32(int nc, int fmt) { return fmt ? 0 : (3 * nc + 2) & ~1; }   // 3nc + 1 chunks, padded to even
+__host__ __device__ constexpr int tcs_steps32(int nc, int fmt) { return tcs_k32(nc, fmt) / 2; }
+__host__ __device__ constexpr int tcs_steps16(int nc, int fmt) { return fmt ? (7 * 4 * nc + 6 + 15) / 16 : nc; }
+__host__ __device__ constexpr int tcs_kb(int nc, int fmt) { return tcs_k32(nc, fmt) + 2 * tcs_steps16(nc, fmt); }
+
+__device__ __forceinline__ float bf_round(float x) { return __bfloat162float(__float2bfloat16_rn(x)); }
 
 struct TcsParams {
     int n;
@@ -577,10 +584,10 @@ struct TcsParams {
 
 // column operand table of the symmetric variant: q-independent, same slot layout as tc_pack_kernel
 __global__ void __launch_bounds__(256)
-tcs_pack_kernel(int n, int np, int64_t n_tiles, float gamma,
+tcs_pack_kernel(int n, int np, int fmt, int64_t n_tiles, float gamma,
                 const float* __restrict__ ST, const float* __restrict__ Cst, uint4* __restrict__ out) {
     const int nc = np >> 2;
-    const int K32 = tcs_k32(nc), K = tcs_kb(nc);
+    const int K32 = tcs_k32(nc, fmt), K = tcs_kb(nc, fmt);
     const int64_t idx = (int64_t)blockIdx.x * 256 + threadIdx.x;
     const int row = (int)(idx & (kTile - 1));
     const int64_t t = idx >> 7;
@@ -596,7 +603,34 @@ tcs_pack_kernel(int n, int np, int64_t n_tiles, float gamma,
     };
     auto bit = [&](int p) -> float { return (p < n && ((z >> p) & 1)) ? 1.f : 0.f; };
     uint32_t w[4] = {0u, 0u, 0u, 0u};
-    if (chunk < 3 * nc) {
+    if (fmt) {
+        float v[8];
+#pragma unroll
+        for (int x = 0; x < 8; ++x) {
+            const int e = 8 * chunk + x;
+            const int f = e / np, p = e - f * np;
+            float val = 0.f;
+            if (f < 7) {
+                if (f == 3 || f == 4) val = bit(p);
+                else {
+                    const float full = f < 3 ? srow[p] : grho(p);
+                    const float x1 = bf_round(full);
+                    val = (f == 1 || f == 6) ? bf_round(full - x1) : x1;
+                }
+            } else {
+                const int k = e - 7 * np;
+                if (k < 3) val = 1.f;
+                else if (k < 6) {
+                    const float C = Cst[z];
+                    const float c1 = bf_round(C), c2 = bf_round(C - c1);
+                    val = k == 3 ? c1 : k == 4 ? c2 : bf_round(C - c1 - c2);
+                }
+            }
+            v[x] = val;
+        }
+#pragma unroll
+        for (int e = 0; e < 4; ++e) w[e] = bf16_pack(v[2 * e], v[2 * e + 1]);
+    } else if (chunk < 3 * nc) {
         const int f = chunk / nc, c = chunk - f * nc;
 #pragma unroll
         for (int e = 0; e < 4; ++e) {
@@ -623,15 +657,15 @@ tcs_pack_kernel(int n, int np, int64_t n_tiles, float gamma,
     out[idx] = make_uint4(w[0], w[1], w[2], w[3]);
 }
 
-template <int NC>
+template <int NC, int FMT>
 struct TcsSmem {
-    static constexpr uint32_t b_bytes = (uint32_t)tcs_kb(NC) * kChunkBytes;
+    static constexpr uint32_t b_bytes = (uint32_t)tcs_kb(NC, FMT) * kChunkBytes;
     static constexpr int stages = (4u * b_bytes <= 216u * 1024u) ? 4 : 3;
     static constexpr uint32_t off_b = 0;
     static constexpr uint32_t off_q = off_b + stages * b_bytes;           // [kQSlots][128] float: q of the column tile
     static constexpr uint32_t off_wl = off_q + kQSlots * kTile * 4;       // [32] float
     static constexpr uint32_t off_red = off_wl + 32 * 4;                  // [128] double
-    static constexpr uint32_t off_bar = off_red + kTile * 8;              // mbarriers
+    static constexpr uint32_t off_bar = off_red + 3 * kTile * 8;          // mbarriers (red: up to 3 column slices)
     static constexpr int n_bars = 1 + 2 * kMaxStages + 4 + kQSlots;
     static constexpr uint32_t off_tmem = off_bar + n_bars * 8;
     static constexpr uint32_t total = off_tmem + 16;
@@ -650,15 +684,25 @@ struct TcsSmem {
           "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31]) \
         : "r"(addr))
 
-template <int NC>
-__global__ void __launch_bounds__(kTcThreads, 1)
+#define TNK_LD_16x256b_x4(v, addr)                                                                              \
+    asm volatile(                                                                                               \
+        "tcgen05.ld.sync.aligned.16x256b.x4.b32 "                                                               \
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"                        \
+        : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),       \
+          "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])  \
+        : "r"(addr))
+
+template <int NC, int FMT, int CS>
+__global__ void __launch_bounds__(64 + 128 * CS, 1)
 tcs_tiles_kernel(const __grid_constant__ TcsParams prm, const float* __restrict__ B_tab,
                  const float* __restrict__ ST, const float* __restrict__ Cst, const float* __restrict__ qT,
                  double* __restrict__ part, double* __restrict__ ucol) {
     extern __shared__ __align__(1024) unsigned char smem[];
-    using SM = TcsSmem<NC>;
+    using SM = TcsSmem<NC, FMT>;
     constexpr int NP = 4 * NC;
-    constexpr int K32 = tcs_k32(NC), S32 = tcs_steps32(NC), S16 = tcs_steps16(NC);
+    constexpr int MC = 16 / CS;          // 8-column atoms per thread and tile: a 4 x 2MC patch
+    static_assert(CS == 2 || CS == 4, "column slices per tile");
+    constexpr int K32 = tcs_k32(NC, FMT), S32 = tcs_steps32(NC, FMT), S16 = tcs_steps16(NC, FMT);
     constexpr int kStages = SM::stages;
     constexpr uint32_t b_bytes = SM::b_bytes;
     static_assert(2 * kTile + 8 * (S32 + S16) <= kTmemCols, "TMEM columns");
@@ -691,9 +735,9 @@ tcs_tiles_kernel(const __grid_constant__ TcsParams prm, const float* __restrict_
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     if (threadIdx.x < 32) sWl[threadIdx.x] = prm.wl[threadIdx.x];
     if (threadIdx.x == 0) {
-        mbar_init(bar_aready, 8);
+        mbar_init(bar_aready, 4 * CS);
         for (int s = 0; s < kStages; ++s) { mbar_init(bar_full + s, 1); mbar_init(bar_empty + s, 1); }
-        for (int s = 0; s < 2; ++s) { mbar_init(bar_tfull + s, 1); mbar_init(bar_tempty + s, 8); }
+        for (int s = 0; s < 2; ++s) { mbar_init(bar_tfull + s, 1); mbar_init(bar_tempty + s, 4 * CS); }
         for (int s = 0; s < kQSlots; ++s) mbar_init(bar_qfull + s, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
@@ -751,7 +795,7 @@ tcs_tiles_kernel(const __grid_constant__ TcsParams prm, const float* __restrict_
 #pragma unroll
                 for (int k = 0; k < S16; ++k) {
                     const uint64_t db = b_desc + (uint64_t)((uint32_t)(K32 + 2 * k) * cu + (cu << 16));
-                    umma_bf16_ts(d_addr, tmem_base + (uint32_t)(kTmemA + 8 * (S32 + k)), db, kIdescBf16, 1u);
+                    umma_bf16_ts(d_addr, tmem_base + (uint32_t)(kTmemA + 8 * (S32 + k)), db, kIdescBf16, (S32 + k) > 0 ? 1u : 0u);
                 }
                 umma_commit(bar_empty + s);
                 umma_commit(bar_tfull + ts);
@@ -760,10 +804,11 @@ tcs_tiles_kernel(const __grid_constant__ TcsParams prm, const float* __restrict_
             if (++s == kStages) { s = 0; ph ^= 1u; }
         }
     } else {
-        // ===== epilogue warps 2..9: lane quarter lqi = warp & 3, column half of every tile = (warp - 2) >> 2
+        // ===== epilogue warps 2..: lane quarter lqi = warp & 3, column slice (128/CS columns) of every tile = (warp - 2) >> 2
         const int lqi = warp & 3;
         const int lq = lqi * 32;
-        const int half = (warp - 2) >> 2;
+        const int cs = (warp - 2) >> 2;
+        const int colbase = cs * 8 * MC;
         const int n = prm.n;
         {
             // A operand: thread <-> TMEM lane <-> row L of the tile (32x32b stores), the two warps of a lane
@@ -791,11 +836,22 @@ tcs_tiles_kernel(const __grid_constant__ TcsParams prm, const float* __restrict_
             };
             auto a16 = [&](int e) -> float {
                 const int f = e / NP, p = e - f * NP;
-                return f == 0 ? sv[p] : f == 1 ? tf_lo(sv[p]) : f == 2 ? tf_lo(gr[p]) : bitf(p);
+                if (FMT == 0) return f == 0 ? sv[p] : f == 1 ? tf_lo(sv[p]) : f == 2 ? tf_lo(gr[p]) : bitf(p);
+                if (f < 7) {
+                    if (f >= 5) return bitf(p);
+                    const float full = f < 3 ? sv[p] : gr[p];
+                    const float x1 = bf_round(full);
+                    return (f == 2 || f == 4) ? bf_round(full - x1) : x1;
+                }
+                const int k = e - 7 * NP;
+                if (k >= 6) return 0.f;
+                if (k >= 3) return 1.f;
+                const float c1 = bf_round(Ci), c2 = bf_round(Ci - c1);
+                return k == 0 ? c1 : k == 1 ? c2 : bf_round(Ci - c1 - c2);
             };
 #pragma unroll
             for (int ks = 0; ks < S32 + S16; ++ks) {
-                if ((ks & 1) == half) {
+                if ((ks % CS) == cs) {
                     uint32_t av[8];
                     if (ks < S32) {
 #pragma unroll
@@ -827,12 +883,12 @@ tcs_tiles_kernel(const __grid_constant__ TcsParams prm, const float* __restrict_
         float2 T2[3][2];                                   // a^(in-tile Hamming distance), packed over e
         {
             const int i0 = (t >> 2) & 1;
-            const int c0 = __popc((unsigned)(((t >> 3) & 3) ^ (t & 3))) + (((lqi >> 1) ^ half) & 1);
+            const int c0 = __popc((unsigned)(((t >> 3) & 3) ^ (t & 3)));
 #pragma unroll
             for (int h = 0; h < 3; ++h)
 #pragma unroll
                 for (int mh = 0; mh < 2; ++mh) {
-                    const int e0 = c0 + h + ((lqi & 1) ^ mh);
+                    const int e0 = c0 + h + __popc((unsigned)((((colbase >> 5) + mh) ^ lqi) & 3));   // column bits 5-6
                     T2[h][mh] = make_float2(sWl[e0 + i0], sWl[e0 + (i0 ^ 1)]);
                 }
         }
@@ -851,28 +907,33 @@ tcs_tiles_kernel(const __grid_constant__ TcsParams prm, const float* __restrict_
             mbar_wait(bar_qfull + qs, qph);
             mbar_wait(bar_tfull + ts, tph);
             tc_fence_after();
-            const uint32_t taddr = tmem_base + ((uint32_t)lq << 16) + (uint32_t)(ts * kTile + half * 64);
-            uint32_t v0[32], v1[32];
-            TNK_LD_16x256b_x8(v0, taddr);
-            TNK_LD_16x256b_x8(v1, taddr + (16u << 16));
-            float2 qj[8];
+            const uint32_t taddr = tmem_base + ((uint32_t)lq << 16) + (uint32_t)(ts * kTile + colbase);
+            uint32_t v0[4 * MC], v1[4 * MC];
+            if constexpr (MC == 8) {
+                TNK_LD_16x256b_x8(v0, taddr);
+                TNK_LD_16x256b_x8(v1, taddr + (16u << 16));
+            } else {
+                TNK_LD_16x256b_x4(v0, taddr);
+                TNK_LD_16x256b_x4(v1, taddr + (16u << 16));
+            }
+            float2 qj[MC];
             {
-                const float2* q2 = reinterpret_cast<const float2*>(sQ + qs * kTile + half * 64 + 2 * (t & 3));
+                const float2* q2 = reinterpret_cast<const float2*>(sQ + qs * kTile + colbase + 2 * (t & 3));
 #pragma unroll
-                for (int m = 0; m < 8; ++m) qj[m] = q2[4 * m];
+                for (int m = 0; m < MC; ++m) qj[m] = q2[4 * m];
             }
             asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(bar_tempty + ts);
-            float2 racc[4], cacc[8];
+            float2 racc[4], cacc[MC];
 #pragma unroll
             for (int k = 0; k < 4; ++k) racc[k] = make_float2(0.f, 0.f);
 #pragma unroll
-            for (int m = 0; m < 8; ++m) cacc[m] = make_float2(0.f, 0.f);
-            auto fold = [&](const uint32_t (&v)[32], const int hr) {
+            for (int m = 0; m < MC; ++m) cacc[m] = make_float2(0.f, 0.f);
+            auto fold = [&](const uint32_t (&v)[4 * MC], const int hr) {
 #pragma unroll
-                for (int m = 0; m < 8; ++m)
+                for (int m = 0; m < MC; ++m)
 #pragma unroll
                     for (int r = 0; r < 2; ++r) {
                         const int k = 2 * hr + r;
@@ -894,34 +955,40 @@ tcs_tiles_kernel(const __grid_constant__ TcsParams prm, const float* __restrict_
                 uhi[k] = sum;
             }
             if (J != I) {
-                // mirrored part: sum over the warp's 32 rows, exchanging halves of the column set per level
-                float2 c1[4], c2[2], c3;
+                // mirrored part: sum over the warp's 32 rows (8 row groups = lane bits 2-4), exchanging halves of the
+                // column set per level; with 4 atoms per thread the last level is a plain exchange-add
+                auto xadd = [&](const float2 keep, const float2 send, const int mask) {
+                    return make_float2(keep.x + __shfl_xor_sync(0xffffffffu, send.x, mask),
+                                       keep.y + __shfl_xor_sync(0xffffffffu, send.y, mask));
+                };
+                float2 c3;
+                int col;
+                if constexpr (MC == 8) {
+                    float2 c1[4], c2[2];
 #pragma unroll
-                for (int k = 0; k < 4; ++k) {
-                    const float2 send = b4 ? cacc[k] : cacc[k + 4], keep = b4 ? cacc[k + 4] : cacc[k];
-                    c1[k].x = keep.x + __shfl_xor_sync(0xffffffffu, send.x, 16);
-                    c1[k].y = keep.y + __shfl_xor_sync(0xffffffffu, send.y, 16);
-                }
+                    for (int k = 0; k < 4; ++k) c1[k] = xadd(b4 ? cacc[k + 4] : cacc[k], b4 ? cacc[k] : cacc[k + 4], 16);
 #pragma unroll
-                for (int k = 0; k < 2; ++k) {
-                    const float2 send = b3 ? c1[k] : c1[k + 2], keep = b3 ? c1[k + 2] : c1[k];
-                    c2[k].x = keep.x + __shfl_xor_sync(0xffffffffu, send.x, 8);
-                    c2[k].y = keep.y + __shfl_xor_sync(0xffffffffu, send.y, 8);
+                    for (int k = 0; k < 2; ++k) c2[k] = xadd(b3 ? c1[k + 2] : c1[k], b3 ? c1[k] : c1[k + 2], 8);
+                    c3 = xadd(b2 ? c2[1] : c2[0], b2 ? c2[0] : c2[1], 4);
+                    col = 2 * t;                                  // atom t>>2: columns 8(t>>2) + 2(t&3) + e
+                } else {
+                    float2 c1[2];
+#pragma unroll
+                    for (int k = 0; k < 2; ++k) c1[k] = xadd(b4 ? cacc[k + 2] : cacc[k], b4 ? cacc[k] : cacc[k + 2], 16);
+                    const float2 c2 = xadd(b3 ? c1[1] : c1[0], b3 ? c1[0] : c1[1], 8);
+                    c3 = xadd(c2, c2, 4);                         // both lanes of a pair hold the sum; b2 == 0 adds it
+                    col = 8 * (t >> 3) + 2 * (t & 3);             // atom t>>3
                 }
-                {
-                    const float2 send = b2 ? c2[0] : c2[1], keep = b2 ? c2[1] : c2[0];
-                    c3.x = keep.x + __shfl_xor_sync(0xffffffffu, send.x, 4);
-                    c3.y = keep.y + __shfl_xor_sync(0xffffffffu, send.y, 4);
+                // one fp64 RED per column, warp and tile (fire and forget; the four lane quarters meet in L2 - measured
+                // faster than combining them in shared memory behind a named barrier)
+                if (MC == 8 || !b2) {
+                    double* dst = ucol + J * kTile + colbase + col;
+                    atomicAdd(dst, (double)(wg * c3.x));
+                    atomicAdd(dst + 1, (double)(wg * c3.y));
                 }
-                // thread t now holds columns 2t, 2t+1 of the half summed over the warp's 32 rows: one fp64 RED each
-                // (fire and forget; the four lane quarters meet in L2 - measured faster than combining them in
-                // shared memory behind a named barrier)
-                double* dst = ucol + J * kTile + half * 64 + 2 * t;
-                atomicAdd(dst, (double)(wg * c3.x));
-                atomicAdd(dst + 1, (double)(wg * c3.y));
             }
         }
-        // row sums: over the 4 threads sharing a row, then over the two column halves
+        // row sums: over the 4 threads sharing a row, then over the CS column slices
         double ud[4];
 #pragma unroll
         for (int k = 0; k < 4; ++k) {
@@ -930,15 +997,19 @@ tcs_tiles_kernel(const __grid_constant__ TcsParams prm, const float* __restrict_
             x += __shfl_xor_sync(0xffffffffu, x, 2);
             ud[k] = x;
         }
-        if (half == 1 && (t & 3) == 0) {
+        if (cs > 0 && (t & 3) == 0) {
 #pragma unroll
-            for (int k = 0; k < 4; ++k) sRed[rq + 8 * k] = ud[k];
+            for (int k = 0; k < 4; ++k) sRed[(cs - 1) * kTile + rq + 8 * k] = ud[k];
         }
-        asm volatile("bar.sync 1, 256;" ::: "memory");
-        if (half == 0 && (t & 3) == 0) {
+        asm volatile("bar.sync 1, %0;" ::"n"(128 * CS) : "memory");   // the epilogue warps only
+        if (cs == 0 && (t & 3) == 0) {
 #pragma unroll
-            for (int k = 0; k < 4; ++k)
-                part[(size_t)blockIdx.y * prm.part_stride + (size_t)blockIdx.x * kTile + rq + 8 * k] = ud[k] + sRed[rq + 8 * k];
+            for (int k = 0; k < 4; ++k) {
+                double x = ud[k];
+#pragma unroll
+                for (int c = 0; c < CS - 1; ++c) x += sRed[c * kTile + rq + 8 * k];
+                part[(size_t)blockIdx.y * prm.part_stride + (size_t)blockIdx.x * kTile + rq + 8 * k] = x;
+            }
         }
     }
 
@@ -1036,27 +1107,34 @@ int tnk_tc_launch(int n, double a, double gamma, const double* wl, const float* 
 }
 
 // ---- symmetric variant: host side
-size_t tnk_tcs_table_bytes(int n, int64_t states) {
+size_t tnk_tcs_table_bytes(int n, int fmt, int64_t states) {
     const int nc = ((n + 3) / 4);
-    return (size_t)states * (size_t)tcs_kb(nc) * 16;
+    return (size_t)states * (size_t)tcs_kb(nc, fmt) * 16;
 }
 
 namespace {
-template <int NC>
-int launch_sym(const TcsParams& prm, dim3 grid, const float* B_tab, const float* ST, const float* Cst,
-               const float* qT, double* part, double* ucol, cudaStream_t st) {
-    const size_t smem = TcsSmem<NC>::total;
-    auto kern = tcs_tiles_kernel<NC>;
+template <int NC, int FMT, int CS>
+int launch_sym_cs(const TcsParams& prm, dim3 grid, const float* B_tab, const float* ST, const float* Cst,
+                  const float* qT, double* part, double* ucol, cudaStream_t st) {
+    const size_t smem = TcsSmem<NC, FMT>::total;
+    auto kern = tcs_tiles_kernel<NC, FMT, CS>;
     TNK_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    kern<<<grid, kTcThreads, smem, st>>>(prm, B_tab, ST, Cst, qT, part, ucol);
+    kern<<<grid, 64 + 128 * CS, smem, st>>>(prm, B_tab, ST, Cst, qT, part, ucol);
     TNK_CUDA_OK(cudaGetLastError());
     return 0;
+}
+template <int NC, int FMT>
+int launch_sym(const TcsParams& prm, dim3 grid, const float* B_tab, const float* ST, const float* Cst,
+               const float* qT, double* part, double* ucol, cudaStream_t st) {
+    // CS = 2: 8 epilogue warps with 4 x 16 patches.  CS = 4 (16 warps, 4 x 8 patches, 88 registers) gives the same
+    // results but measured slower (n = 20: 183.1 vs 178.6 ms): the kernel is bound by power, not by exposed latency.
+    return launch_sym_cs<NC, FMT, 2>(prm, grid, B_tab, ST, Cst, qT, part, ucol, st);
 }
 }  // namespace
 
 // Builds the (q-independent) column table unless the caller vouches for the one in B_tab, zeroes ucol and
 // launches the symmetric tile kernel for row tiles tile_offset + k*tile_stride, k < row_tiles.
-int tnk_tcs_launch(int n, double gamma, const double* wl, const float* ST, const float* Cst, const float* qT,
+int tnk_tcs_launch(int n, int fmt, double gamma, const double* wl, const float* ST, const float* Cst, const float* qT,
                    int tile_offset, int tile_stride, int row_tiles, int splits, float* B_tab, int reuse_table,
                    double* part, double* ucol, cudaEvent_t ev_start, cudaEvent_t ev_stop, int* launches,
                    cudaStream_t st) {
@@ -1066,8 +1144,8 @@ int tnk_tcs_launch(int n, double gamma, const double* wl, const float* ST, const
     const int64_t N = (int64_t)1 << n;
     const int64_t col_tiles = N / kTile;
     if (!reuse_table) {
-        const int64_t items = col_tiles * tcs_kb(nc) * kTile;
-        tcs_pack_kernel<<<(unsigned)((items + 255) / 256), 256, 0, st>>>(n, np, col_tiles, (float)gamma, ST, Cst,
+        const int64_t items = col_tiles * tcs_kb(nc, fmt) * kTile;
+        tcs_pack_kernel<<<(unsigned)((items + 255) / 256), 256, 0, st>>>(n, np, fmt, col_tiles, (float)gamma, ST, Cst,
                                                                         reinterpret_cast<uint4*>(B_tab));
         TNK_CUDA_OK(cudaGetLastError());
         if (launches) *launches += 1;
@@ -1081,12 +1159,17 @@ int tnk_tcs_launch(int n, double gamma, const double* wl, const float* ST, const
     if (ev_start) TNK_CUDA_OK(cudaEventRecord(ev_start, st));
     dim3 grid((unsigned)row_tiles, (unsigned)splits, 1);
     int rc = 2;
-    switch (nc) {
-        case 2: rc = launch_sym<2>(prm, grid, B_tab, ST, Cst, qT, part, ucol, st); break;
-        case 3: rc = launch_sym<3>(prm, grid, B_tab, ST, Cst, qT, part, ucol, st); break;
-        case 4: rc = launch_sym<4>(prm, grid, B_tab, ST, Cst, qT, part, ucol, st); break;
-        case 5: rc = launch_sym<5>(prm, grid, B_tab, ST, Cst, qT, part, ucol, st); break;
-        case 6: rc = launch_sym<6>(prm, grid, B_tab, ST, Cst, qT, part, ucol, st); break;
+    switch (nc * 2 + (fmt ? 1 : 0)) {
+        case 4: rc = launch_sym<2, 0>(prm, grid, B_tab, ST, Cst, qT, part, ucol, st); break;
+        case 5: rc = launch_sym<2, 1>(prm, grid, B_tab, ST, Cst, qT, part, ucol, st); break;
+        case 6: rc = launch_sym<3, 0>(prm, grid, B_tab, ST, Cst, qT, part, ucol, st); break;
+        case 7: rc = launch_sym<3, 1>(prm, grid, B_tab, ST, Cst, qT, part, ucol, st); break;
+        case 8: rc = launch_sym<4, 0>(prm, grid, B_tab, ST, Cst, qT, part, ucol, st); break;
+        case 9: rc = launch_sym<4, 1>(prm, grid, B_tab, ST, Cst, qT, part, ucol, st); break;
+        case 10: rc = launch_sym<5, 0>(prm, grid, B_tab, ST, Cst, qT, part, ucol, st); break;
+        case 11: rc = launch_sym<5, 1>(prm, grid, B_tab, ST, Cst, qT, part, ucol, st); break;
+        case 12: rc = launch_sym<6, 0>(prm, grid, B_tab, ST, Cst, qT, part, ucol, st); break;
+        case 13: rc = launch_sym<6, 1>(prm, grid, B_tab, ST, Cst, qT, part, ucol, st); break;
         default: tnk_set_error("tnk_ksd_sym: no kernel instance for %d chunks", nc); break;
     }
     if (rc) return rc;

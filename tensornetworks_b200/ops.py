@@ -143,11 +143,16 @@ class SteinTables:
         return u, part
 
 
-    def ksd_sym(self, q, tile_offset=0, tile_stride=1):
+    def ksd_sym(self, q, tile_offset=0, tile_stride=1, split="tf32"):
         """Symmetric tensor-core evaluation (tnk_ksd_sym): every unordered pair of 128-state tiles is evaluated
         once and feeds both its row tile and, mirrored, its column tile.  This call owns the row tiles
         tile_offset + k*tile_stride; returns (u_partial [N] fp64, part [1] fp64) whose sums over all offsets of
-        one stride are u = K_p q and KSD^2.  Needs the fp32 tables (precision "tc32" or "fp32"), 7 <= n <= 24."""
+        one stride are u = K_p q and KSD^2.  Needs the fp32 tables (precision "tc32" or "fp32"), 7 <= n <= 24.
+        split: "tf32" = tf32 high parts + bf16 cross terms (errors of the tc32 kernel, ~1e-6), "bf16x2" = two bf16
+        pieces per factor (fewer MMA K-steps, errors ~1e-5)."""
+        if split not in _lib.SYM_SPLIT:
+            raise ValueError(f"split must be one of {tuple(_lib.SYM_SPLIT)}")
+        code = _lib.SYM_SPLIT[split]
         if self.dtype != torch.float32:
             raise ValueError('the symmetric tile kernel reads the fp32 tables: build SteinTables with precision "tc32"')
         if q.device != self.device or q.dim() != 1 or q.numel() != self.N:
@@ -157,10 +162,10 @@ class SteinTables:
         q = q.contiguous()
         lib = _lib.load()
         with torch.cuda.device(self.device):
-            key = ("sym", tile_offset, tile_stride)
+            key = ("sym", tile_offset, tile_stride, split)
             reuse = key in self._ws
             if not reuse:
-                nbytes = lib.tnk_ksd_sym_workspace_bytes(self.n, tile_offset, tile_stride)
+                nbytes = lib.tnk_ksd_sym_workspace_bytes(self.n, code, tile_offset, tile_stride)
                 if nbytes == 0:
                     raise RuntimeError(f"tnk_ksd_sym_workspace_bytes rejected n={self.n}, tiles ({tile_offset}, {tile_stride})")
                 self._ws[key] = torch.empty(nbytes, dtype=torch.uint8, device=self.device)
@@ -168,7 +173,7 @@ class SteinTables:
             u = torch.empty(self.N, dtype=torch.float64, device=self.device)
             part = torch.empty(1, dtype=torch.float64, device=self.device)
             launched = ctypes.c_int(0)
-            _lib.check(lib.tnk_ksd_sym(self.n, self.length_scale, _ptr(q), 0 if q.dtype == torch.float64 else 1,
+            _lib.check(lib.tnk_ksd_sym(self.n, self.length_scale, code, _ptr(q), 0 if q.dtype == torch.float64 else 1,
                                        _ptr(self.ST), _ptr(self.Cst), tile_offset, tile_stride, 1 if reuse else 0,
                                        _ptr(u), _ptr(part), _ptr(ws), ws.numel(), ctypes.byref(launched),
                                        _stream_ptr(self.device)), "tnk_ksd_sym")

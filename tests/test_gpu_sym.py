@@ -178,3 +178,23 @@ def test_trainer_epochs_pairs_sym_match_fp64(ops):
             a, b = np.array(hist["fp64"][key], dtype=float), np.array(hist[name][key], dtype=float)
             assert a.shape == b.shape == (10,), key
             assert np.max(np.abs(a - b) / np.maximum(np.abs(a), 1e-12)) < 2e-3, (name, key, a, b)
+
+
+@pytest.mark.parametrize("n,seed", [(7, 0), (10, 2), (12, 0), (13, 1), (16, 0), (17, 3)])
+def test_sym_bf16x2_operands(ops, n, seed):
+    """split="bf16x2": every real factor as two bf16 pieces (fewer MMA K-steps); errors ~1e-5, inside the 1e-4 mode."""
+    bn, lat, obs, x = random_binary_bn(n, seed=seed)
+    tabs = ops.SteinTables.from_network(bn, x, lat, precision="tc32")
+    ref = ops.SteinTables.from_network(bn, x, lat, precision="fp64")
+    q = random_q(1 << n, seed=seed).cuda()
+    u0, k0 = ref.ksd_rows(q) if n <= 14 else ref.ksd_modeproduct(q)
+    u1, k1 = tabs.ksd_sym(q, split="bf16x2")
+    ua, ka = tabs.ksd_sym(q, 0, 2, split="bf16x2")
+    ub, kb = tabs.ksd_sym(q, 1, 2, split="bf16x2")
+    torch.cuda.synchronize()
+    scale = u0.abs().max().item()
+    assert abs(k1.item() - k0.item()) <= TOL * abs(k0.item())
+    assert (u1 - u0).abs().max().item() <= TOL * scale
+    assert (ua + ub - u1).abs().max().item() <= 1e-9 * scale
+    with pytest.raises(ValueError):
+        tabs.ksd_sym(q, split="fp8")

@@ -47,6 +47,44 @@ def _features(S, n, length_scale=1.0):
     return A32, B32, A16, B16, a
 
 
+def _features_bf16x2(S, n, length_scale=1.0):
+    """Operand format 1: every real factor as two bf16 pieces; all products in bf16."""
+    N = 1 << n
+    np_ = (n + 3) // 4 * 4
+    a = np.exp(-1.0 / (n * length_scale))
+    alpha, gamma = 1.0 - a, a - 1.0 / a
+    z = np.arange(N)
+    s = np.zeros((N, np_), dtype=np.float32)
+    s[:, :n] = S[:, ::-1].astype(np.float32)
+    bit = np.zeros((N, np_), dtype=np.float32)
+    bit[:, :n] = (z[:, None] >> np.arange(n)[None, :]) & 1
+    valid = np.zeros(np_, dtype=np.float32)
+    valid[:n] = 1
+    g = (np.float32(gamma) * (1 - s)) * (1 - 2 * bit) * valid
+    C = (alpha * ((1 - s) * valid).sum(1) + gamma * ((1 - s) * bit).sum(1)).astype(np.float32)
+    s1 = _bf(s); s2 = _bf(s - s1)
+    g1 = _bf(g); g2 = _bf(g - g1)
+    c1 = _bf(C); c2 = _bf(C - c1); c3 = _bf(C - c1 - c2)
+    one = np.ones(N, dtype=np.float32)
+    A = np.concatenate([s1, s1, s2, g1, g2, bit, bit, np.stack([c1, c2, c3, one, one, one], 1)], 1)
+    B = np.concatenate([s1, s2, s1, bit, bit, g1, g2, np.stack([one, one, one, c1, c2, c3], 1)], 1)
+    assert A.shape[1] == 7 * np_ + 6
+    return A, B, a
+
+
+@pytest.mark.parametrize("n", [8, 9])
+def test_emulated_bf16x2_operands_match_oracle(n):
+    bn, lat, obs, x = random_binary_bn(n, seed=n)
+    S = orc.score_table(orc.joint_table(bn, x, lat), n)
+    q64 = random_q(1 << n, seed=n).numpy()
+    Kref, gref = orc.ksd_dense(q64, S, n)
+    N = 1 << n
+    A, B, a = _features_bf16x2(S, n)
+    h = np.array([[bin(i ^ j).count("1") for j in range(N)] for i in range(N)])
+    u = (a ** h * (A.astype(np.float64) @ B.astype(np.float64).T)) @ q64.astype(np.float32).astype(np.float64)
+    assert np.max(np.abs(u - gref / 2)) <= 3e-5 * np.max(np.abs(gref / 2))
+
+
 @pytest.mark.parametrize("n,stride", [(8, 1), (9, 1), (9, 3)])
 def test_emulated_symmetric_tiles_match_oracle(n, stride):
     bn, lat, obs, x = random_binary_bn(n, seed=n)
@@ -114,11 +152,14 @@ def test_transposing_exchange_lands_on_columns_2t():
 
 def test_workspace_query():
     lib = _lib.load()
-    for n in range(7, 25):
-        assert lib.tnk_ksd_sym_workspace_bytes(n, 0, 1) > 0
-        assert lib.tnk_ksd_sym_workspace_bytes(n, 3, 8) > 0
-    for n in (0, 6, 25, 30):
-        assert lib.tnk_ksd_sym_workspace_bytes(n, 0, 1) == 0
-    assert lib.tnk_ksd_sym_workspace_bytes(12, 0, 0) == 0 and lib.tnk_ksd_sym_workspace_bytes(12, -1, 2) == 0
-    # n = 20: q (4 MB) + row partials + column sums (8 MB) + column table 2^20 * 26 chunks * 16 B
-    assert lib.tnk_ksd_sym_workspace_bytes(20, 0, 1) >= (1 << 20) * 26 * 16
+    for split in (0, 1):
+        for n in range(7, 25):
+            assert lib.tnk_ksd_sym_workspace_bytes(n, split, 0, 1) > 0
+            assert lib.tnk_ksd_sym_workspace_bytes(n, split, 3, 8) > 0
+        for n in (0, 6, 25, 30):
+            assert lib.tnk_ksd_sym_workspace_bytes(n, split, 0, 1) == 0
+    assert lib.tnk_ksd_sym_workspace_bytes(12, 0, 0, 0) == 0 and lib.tnk_ksd_sym_workspace_bytes(12, 0, -1, 2) == 0
+    assert lib.tnk_ksd_sym_workspace_bytes(12, 2, 0, 1) == 0                    # unknown operand split
+    # n = 20: q (4 MB) + row partials + column sums (8 MB) + column table 2^20 * (26 | 20) chunks * 16 B
+    assert lib.tnk_ksd_sym_workspace_bytes(20, 0, 0, 1) >= (1 << 20) * 26 * 16
+    assert (1 << 20) * 20 * 16 <= lib.tnk_ksd_sym_workspace_bytes(20, 1, 0, 1) <= lib.tnk_ksd_sym_workspace_bytes(20, 0, 0, 1) - (1 << 20) * 6 * 16
