@@ -1,7 +1,7 @@
 """BASELINE.json config #5: full KSDVariationalInference.train epochs on a synthetic random binary BN
 (default n = 24) on 1..8 B200s.  One rank per GPU under torchrun; prints one JSON line with s/epoch.
 
-    python scripts/train_epochs.py [--n 24] [--epochs 2] [--precision tc32] [--algorithm pairs|modeproduct]
+    python scripts/train_epochs.py [--n 24] [--epochs 2] [--precision tc32] [--algorithm pairs|pairs_sym|modeproduct]
 """
 import argparse
 import json
@@ -60,7 +60,7 @@ def main():
     if rank == 0:
         print(json.dumps({"workload": f"KSDVariationalInference.train, synthetic random binary BN, {args.n} latent vars",
                           "n_gpus": world, "precision": args.precision, "algorithm": args.algorithm, "cuda_graph": args.cuda_graph,
-                          "s_per_epoch": per_epoch, "pairs_per_s": 4.0 ** args.n / per_epoch if args.algorithm == "pairs" else None,
+                          "s_per_epoch": per_epoch, "pairs_per_s": 4.0 ** args.n / per_epoch if args.algorithm.startswith("pairs") else None,
                           "epochs_timed": args.epochs, "first_train_call_s": first_s, "constructor_s": build_s,
                           "loss_ksd": hist["loss_ksd"][-1]}), flush=True)
     if world > 1:

@@ -665,7 +665,7 @@ namespace {
 struct SymPlan {
     int64_t N, T, finish_blocks;
     int row_tiles, splits;
-    size_t off_q, off_part, off_col, off_block, off_b, total;
+    size_t off_q, off_col, off_block, off_b, total;
 };
 
 int make_sym_plan(int n, int split, int tile_offset, int tile_stride, SymPlan* p) {
@@ -683,7 +683,6 @@ int make_sym_plan(int n, int split, int tile_offset, int tile_stride, SymPlan* p
     size_t off = 0;
     auto take = [&](size_t bytes) { const size_t at = off; off += (bytes + 255) / 256 * 256; return at; };
     p->off_q = take((size_t)p->N * sizeof(float));
-    p->off_part = take((size_t)splits * (size_t)(p->row_tiles > 0 ? p->row_tiles : 1) * TNK_TC_TILE * sizeof(double));
     p->off_col = take((size_t)p->N * sizeof(double));
     p->off_block = take((size_t)(p->finish_blocks + 1) * sizeof(double));
     p->off_b = take(b_bytes);
@@ -691,24 +690,16 @@ int make_sym_plan(int n, int split, int tile_offset, int tile_stride, SymPlan* p
     return 0;
 }
 
-// u_partial[z] = mirrored column sums + (row sums over the column splits if this call owns z's row tile)
+// u_partial = the accumulator the tile kernel added its row sums and mirrored column sums to; block partials of q.u
 template <typename Q>
 __global__ void __launch_bounds__(256)
-finish_sym_kernel(const double* __restrict__ part, int splits, int64_t part_stride, int tile_offset, int tile_stride,
-                  int row_tiles, const double* __restrict__ ucol, const Q* __restrict__ q, int64_t N,
+finish_sym_kernel(const double* __restrict__ uacc, const Q* __restrict__ q, int64_t N,
                   double* __restrict__ u, double* __restrict__ blockpart) {
     __shared__ double red[256];
     const int64_t z = (int64_t)blockIdx.x * 256 + threadIdx.x;
     double contrib = 0.0;
     if (z < N) {
-        double acc = ucol[z];
-        const int64_t d = (z / TNK_TC_TILE) - tile_offset;
-        if (d >= 0 && d % tile_stride == 0 && d / tile_stride < row_tiles) {
-            const int64_t r = (d / tile_stride) * TNK_TC_TILE + (z % TNK_TC_TILE);
-            double rows = 0.0;
-            for (int s = 0; s < splits; ++s) rows += part[(size_t)s * part_stride + r];
-            acc += rows;
-        }
+        const double acc = uacc[z];
         u[z] = acc;
         contrib = (double)q[z] * acc;
     }
@@ -746,7 +737,6 @@ extern "C" int tnk_ksd_sym(int n_latent, double length_scale, int split, const v
     const int n = n_latent;
     unsigned char* ws = (unsigned char*)workspace;
     float* qT = (float*)(ws + p.off_q);
-    double* part = (double*)(ws + p.off_part);
     double* ucol = (double*)(ws + p.off_col);
     double* blockpart = (double*)(ws + p.off_block);
     int launches = 0;
@@ -761,16 +751,13 @@ extern "C" int tnk_ksd_sym(int n_latent, double length_scale, int split, const v
     TNK_CUDA_OK(cudaGetLastError());
     ++launches;
     const int rc = tnk_tcs_launch(n, split, gamma, wl, (const float*)ST, (const float*)Cst, qT, tile_offset, tile_stride,
-                                  p.row_tiles, p.splits, (float*)(ws + p.off_b), reuse_table, part, ucol,
+                                  p.row_tiles, p.splits, (float*)(ws + p.off_b), reuse_table, ucol,
                                   g_ev_start, g_ev_stop, &launches, st);
     if (rc) return rc;
-    const int64_t part_stride = (int64_t)p.row_tiles * TNK_TC_TILE;
     if (q_dtype == 0)
-        finish_sym_kernel<double><<<(unsigned)p.finish_blocks, 256, 0, st>>>(part, p.splits, part_stride, tile_offset, tile_stride,
-                                                                            p.row_tiles, ucol, (const double*)q, p.N, u_partial, blockpart);
+        finish_sym_kernel<double><<<(unsigned)p.finish_blocks, 256, 0, st>>>(ucol, (const double*)q, p.N, u_partial, blockpart);
     else
-        finish_sym_kernel<float><<<(unsigned)p.finish_blocks, 256, 0, st>>>(part, p.splits, part_stride, tile_offset, tile_stride,
-                                                                           p.row_tiles, ucol, (const float*)q, p.N, u_partial, blockpart);
+        finish_sym_kernel<float><<<(unsigned)p.finish_blocks, 256, 0, st>>>(ucol, (const float*)q, p.N, u_partial, blockpart);
     TNK_CUDA_OK(cudaGetLastError());
     PeerSinks none;
     none.n = 0;

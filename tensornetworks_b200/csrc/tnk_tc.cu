@@ -557,8 +557,9 @@ tc_rows_kernel(const __grid_constant__ TcParams prm, const float* __restrict__ B
 // its 4 rows in registers and over the 8 row groups of the warp with a transposing exchange (14 SHFL),
 // then added to ucol[] with one fp64 RED per column, warp and tile (the 4 lane quarters meet in L2).  The Hamming weight of the 7 in-tile bits factorises over the patch: per-thread constant x
 // (compile-time power of a from the unrolled row/column slots) -> 6 packed weights in registers.
-// Row sums: fp32 per tile, compensated fp32 across tiles, fp64 at the end (as in tc_rows_kernel).
-// Column sums arrive in ucol[] by atomics, so the last bits of u depend on the arrival order.
+// Row sums: fp32 per tile, compensated fp32 across tiles, fp64 at the end (as in tc_rows_kernel), added to the
+// same accumulator u[] with one fp64 RED per row and CTA (no per-split partial buffer: at n = 24 it would be 68 GB).
+// Both kinds of sums arrive by atomics, so the last bits of u depend on the arrival order (observed: <= 2e-16).
 // ======================================================================================================
 // Operand format 0 (above): tf32 high parts + bf16 cross terms, ~2^-19 per product.  Format 1: every real factor
 // as TWO bf16 pieces x = x1 + x2 (x1 = bf(x), x2 = bf(x - x1), residual <= 2^-18 |x|), all K-steps kind::f16:
@@ -577,7 +578,6 @@ struct TcsParams {
     int tile_offset, tile_stride;  // row tile of blockIdx.x = tile_offset + tile_stride * blockIdx.x
     int64_t n_tiles;               // 2^n / 128
     int col_splits;                // gridDim.y
-    int64_t part_stride;           // rows covered by the launch (gridDim.x * 128)
     float gamma;
     float wl[32];
 };
@@ -696,7 +696,7 @@ template <int NC, int FMT, int CS>
 __global__ void __launch_bounds__(64 + 128 * CS, 1)
 tcs_tiles_kernel(const __grid_constant__ TcsParams prm, const float* __restrict__ B_tab,
                  const float* __restrict__ ST, const float* __restrict__ Cst, const float* __restrict__ qT,
-                 double* __restrict__ part, double* __restrict__ ucol) {
+                 double* __restrict__ ucol) {
     extern __shared__ __align__(1024) unsigned char smem[];
     using SM = TcsSmem<NC, FMT>;
     constexpr int NP = 4 * NC;
@@ -713,11 +713,7 @@ tcs_tiles_kernel(const __grid_constant__ TcsParams prm, const float* __restrict_
     const int64_t j_split = (int64_t)blockIdx.y * n_per;
     const int64_t j_begin = j_split > I ? j_split : I;
     const int64_t n_local = j_split + n_per - j_begin;
-    if (n_local <= 0) {
-        if (threadIdx.x < kTile)
-            part[(size_t)blockIdx.y * prm.part_stride + (size_t)blockIdx.x * kTile + threadIdx.x] = 0.0;
-        return;
-    }
+    if (n_local <= 0) return;
 
     unsigned char* sB = smem + SM::off_b;
     float* sQ = reinterpret_cast<float*>(smem + SM::off_q);
@@ -1008,7 +1004,7 @@ tcs_tiles_kernel(const __grid_constant__ TcsParams prm, const float* __restrict_
                 double x = ud[k];
 #pragma unroll
                 for (int c = 0; c < CS - 1; ++c) x += sRed[c * kTile + rq + 8 * k];
-                part[(size_t)blockIdx.y * prm.part_stride + (size_t)blockIdx.x * kTile + rq + 8 * k] = x;
+                atomicAdd(ucol + I * kTile + rq + 8 * k, x);    // row sums of this column split
             }
         }
     }
@@ -1115,20 +1111,20 @@ size_t tnk_tcs_table_bytes(int n, int fmt, int64_t states) {
 namespace {
 template <int NC, int FMT, int CS>
 int launch_sym_cs(const TcsParams& prm, dim3 grid, const float* B_tab, const float* ST, const float* Cst,
-                  const float* qT, double* part, double* ucol, cudaStream_t st) {
+                  const float* qT, double* ucol, cudaStream_t st) {
     const size_t smem = TcsSmem<NC, FMT>::total;
     auto kern = tcs_tiles_kernel<NC, FMT, CS>;
     TNK_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    kern<<<grid, 64 + 128 * CS, smem, st>>>(prm, B_tab, ST, Cst, qT, part, ucol);
+    kern<<<grid, 64 + 128 * CS, smem, st>>>(prm, B_tab, ST, Cst, qT, ucol);
     TNK_CUDA_OK(cudaGetLastError());
     return 0;
 }
 template <int NC, int FMT>
 int launch_sym(const TcsParams& prm, dim3 grid, const float* B_tab, const float* ST, const float* Cst,
-               const float* qT, double* part, double* ucol, cudaStream_t st) {
+               const float* qT, double* ucol, cudaStream_t st) {
     // CS = 2: 8 epilogue warps with 4 x 16 patches.  CS = 4 (16 warps, 4 x 8 patches, 88 registers) gives the same
     // results but measured slower (n = 20: 183.1 vs 178.6 ms): the kernel is bound by power, not by exposed latency.
-    return launch_sym_cs<NC, FMT, 2>(prm, grid, B_tab, ST, Cst, qT, part, ucol, st);
+    return launch_sym_cs<NC, FMT, 2>(prm, grid, B_tab, ST, Cst, qT, ucol, st);
 }
 }  // namespace
 
@@ -1136,7 +1132,7 @@ int launch_sym(const TcsParams& prm, dim3 grid, const float* B_tab, const float*
 // launches the symmetric tile kernel for row tiles tile_offset + k*tile_stride, k < row_tiles.
 int tnk_tcs_launch(int n, int fmt, double gamma, const double* wl, const float* ST, const float* Cst, const float* qT,
                    int tile_offset, int tile_stride, int row_tiles, int splits, float* B_tab, int reuse_table,
-                   double* part, double* ucol, cudaEvent_t ev_start, cudaEvent_t ev_stop, int* launches,
+                   double* ucol, cudaEvent_t ev_start, cudaEvent_t ev_stop, int* launches,
                    cudaStream_t st) {
     TNK_REQUIRE(n >= TNK_TC_MIN_LATENT && n <= TNK_TC_MAX_LATENT, "tnk_ksd_sym: n=%d outside %d..%d", n,
                 TNK_TC_MIN_LATENT, TNK_TC_MAX_LATENT);
@@ -1154,22 +1150,22 @@ int tnk_tcs_launch(int n, int fmt, double gamma, const double* wl, const float* 
     if (row_tiles <= 0) return 0;
     TcsParams prm;
     prm.n = n; prm.tile_offset = tile_offset; prm.tile_stride = tile_stride; prm.n_tiles = col_tiles;
-    prm.col_splits = splits; prm.part_stride = (int64_t)row_tiles * kTile; prm.gamma = (float)gamma;
+    prm.col_splits = splits; prm.gamma = (float)gamma;
     for (int h = 0; h < 32; ++h) prm.wl[h] = (float)wl[h];
     if (ev_start) TNK_CUDA_OK(cudaEventRecord(ev_start, st));
     dim3 grid((unsigned)row_tiles, (unsigned)splits, 1);
     int rc = 2;
     switch (nc * 2 + (fmt ? 1 : 0)) {
-        case 4: rc = launch_sym<2, 0>(prm, grid, B_tab, ST, Cst, qT, part, ucol, st); break;
-        case 5: rc = launch_sym<2, 1>(prm, grid, B_tab, ST, Cst, qT, part, ucol, st); break;
-        case 6: rc = launch_sym<3, 0>(prm, grid, B_tab, ST, Cst, qT, part, ucol, st); break;
-        case 7: rc = launch_sym<3, 1>(prm, grid, B_tab, ST, Cst, qT, part, ucol, st); break;
-        case 8: rc = launch_sym<4, 0>(prm, grid, B_tab, ST, Cst, qT, part, ucol, st); break;
-        case 9: rc = launch_sym<4, 1>(prm, grid, B_tab, ST, Cst, qT, part, ucol, st); break;
-        case 10: rc = launch_sym<5, 0>(prm, grid, B_tab, ST, Cst, qT, part, ucol, st); break;
-        case 11: rc = launch_sym<5, 1>(prm, grid, B_tab, ST, Cst, qT, part, ucol, st); break;
-        case 12: rc = launch_sym<6, 0>(prm, grid, B_tab, ST, Cst, qT, part, ucol, st); break;
-        case 13: rc = launch_sym<6, 1>(prm, grid, B_tab, ST, Cst, qT, part, ucol, st); break;
+        case 4: rc = launch_sym<2, 0>(prm, grid, B_tab, ST, Cst, qT, ucol, st); break;
+        case 5: rc = launch_sym<2, 1>(prm, grid, B_tab, ST, Cst, qT, ucol, st); break;
+        case 6: rc = launch_sym<3, 0>(prm, grid, B_tab, ST, Cst, qT, ucol, st); break;
+        case 7: rc = launch_sym<3, 1>(prm, grid, B_tab, ST, Cst, qT, ucol, st); break;
+        case 8: rc = launch_sym<4, 0>(prm, grid, B_tab, ST, Cst, qT, ucol, st); break;
+        case 9: rc = launch_sym<4, 1>(prm, grid, B_tab, ST, Cst, qT, ucol, st); break;
+        case 10: rc = launch_sym<5, 0>(prm, grid, B_tab, ST, Cst, qT, ucol, st); break;
+        case 11: rc = launch_sym<5, 1>(prm, grid, B_tab, ST, Cst, qT, ucol, st); break;
+        case 12: rc = launch_sym<6, 0>(prm, grid, B_tab, ST, Cst, qT, ucol, st); break;
+        case 13: rc = launch_sym<6, 1>(prm, grid, B_tab, ST, Cst, qT, ucol, st); break;
         default: tnk_set_error("tnk_ksd_sym: no kernel instance for %d chunks", nc); break;
     }
     if (rc) return rc;

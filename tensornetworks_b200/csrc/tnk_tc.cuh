@@ -95,5 +95,5 @@ int tnk_tc_launch(int n, double a, double gamma, const double* wl, const float* 
 size_t tnk_tcs_table_bytes(int n, int fmt, int64_t states);
 int tnk_tcs_launch(int n, int fmt, double gamma, const double* wl, const float* ST, const float* Cst, const float* qT,
                    int tile_offset, int tile_stride, int row_tiles, int splits, float* B_tab, int reuse_table,
-                   double* part, double* ucol, cudaEvent_t ev_start, cudaEvent_t ev_stop, int* launches,
+                   double* ucol, cudaEvent_t ev_start, cudaEvent_t ev_stop, int* launches,
                    cudaStream_t st);
