@@ -557,7 +557,7 @@ tc_rows_kernel(const __grid_constant__ TcParams prm, const float* __restrict__ B
 // its 4 rows in registers and over the 8 row groups of the warp with a transposing exchange (14 SHFL),
 // then added to ucol[] with one fp64 RED per column, warp and tile (the 4 lane quarters meet in L2).  The Hamming weight of the 7 in-tile bits factorises over the patch: per-thread constant x
 // (compile-time power of a from the unrolled row/column slots) -> 6 packed weights in registers.
-// Row sums: fp32 per tile, compensated fp32 across tiles, fp64 at the end (as in tc_rows_kernel), added to the
+// Row sums: fp32 per chunk of 8 tiles, compensated fp32 across chunks, fp64 at the end, added to the
 // same accumulator u[] with one fp64 RED per row and CTA (no per-split partial buffer: at n = 24 it would be 68 GB).
 // Both kinds of sums arrive by atomics, so the last bits of u depend on the arrival order (observed: <= 2e-16).
 // ======================================================================================================
@@ -891,7 +891,7 @@ tcs_tiles_kernel(const __grid_constant__ TcsParams prm, const float* __restrict_
         float qi[4];
 #pragma unroll
         for (int k = 0; k < 4; ++k) qi[k] = qT[I * kTile + rq + 8 * k];
-        float uhi[4] = {0.f, 0.f, 0.f, 0.f}, ulo[4] = {0.f, 0.f, 0.f, 0.f};
+        float uhi[4] = {0.f, 0.f, 0.f, 0.f}, ulo[4] = {0.f, 0.f, 0.f, 0.f}, uch[4] = {0.f, 0.f, 0.f, 0.f};
         const bool b4 = (t & 16) != 0, b3 = (t & 8) != 0, b2 = (t & 4) != 0;
         for (int64_t it = 0; it < n_local; ++it) {
             const int ts = (int)(it & 1);
@@ -942,13 +942,18 @@ tcs_tiles_kernel(const __grid_constant__ TcsParams prm, const float* __restrict_
             };
             fold(v0, 0);
             fold(v1, 1);
+            // row sums: plain fp32 over a chunk of 8 tiles, TwoSum across chunks
 #pragma unroll
-            for (int k = 0; k < 4; ++k) {
-                const float utile = wg * (racc[k].x + racc[k].y);
-                const float sum = uhi[k] + utile;           // TwoSum
-                const float bb = sum - uhi[k];
-                ulo[k] += (uhi[k] - (sum - bb)) + (utile - bb);
-                uhi[k] = sum;
+            for (int k = 0; k < 4; ++k) uch[k] = fmaf(wg, racc[k].x + racc[k].y, uch[k]);
+            if ((it & 7) == 7 || it + 1 == n_local) {
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    const float sum = uhi[k] + uch[k];      // TwoSum
+                    const float bb = sum - uhi[k];
+                    ulo[k] += (uhi[k] - (sum - bb)) + (uch[k] - bb);
+                    uhi[k] = sum;
+                    uch[k] = 0.f;
+                }
             }
             if (J != I) {
                 // mirrored part: sum over the warp's 32 rows (8 row groups = lane bits 2-4), exchanging halves of the
