@@ -210,11 +210,9 @@ def run_ours(args):
 
     def device_step():
         if sym:
-            u, part = tables.ksd_sym(q_dev, rank, world)          # row tiles rank, rank + world, ...
+            u, part = tables.ksd_sym(q_dev, *ops.sym_tile_stripe(rank, world))   # row tiles rank, rank + world, ...
             if world > 1:
-                buf = torch.cat([u, part])
-                dist.all_reduce(buf, op=dist.ReduceOp.SUM)
-                u, part = buf[:-1], buf[-1:]
+                u, part = ops.combine_partial_sums(u, part)
             return u, part
         if exchange is not None:
             return ops.ksd_rows_fused(tables, q_dev, exchange)   # K3 + K4 with peer stores + barrier

@@ -270,6 +270,21 @@ def combine_row_shards(u_rows, part, num_states, rank, world, group=None):
     return buf[:num_states], buf[num_states:].clone()
 
 
+def sym_tile_stripe(rank, world):
+    """(tile_offset, tile_stride) of rank `rank` for the symmetric evaluation: 128-state row tiles dealt round-robin,
+    so every rank owns the same share of the triangle J >= I."""
+    return rank, world
+
+
+def combine_partial_sums(u_partial, part, group=None):
+    """Exchange step of the symmetric evaluation: every rank holds a full-length partial of u = K_p q (its row
+    tiles' rows and mirrored columns) and of q.u; one sum-all-reduce of [u | part] gives every rank u [N] and K [1].
+    Backend-neutral (NCCL on the GPUs, gloo in the CPU tests)."""
+    buf = torch.cat([u_partial, part.reshape(1)])
+    dist.all_reduce(buf, op=dist.ReduceOp.SUM, group=group)
+    return buf[:-1], buf[-1:].clone()
+
+
 class PeerExchange:
     """Sinks of the fused exchange (tnk_ksd_rows_peers): per rank a symmetric-memory buffer
     [buffers][N + world] of fp64 - u rows followed by one partial-K slot per rank - mapped into
@@ -358,11 +373,9 @@ class _KsdQuadraticForm(torch.autograd.Function):
                 dist.all_reduce(buf, op=dist.ReduceOp.SUM, group=group)
                 u, part = buf[:-1], buf[-1:].clone()
         elif algorithm == "pairs_sym":
-            u, part = tables.ksd_sym(q_dev, rank, world)    # row tiles dealt round-robin: equal triangle shares
+            u, part = tables.ksd_sym(q_dev, *sym_tile_stripe(rank, world))
             if world > 1:
-                buf = torch.cat([u, part])
-                dist.all_reduce(buf, op=dist.ReduceOp.SUM, group=group)
-                u, part = buf[:-1], buf[-1:].clone()
+                u, part = combine_partial_sums(u, part, group)
         elif exchange is not None and world > 1:
             u, part = ksd_rows_fused(tables, q_dev, exchange)
             u = u.clone()     # the symmetric buffer is rewritten two evaluations later

@@ -151,3 +151,41 @@ def test_row_shard_exchange_gloo_world2():
         u, Kr = ret[(rank, (1 << n) - 3)]
         assert np.allclose(2 * u, g[:-3], rtol=1e-12)
         assert np.isclose(Kr, float(q[:-3] @ (g[:-3] / 2)), rtol=1e-12)
+
+
+def _gloo_sym_worker(rank, world, port, n, ret):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    from tensornetworks_b200 import ops
+    bn, lat, obs, x = random_binary_bn(n, seed=2)
+    S = orc.score_table(orc.joint_table(bn, x, lat), n)
+    q = np.random.default_rng(0).dirichlet(np.ones(1 << n))
+    N, T = 1 << n, (1 << n) // 128
+    offset, stride = ops.sym_tile_stripe(rank, world)
+    u = np.zeros(N)                                   # what tnk_ksd_sym(tile_offset, tile_stride) returns: the oracle's
+    for I in range(offset, T, stride):                # dense blocks stand in for the CUDA tiles in this CPU test
+        rows = np.arange(128 * I, 128 * I + 128)
+        Kp = orc.stein_matrix_dense(S, n, 1.0, rows)
+        for J in range(I, T):
+            cols = slice(128 * J, 128 * J + 128)
+            u[rows] += Kp[:, cols] @ q[cols]
+            if J != I:
+                u[cols] += Kp[:, cols].T @ q[rows]
+    uu, K = ops.combine_partial_sums(torch.from_numpy(u), torch.tensor([float(q @ u)], dtype=torch.float64))
+    ret[rank] = (uu.numpy().copy(), float(K.item()))
+    dist.destroy_process_group()
+
+
+def test_symmetric_stripe_exchange_gloo_world2():
+    """N > 1 path of algorithm "pairs_sym": row tiles dealt round-robin, full-length partials, one sum-all-reduce."""
+    n, world, port = 9, 2, 29741
+    mgr = mp.Manager()
+    ret = mgr.dict()
+    mp.spawn(_gloo_sym_worker, args=(world, port, n, ret), nprocs=world, join=True)
+    bn, lat, obs, x = random_binary_bn(n, seed=2)
+    S = orc.score_table(orc.joint_table(bn, x, lat), n)
+    q = np.random.default_rng(0).dirichlet(np.ones(1 << n))
+    K, g = orc.ksd_dense(q, S, n)
+    for rank in range(world):
+        u, Kr = ret[rank]
+        assert np.allclose(2 * u, g, rtol=1e-10, atol=1e-10 * np.max(np.abs(g))) and np.isclose(Kr, K, rtol=1e-10)
