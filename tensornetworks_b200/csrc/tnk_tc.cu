@@ -70,17 +70,21 @@ __device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t by
                  ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
 }
 // Bounded wait: a protocol error traps (launch failure) instead of hanging the GPU.
+__device__ __forceinline__ uint32_t mbar_try(uint32_t addr, uint32_t parity) {
+    uint32_t done;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(done) : "r"(addr), "r"(parity) : "memory");
+    return done;
+}
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
     const uint32_t addr = smem_u32(bar);
+    if (mbar_try(addr, parity)) return;          // the common case costs no clock read
     const long long t0 = clock64();
     for (;;) {
-        uint32_t done;
-        asm volatile(
-            "{\n\t.reg .pred p;\n\t"
-            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
-            "selp.u32 %0, 1, 0, p;\n\t}"
-            : "=r"(done) : "r"(addr), "r"(parity) : "memory");
-        if (done) return;
+        if (mbar_try(addr, parity)) return;
         if (clock64() - t0 > 8000000000LL) __trap();
     }
 }
@@ -893,13 +897,14 @@ tcs_tiles_kernel(const __grid_constant__ TcsParams prm, const float* __restrict_
         for (int k = 0; k < 4; ++k) qi[k] = qT[I * kTile + rq + 8 * k];
         float uhi[4] = {0.f, 0.f, 0.f, 0.f}, ulo[4] = {0.f, 0.f, 0.f, 0.f}, uch[4] = {0.f, 0.f, 0.f, 0.f};
         const bool b4 = (t & 16) != 0, b3 = (t & 8) != 0, b2 = (t & 4) != 0;
-        for (int64_t it = 0; it < n_local; ++it) {
+        const uint32_t n_loc = (uint32_t)n_local, I32 = (uint32_t)I, j0 = (uint32_t)j_begin;   // < 2^17 tiles
+        for (uint32_t it = 0; it < n_loc; ++it) {
             const int ts = (int)(it & 1);
-            const uint32_t tph = (uint32_t)((it >> 1) & 1);
+            const uint32_t tph = (it >> 1) & 1;
             const int qs = (int)(it & (kQSlots - 1));
-            const uint32_t qph = (uint32_t)((it / kQSlots) & 1);
-            const int64_t J = j_begin + it;
-            const float wg = sWl[__popc((uint32_t)I ^ (uint32_t)J)];
+            const uint32_t qph = (it / kQSlots) & 1;
+            const uint32_t J = j0 + it;
+            const float wg = sWl[__popc(I32 ^ J)];
             mbar_wait(bar_qfull + qs, qph);
             mbar_wait(bar_tfull + ts, tph);
             tc_fence_after();
@@ -945,7 +950,7 @@ tcs_tiles_kernel(const __grid_constant__ TcsParams prm, const float* __restrict_
             // row sums: plain fp32 over a chunk of 8 tiles, TwoSum across chunks
 #pragma unroll
             for (int k = 0; k < 4; ++k) uch[k] = fmaf(wg, racc[k].x + racc[k].y, uch[k]);
-            if ((it & 7) == 7 || it + 1 == n_local) {
+            if ((it & 7) == 7 || it + 1 == n_loc) {
 #pragma unroll
                 for (int k = 0; k < 4; ++k) {
                     const float sum = uhi[k] + uch[k];      // TwoSum
@@ -955,7 +960,7 @@ tcs_tiles_kernel(const __grid_constant__ TcsParams prm, const float* __restrict_
                     uch[k] = 0.f;
                 }
             }
-            if (J != I) {
+            if (J != I32) {
                 // mirrored part: sum over the warp's 32 rows (8 row groups = lane bits 2-4), exchanging halves of the
                 // column set per level; with 4 atoms per thread the last level is a plain exchange-add
                 auto xadd = [&](const float2 keep, const float2 send, const int mask) {
@@ -983,7 +988,7 @@ tcs_tiles_kernel(const __grid_constant__ TcsParams prm, const float* __restrict_
                 // one fp64 RED per column, warp and tile (fire and forget; the four lane quarters meet in L2 - measured
                 // faster than combining them in shared memory behind a named barrier)
                 if (MC == 8 || !b2) {
-                    double* dst = ucol + J * kTile + colbase + col;
+                    double* dst = ucol + (size_t)J * kTile + colbase + col;
                     atomicAdd(dst, (double)(wg * c3.x));
                     atomicAdd(dst + 1, (double)(wg * c3.y));
                 }
