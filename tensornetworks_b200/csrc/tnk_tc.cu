@@ -964,8 +964,8 @@ tcs_tiles_kernel(const __grid_constant__ TcsParams prm, const float* __restrict_
                 // mirrored part: sum over the warp's 32 rows (8 row groups = lane bits 2-4), exchanging halves of the
                 // column set per level; with 4 atoms per thread the last level is a plain exchange-add
                 auto xadd = [&](const float2 keep, const float2 send, const int mask) {
-                    return make_float2(keep.x + __shfl_xor_sync(0xffffffffu, send.x, mask),
-                                       keep.y + __shfl_xor_sync(0xffffffffu, send.y, mask));
+                    return __fadd2_rn(keep, make_float2(__shfl_xor_sync(0xffffffffu, send.x, mask),
+                                                        __shfl_xor_sync(0xffffffffu, send.y, mask)));
                 };
                 float2 c3;
                 int col;
