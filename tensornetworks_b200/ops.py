@@ -163,8 +163,11 @@ class SteinTables:
         lib = _lib.load()
         with torch.cuda.device(self.device):
             key = ("sym", tile_offset, tile_stride, split)
-            reuse = key in self._ws
-            if not reuse:
+            built = getattr(self, "_sym_tables", None)
+            if built is None:
+                built = self._sym_tables = set()      # workspaces whose column table a successful call has built
+            reuse = key in built and key in self._ws
+            if key not in self._ws:
                 nbytes = lib.tnk_ksd_sym_workspace_bytes(self.n, code, tile_offset, tile_stride)
                 if nbytes == 0:
                     raise RuntimeError(f"tnk_ksd_sym_workspace_bytes rejected n={self.n}, tiles ({tile_offset}, {tile_stride})")
@@ -177,6 +180,7 @@ class SteinTables:
                                        _ptr(self.ST), _ptr(self.Cst), tile_offset, tile_stride, 1 if reuse else 0,
                                        _ptr(u), _ptr(part), _ptr(ws), ws.numel(), ctypes.byref(launched),
                                        _stream_ptr(self.device)), "tnk_ksd_sym")
+            built.add(key)
             launch_counter["kernels"] += launched.value
         return u, part
 
