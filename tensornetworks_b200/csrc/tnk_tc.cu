@@ -457,19 +457,20 @@ tc_rows_kernel(const __grid_constant__ TcParams prm, const float* __restrict__ B
         // cycles behind the tensor pipe (ncu: math-pipe throttle on a per-tile DADD), so fp64 is
         // touched only once, after the sweep.
         float uhi = 0.f, ulo = 0.f;
-        for (int64_t it = 0; it < n_local; ++it) {
+        const uint32_t n_loc = (uint32_t)n_local, j0 = (uint32_t)j_first;   // < 2^17 column tiles
+        for (uint32_t it = 0; it < n_loc; ++it) {
             const int ts = (int)(it & 1);
-            const uint32_t tph = (uint32_t)((it >> 1) & 1);
+            const uint32_t tph = (it >> 1) & 1;
             const int qs = (int)(it & (kQSlots - 1));
-            const uint32_t qph = (uint32_t)((it / kQSlots) & 1);
-            const int64_t J = j_first + it;
-            const int xhi = __popc(ihi ^ (uint32_t)J);
+            const uint32_t qph = (it / kQSlots) & 1;
+            const uint32_t J = j0 + it;
+            const int xhi = __popc(ihi ^ J);
             if (it == 0 || (J & 15) == 0) {
                 Ehi = Ci;
 #pragma unroll
                 for (int p = 7; p < NP; ++p) Ehi += ((J >> (p - 7)) & 1) ? gp[p] : 0.f;
             } else {
-                const int k = __ffsll(J) - 1;
+                const int k = __ffs((int)J) - 1;
                 Ehi += (k == 0) ? dE[0] : (k == 1) ? dE[1] : (k == 2) ? dE[2] : dE[3];
             }
             mbar_wait(bar_qfull + qs, qph);
