@@ -194,8 +194,26 @@ int tnk_ksd_sym(int n_latent, double length_scale, int split, const void* q, int
                 double* u_partial, double* ksd_part,
                 void* workspace, size_t workspace_bytes, int* n_launch, void* stream);
 
-/* Measurement hook: when both are non-NULL cudaEvent_t handles, every following tnk_ksd_rows or
- * tnk_ksd_sym call on this host thread records them on its stream immediately before and after the pair kernel
+/* Symmetric fp64 evaluation of the same quadratic form (reference ksd_vi.py:110-131; k_p symmetric, stein_utils.py:161-196):
+ * the 1e-6 mode at N(N+128)/2 instead of 4^n pair evaluations.  fp64 throughout (score dot product as fp64 tensor-core
+ * MMAs, everything else DFMA/DADD); the result is bit-reproducible run to run (fixed summation order, no floating-point
+ * atomics between different threads).  7 <= n <= 24.
+ *   ST, Cst   the fp64 tables tnk_score emits for TNK_PREC_FP64
+ *   unit_offset, unit_stride   the pair space is cut into tnk_ksd_sym64_units(n) work units (pairs of tile panels); this
+ *             call owns units unit_offset + k*unit_stride: rank g of G passes (g, G); (0, 1) is the whole evaluation
+ *   u_partial device double [N] (out): contributions of the owned units to u = K_p q; the sum over all offsets of one
+ *             stride is u.  ksd_part device double [1] (out): sum_z q_z u_partial[z]. */
+#define TNK_SYM64_MIN_LATENT 7
+#define TNK_SYM64_MAX_LATENT 24
+size_t tnk_ksd_sym64_workspace_bytes(int n_latent, int unit_offset, int unit_stride);
+int tnk_ksd_sym64_units(int n_latent);
+int tnk_ksd_sym64(int n_latent, double length_scale, const void* q, int q_dtype,
+                  const double* ST, const double* Cst, int unit_offset, int unit_stride,
+                  double* u_partial, double* ksd_part,
+                  void* workspace, size_t workspace_bytes, int* n_launch, void* stream);
+
+/* Measurement hook: when both are non-NULL cudaEvent_t handles, every following tnk_ksd_rows,
+ * tnk_ksd_sym or tnk_ksd_sym64 call on this host thread records them on its stream immediately before and after the pair kernel
  * (K3) alone, so a benchmark can time the dominant kernel live.  Pass NULL, NULL to switch off. */
 int tnk_ksd_timing_events(void* start_event, void* stop_event);
 

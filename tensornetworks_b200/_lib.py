@@ -16,7 +16,7 @@ REPO_DIR = os.path.dirname(PKG_DIR)
 CSRC = os.path.join(PKG_DIR, "csrc")
 INCLUDE = os.path.join(REPO_DIR, "include")
 LIB_PATH = os.path.join(PKG_DIR, "libtnk_b200.so")
-SOURCES = ["tnk_enum.cu", "tnk_ksd.cu", "tnk_peak.cu", "tnk_modeprod.cu", "tnk_tc.cu", "tnk_born.cu"]
+SOURCES = ["tnk_enum.cu", "tnk_ksd.cu", "tnk_peak.cu", "tnk_modeprod.cu", "tnk_tc.cu", "tnk_born.cu", "tnk_sym64.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC", "-I", INCLUDE]
 
@@ -30,7 +30,8 @@ EXPORTS = ["tnk_last_error", "tnk_version", "tnk_bn_joint", "tnk_ksd_layout", "t
            "tnk_ksd_workspace_bytes", "tnk_ksd_rows", "tnk_ksd_rows_peers", "tnk_ksd_timing_events", "tnk_alu_peak",
            "tnk_ksd_modeproduct_workspace_bytes", "tnk_modeproduct_tables", "tnk_modeproduct_plan_limit", "tnk_ksd_modeproduct", "tnk_tc_plan",
            "tnk_born_blocks", "tnk_born_forward", "tnk_born_backward",
-           "tnk_ksd_sym_workspace_bytes", "tnk_ksd_sym"]
+           "tnk_ksd_sym_workspace_bytes", "tnk_ksd_sym",
+           "tnk_ksd_sym64_workspace_bytes", "tnk_ksd_sym64_units", "tnk_ksd_sym64"]
 
 
 def _nvcc():
@@ -110,6 +111,13 @@ def load():
     lib.tnk_ksd_sym.restype = c_int
     lib.tnk_ksd_sym.argtypes = [c_int, c_dbl, c_int, c_vp, c_int, c_vp, c_vp, c_int, c_int, c_int, c_vp, c_vp,
                                 c_vp, c_sz, ctypes.POINTER(c_int), c_vp]
+    lib.tnk_ksd_sym64_workspace_bytes.restype = c_sz
+    lib.tnk_ksd_sym64_workspace_bytes.argtypes = [c_int, c_int, c_int]
+    lib.tnk_ksd_sym64_units.restype = c_int
+    lib.tnk_ksd_sym64_units.argtypes = [c_int]
+    lib.tnk_ksd_sym64.restype = c_int
+    lib.tnk_ksd_sym64.argtypes = [c_int, c_dbl, c_vp, c_int, c_vp, c_vp, c_int, c_int, c_vp, c_vp,
+                                  c_vp, c_sz, ctypes.POINTER(c_int), c_vp]
     lib.tnk_ksd_modeproduct_workspace_bytes.restype = c_sz
     lib.tnk_ksd_modeproduct_workspace_bytes.argtypes = [c_int, c_int, c_int, c_int]
     lib.tnk_ksd_modeproduct.restype = c_int

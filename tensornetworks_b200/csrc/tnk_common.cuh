@@ -11,6 +11,8 @@
 #endif
 
 void tnk_set_error(const char* fmt, ...);
+// the event pair of tnk_ksd_timing_events for the calling thread (both NULL when switched off)
+void tnk_timing_events_get(cudaEvent_t* start, cudaEvent_t* stop);
 
 #define TNK_CUDA_OK(call)                                                              \
     do {                                                                               \

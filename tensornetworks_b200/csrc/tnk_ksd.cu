@@ -517,6 +517,11 @@ int dispatch_np_wide(int np, const KsdParams& prm, dim3 grid, const void* ST, co
 
 static thread_local cudaEvent_t g_ev_start = nullptr, g_ev_stop = nullptr;
 
+void tnk_timing_events_get(cudaEvent_t* start, cudaEvent_t* stop) {
+    *start = g_ev_start;
+    *stop = g_ev_stop;
+}
+
 extern "C" int tnk_ksd_timing_events(void* start_event, void* stop_event) {
     g_ev_start = (cudaEvent_t)start_event;
     g_ev_stop = (cudaEvent_t)stop_event;

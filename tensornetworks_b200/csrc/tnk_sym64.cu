@@ -1,0 +1,535 @@
+// K3-S64: symmetric fp64 pair kernel (tnk_ksd_sym64) - the 1e-6 mode at half the pair evaluations.
+//
+// k_p(z,z') = k_p(z',z) (reference stein_utils.py:161-196 is symmetric in its arguments), so the pair space is cut
+// into 128 x 128-state tiles and every unordered pair of tiles (I <= J) is evaluated once: its values feed the rows of
+// tile I and, mirrored, the rows of tile J.  Per pair (closed form of tnk_ksd.cu / DESIGN.md section 2)
+//     Y(i,j) = a^popc(i^j) * [ s(i).s(j) + C(i) + C(j) + T1(i,j) + T2(i,j) ],   T1 = sum_p g_p(i) b_p(j) = T2(j,i),
+// with g_p(z) = gamma * (1 - s_p(z)) * (1 - 2 b_p(z)).
+//
+// Arithmetic.  The score dot product and the T1/T2 terms of bit positions 3 and 4 run as fp64 tensor-core MMAs
+// (mma.sync.m8n8k4.f64 = DMMA: NP/4 + 1 K-steps per 8 x 8 pairs; the probe scripts/probes/dmma_rate.cu shows DMMA
+// and DFMA share one pipe at about the same FMA rate, so the gain is issue slots, register and shared-memory
+// traffic, not flops).  A warp owns 32 rows (A fragments resident in registers for a whole row tile) and walks
+// 32-column blocks in two batches of 16 columns; the accumulator fragment gives thread t the rows t/4 + 8a
+// (a = 0..3) and the columns 2(t%4) + e + 8b (e = 0,1; b = 0..3) of the block.  Every index bit that is not a/b is
+// constant per thread, warp, block or tile, so the remaining T1/T2 terms and C(i) + C(j) arrive as ONE add per pair
+// (the accumulator seed Erow[a][e] + Ecol[b][e]) and the Hamming weight as one multiply by a^popc(a^b) (a compile-
+// time constant after unrolling) - the rest of the weight is folded into q_j, into the column sums and into one
+// factor per block.  Per executed pair: 4 (NP/4 + 1) DMMA lane-FMAs + 1 DADD + 0.75 DMUL + 2 DFMA.
+//
+// Schedule and determinism.  The T = N/128 tiles are grouped into B <= 128 panels of s tiles; a work unit is a
+// panel pair (pa <= pb) handled by one CTA: for every row tile I of pa it sweeps the column tiles J of pb (J >= I on
+// the diagonal).  Row sums stay in registers over a sweep and are stored once into RowPart[pb][rows of I]; the
+// mirrored column sums of a tile are added over the CTA's 32 row groups in shared memory in a fixed order and then
+// accumulated into ColPart[pa][cols of J] by the same thread every time (first a plain store, afterwards
+// red.global.add.f64 from that one thread: same-address program order).  tnk_sym64 finish kernel adds the slots in a
+// fixed order: the result is bit-reproducible run to run (the tcgen05 tile kernel's is not).
+#include "tnk_common.cuh"
+
+namespace {
+
+constexpr int kTile = 128;
+constexpr int kThreads = 256;
+constexpr int kStageStride = 136;      // doubles per row group of the column-sum stage (128 + 8: conflict-free STS.128)
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, int count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "WAIT_%=:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+        "@p bra DONE_%=;\n\t"
+        "bra WAIT_%=;\n\t"
+        "DONE_%=:\n\t}"
+        ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+// D(8x8) += A(8x4) * B(4x8), fp64.  A: row t/4, k t%4;  B: k t%4, col t/4;  D: row t/4, cols 2(t%4)+{0,1}.
+__device__ __forceinline__ void dmma(double& d0, double& d1, double a, double b) {
+    asm("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
+        : "+d"(d0), "+d"(d1) : "d"(a), "d"(b));
+}
+__device__ __forceinline__ void red_add_f64(double* addr, double v) {
+    asm volatile("red.global.add.f64 [%0], %1;" ::"l"(addr), "d"(v) : "memory");
+}
+
+struct Sym64Params {
+    int n;
+    int T;               // tiles of 128 states
+    int B;               // panels
+    int s;               // tiles per panel
+    int unit_offset, unit_stride, n_units;   // this launch owns units unit_offset + k*unit_stride, k < n_units
+    double a, gamma;
+    double wl[32];       // exp(-h/(n l))
+};
+
+// unit k (row-major over the upper triangle incl. the diagonal) -> (pa, pb)
+__host__ __device__ inline void unit_to_panels(int k, int B, int* pa, int* pb) {
+    int a = 0;
+    while (k >= B - a) { k -= B - a; ++a; }
+    *pa = a;
+    *pb = a + k;
+}
+__host__ __device__ inline int64_t panels_to_unit(int pa, int pb, int B) {
+    return (int64_t)pa * B - (int64_t)pa * (pa - 1) / 2 + (pb - pa);
+}
+
+template <int NP>
+struct Smem64 {
+    static constexpr int DOT = NP / 4;                  // K-steps of the score dot product
+    static constexpr size_t raw_bytes = (size_t)kTile * NP * sizeof(double);
+    static constexpr size_t buf_bytes = raw_bytes + 2 * kTile * sizeof(double);      // raw | Cst | q
+    static constexpr size_t off_buf = 0;                                              // [2] buffers
+    static constexpr size_t off_stage = off_buf + 2 * buf_bytes;                      // [32][kStageStride]
+    static constexpr size_t off_rowg = off_stage + (size_t)32 * kStageStride * sizeof(double);   // [24][128]
+    static constexpr size_t off_colA = off_rowg + (size_t)24 * kTile * sizeof(double);           // [4][128]
+    static constexpr size_t off_colB = off_colA + (size_t)4 * kTile * sizeof(double);            // [8][128]
+    static constexpr size_t off_colG = off_colB + (size_t)8 * kTile * sizeof(double);            // [128][2]
+    static constexpr size_t off_rowred = off_colG + (size_t)2 * kTile * sizeof(double);          // [2][128]
+    static constexpr size_t off_wl = off_rowred + (size_t)2 * kTile * sizeof(double);            // [32]
+    static constexpr size_t off_bar = off_wl + 32 * sizeof(double);
+    static constexpr size_t total = off_bar + 16;
+};
+
+// physical score component a lane supplies to dot K-step `t` (the same permutation on the A and the B side):
+// steps come in pairs that split an 8-wide group so that one 16-byte load feeds two steps
+template <int NP>
+__device__ __forceinline__ int dot_component(int t, int k) {
+    constexpr int PAIRS = (NP / 4) / 2;
+    return (t < 2 * PAIRS) ? 8 * (t >> 1) + 2 * k + (t & 1) : NP - 4 + k;
+}
+
+template <int NP>
+__global__ void __launch_bounds__(kThreads, 1)
+sym64_kernel(const Sym64Params prm, const double* __restrict__ ST, const double* __restrict__ Cst,
+             const double* __restrict__ qT, double* __restrict__ RowPart, double* __restrict__ ColPart) {
+    using SM = Smem64<NP>;
+    constexpr int DOT = SM::DOT, PAIRS = DOT / 2;
+    extern __shared__ __align__(128) unsigned char smem[];
+    double* stage = reinterpret_cast<double*>(smem + SM::off_stage);
+    double* rowg = reinterpret_cast<double*>(smem + SM::off_rowg);
+    double* colA = reinterpret_cast<double*>(smem + SM::off_colA);
+    double* colB = reinterpret_cast<double*>(smem + SM::off_colB);
+    double* colG = reinterpret_cast<double*>(smem + SM::off_colG);
+    double* rowred = reinterpret_cast<double*>(smem + SM::off_rowred);
+    double* sWl = reinterpret_cast<double*>(smem + SM::off_wl);
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + SM::off_bar);
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int wr = warp >> 1, wc = warp & 1;       // row block (32 rows) and column half (64 columns) of the warp
+    const int r = lane >> 2, k4 = lane & 3;        // row inside an 8-row group; K index / column pair of the fragments
+    const int n = prm.n;
+    const int64_t N = (int64_t)1 << n;
+    const double gam = prm.gamma, av = prm.a;
+
+    int pa, pb;
+    unit_to_panels(prm.unit_offset + (int)blockIdx.x * prm.unit_stride, prm.B, &pa, &pb);
+    const int s = prm.s;
+    const int I_begin = pa * s, J_end = (pb + 1) * s;
+    const bool diag = pa == pb;
+    double* rowpart = RowPart + (size_t)pb * N;
+    double* colpart = ColPart + (size_t)pa * N;
+
+    if (tid < 32) sWl[tid] = prm.wl[tid];
+    if (tid == 0) {
+        mbar_init(&bars[0], 1);
+        mbar_init(&bars[1], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+
+    auto issue_tile = [&](int J, int buf) {          // one thread: three bulk copies on the buffer's barrier
+        unsigned char* dst = smem + SM::off_buf + (size_t)buf * SM::buf_bytes;
+        mbar_expect_tx(&bars[buf], (uint32_t)SM::buf_bytes);
+        bulk_g2s(dst, ST + (size_t)J * kTile * NP, (uint32_t)SM::raw_bytes, &bars[buf]);
+        bulk_g2s(dst + SM::raw_bytes, Cst + (size_t)J * kTile, kTile * sizeof(double), &bars[buf]);
+        bulk_g2s(dst + SM::raw_bytes + kTile * sizeof(double), qT + (size_t)J * kTile, kTile * sizeof(double), &bars[buf]);
+    };
+
+    // thread constants of the Hamming weight: bits 1,2 of i^j, and the e-dependent bit 0
+    const double wt = (__popc(((r >> 1) & 3) ^ k4) == 0) ? 1.0 : (__popc(((r >> 1) & 3) ^ k4) == 1 ? av : av * av);
+    const double we0 = (r & 1) ? av : 1.0, we1 = (r & 1) ? 1.0 : av;     // a^((r&1)^e)
+    const double w1 = av, w2 = av * av;
+
+    uint32_t t_iter = 0;                             // tiles issued so far by this CTA (buffer = t&1, parity = (t>>1)&1)
+    int pend_J = -1;                                 // column tile whose stage still has to be flushed
+    bool pend_first = false;
+
+    auto flush_stage = [&](int J, bool first) {      // threads 0..127: fixed-order sum of the 32 row groups, then global
+        if (tid < kTile) {
+            double acc = 0.0;
+#pragma unroll 8
+            for (int g = 0; g < 32; ++g) acc += stage[g * kStageStride + tid];
+            double* dst = colpart + (size_t)J * kTile + tid;
+            if (first) *dst = acc; else red_add_f64(dst, acc);
+        }
+    };
+
+    for (int I = I_begin; I < I_begin + s; ++I) {
+        const int J_begin = diag ? I : pb * s;
+        const int64_t i_base = (int64_t)I * kTile + wr * 32 + r;     // + 8a
+
+        __syncthreads();                             // previous row tile fully consumed (rowg, stage, buffers)
+        if (pend_J >= 0) { flush_stage(pend_J, pend_first); pend_J = -1; }
+        if (tid == 0) issue_tile(J_begin, (int)(t_iter & 1));
+
+        // ---- row operands of tile I: A fragments, per-row constants, shared table of g_p(i) for p >= 7
+        double Af[DOT + 1][4];
+        double qi[4], g0[4], g5[4], g6[4], rbase[4];
+#pragma unroll
+        for (int a = 0; a < 4; ++a) {
+            const int64_t i = i_base + 8 * a;
+            const double* si = ST + i * NP;
+#pragma unroll
+            for (int m = 0; m < PAIRS; ++m) {
+                const double2 v = *reinterpret_cast<const double2*>(si + 8 * m + 2 * k4);
+                Af[2 * m][a] = v.x;
+                Af[2 * m + 1][a] = v.y;
+            }
+            if (DOT & 1) Af[DOT - 1][a] = si[NP - 4 + k4];
+            auto grow = [&](int p) -> double {       // g_p(i)
+                const double v = gam * (1.0 - si[p]);
+                return ((i >> p) & 1) ? -v : v;
+            };
+            // K-step DOT: [g_3(i), g_4(i), b_3(i), b_4(i)] . [b_3(j), b_4(j), g_3(j), g_4(j)]
+            Af[DOT][a] = k4 == 0 ? grow(3) : k4 == 1 ? grow(4) : k4 == 2 ? (double)(a & 1) : (double)(a >> 1);
+            qi[a] = qT[i];
+            g0[a] = grow(0);
+            g5[a] = grow(5);
+            g6[a] = grow(6);
+            // C(i) + column bits 1,2 (thread constants) + column bit 6 (warp constant)
+            rbase[a] = Cst[i] + ((k4 & 1) ? grow(1) : 0.0) + ((k4 & 2) ? grow(2) : 0.0) + (wc ? g6[a] : 0.0);
+        }
+        for (int item = tid; item < kTile * (n - 7); item += kThreads) {
+            const int row = item & (kTile - 1), p = 7 + (item >> 7);
+            const int64_t i = (int64_t)I * kTile + row;
+            const double v = gam * (1.0 - ST[i * NP + p]);
+            rowg[(p - 7) * kTile + row] = ((i >> p) & 1) ? -v : v;
+        }
+        double rsum[4] = {0.0, 0.0, 0.0, 0.0};
+
+        for (int J = J_begin; J < J_end; ++J, ++t_iter) {
+            const int buf = (int)(t_iter & 1);
+            const unsigned char* bufp = smem + SM::off_buf + (size_t)buf * SM::buf_bytes;
+            const double* raw = reinterpret_cast<const double*>(bufp);
+            const double* cC = reinterpret_cast<const double*>(bufp + SM::raw_bytes);
+            const double* cq = cC + kTile;
+            const bool mirrored = J != I;
+
+            __syncthreads();      // (A) tile t-1 fully consumed: tables, stage (complete), buffer buf^1 free; rowg visible
+            if (pend_J >= 0) { flush_stage(pend_J, pend_first); pend_J = -1; }
+            if (tid == 0 && J + 1 < J_end) issue_tile(J + 1, buf ^ 1);
+            mbar_wait(&bars[buf], (t_iter >> 1) & 1);
+
+            // ---- per-tile column tables: colA[wr][c] = C(c) + sum_{p>=7} b_p(I) g_p(c) + bits 5,6 of the row block;
+            //      colB[r][c] = sum_{p<3} b_p(r) g_p(c);  colG[c][0..1] = g_3(c), g_4(c)
+            {
+                const int c = tid & (kTile - 1), half = tid >> 7;
+                const int64_t j = (int64_t)J * kTile + c;
+                const double* sc = raw + c * NP;
+                auto gcol = [&](int p) -> double {
+                    const double v = gam * (1.0 - sc[p]);
+                    return ((j >> p) & 1) ? -v : v;
+                };
+                if (half == 0) {
+                    double e = cC[c];
+                    for (uint32_t x = (uint32_t)I; x; x &= x - 1) e += gcol(7 + (__ffs(x) - 1));
+                    const double c5 = gcol(5), c6 = gcol(6);
+                    colA[0 * kTile + c] = e;
+                    colA[1 * kTile + c] = e + c5;
+                    colA[2 * kTile + c] = e + c6;
+                    colA[3 * kTile + c] = (e + c5) + c6;
+                } else {
+                    const double c0 = gcol(0), c1 = gcol(1), c2 = gcol(2);
+#pragma unroll
+                    for (int rr = 0; rr < 8; ++rr)
+                        colB[rr * kTile + c] = ((rr & 1) ? c0 : 0.0) + ((rr & 2) ? c1 : 0.0) + ((rr & 4) ? c2 : 0.0);
+                    colG[2 * c] = gcol(3);
+                    colG[2 * c + 1] = gcol(4);
+                }
+            }
+            // row side of the tile: rbase + sum_{p>=7} g_p(i) b_p(J)
+            double trow[4];
+#pragma unroll
+            for (int a = 0; a < 4; ++a) trow[a] = rbase[a];
+            for (uint32_t x = (uint32_t)J; x; x &= x - 1) {
+                const double* gp = rowg + (__ffs(x) - 1) * kTile + wr * 32 + r;
+#pragma unroll
+                for (int a = 0; a < 4; ++a) trow[a] += gp[8 * a];
+            }
+            const int hh = __popc((uint32_t)(I ^ J));
+            __syncthreads();      // (B) tables built
+
+#pragma unroll 1
+            for (int cbi = 0; cbi < 2; ++cbi) {
+                const int cb = 2 * wc + cbi;                           // 32-column block of the tile
+                const double wb = sWl[hh + __popc((uint32_t)(wr ^ cb))] * wt;
+                double er[4][2];                                       // row part of the seed
+#pragma unroll
+                for (int a = 0; a < 4; ++a) {
+                    er[a][0] = cbi ? trow[a] + g5[a] : trow[a];
+                    er[a][1] = er[a][0] + g0[a];
+                }
+                double racc[4] = {0.0, 0.0, 0.0, 0.0};
+#pragma unroll
+                for (int hb = 0; hb < 2; ++hb) {                       // batch: 16 columns (b = 2hb, 2hb+1)
+                    double acc[4][2][2];
+                    double qe[2][2];
+                    double Bf[DOT + 1][2];
+#pragma unroll
+                    for (int bb = 0; bb < 2; ++bb) {
+                        const int b = 2 * hb + bb;
+                        const int cfrag = cb * 32 + 8 * b + r;         // column this lane supplies to the B fragment
+                        const double* sc = raw + cfrag * NP;
+#pragma unroll
+                        for (int m = 0; m < PAIRS; ++m) {
+                            const double2 v = *reinterpret_cast<const double2*>(sc + 8 * m + 2 * k4);
+                            Bf[2 * m][bb] = v.x;
+                            Bf[2 * m + 1][bb] = v.y;
+                        }
+                        if (DOT & 1) Bf[DOT - 1][bb] = sc[NP - 4 + k4];
+                        const double gsel = colG[2 * cfrag + (k4 & 1)];
+                        Bf[DOT][bb] = k4 == 0 ? (double)(b & 1) : k4 == 1 ? (double)(b >> 1) : gsel;
+                        const int cacc = cb * 32 + 8 * b + 2 * k4;     // first of the two columns of the accumulator
+                        const double2 ea = *reinterpret_cast<const double2*>(colA + wr * kTile + cacc);
+                        const double2 eb = *reinterpret_cast<const double2*>(colB + r * kTile + cacc);
+                        const double2 qv = *reinterpret_cast<const double2*>(cq + cacc);
+                        const double ec0 = ea.x + eb.x, ec1 = ea.y + eb.y;
+                        qe[bb][0] = qv.x * we0;
+                        qe[bb][1] = qv.y * we1;
+#pragma unroll
+                        for (int a = 0; a < 4; ++a) {
+                            acc[a][bb][0] = er[a][0] + ec0;
+                            acc[a][bb][1] = er[a][1] + ec1;
+                        }
+                    }
+#pragma unroll
+                    for (int t = 0; t <= DOT; ++t)
+#pragma unroll
+                        for (int a = 0; a < 4; ++a)
+#pragma unroll
+                            for (int bb = 0; bb < 2; ++bb) dmma(acc[a][bb][0], acc[a][bb][1], Af[t][a], Bf[t][bb]);
+                    double cs[2][2] = {{0.0, 0.0}, {0.0, 0.0}};
+#pragma unroll
+                    for (int a = 0; a < 4; ++a)
+#pragma unroll
+                        for (int bb = 0; bb < 2; ++bb) {
+                            const int x = a ^ (2 * hb + bb);           // bits 3,4 of i^j
+                            const int pc = (x & 1) + (x >> 1);
+#pragma unroll
+                            for (int e = 0; e < 2; ++e) {
+                                const double v = pc == 0 ? acc[a][bb][e] : acc[a][bb][e] * (pc == 1 ? w1 : w2);
+                                racc[a] = fma(v, qe[bb][e], racc[a]);
+                                cs[bb][e] = fma(v, qi[a], cs[bb][e]);
+                            }
+                        }
+                    if (mirrored) {
+#pragma unroll
+                        for (int bb = 0; bb < 2; ++bb) {
+                            const int cacc = cb * 32 + 8 * (2 * hb + bb) + 2 * k4;
+                            *reinterpret_cast<double2*>(stage + (wr * 8 + r) * kStageStride + cacc) =
+                                make_double2(cs[bb][0] * (wb * we0), cs[bb][1] * (wb * we1));
+                        }
+                    }
+                }
+#pragma unroll
+                for (int a = 0; a < 4; ++a) rsum[a] = fma(wb, racc[a], rsum[a]);
+            }
+            if (mirrored) { pend_J = J; pend_first = (I == I_begin); }   // a column tile is first met by the panel's first row tile
+        }
+
+        // ---- row sums of tile I over this sweep: 4 lanes share a row, 2 warps share a row block
+#pragma unroll
+        for (int a = 0; a < 4; ++a) {
+            double v = rsum[a];
+            v += __shfl_xor_sync(0xffffffffu, v, 1);
+            v += __shfl_xor_sync(0xffffffffu, v, 2);
+            if (k4 == 0) rowred[wc * kTile + wr * 32 + 8 * a + r] = v;
+        }
+        __syncthreads();
+        if (tid < kTile) rowpart[(size_t)I * kTile + tid] = rowred[tid] + rowred[kTile + tid];
+    }
+    __syncthreads();
+    if (pend_J >= 0) flush_stage(pend_J, pend_first);
+}
+
+// u[z] = sum of the row-part and column-part slots of the units this launch owned (fixed order); block partials of q.u
+template <typename Q>
+__global__ void __launch_bounds__(256)
+sym64_finish_kernel(const Sym64Params prm, const double* __restrict__ RowPart, const double* __restrict__ ColPart,
+                    const Q* __restrict__ q, double* __restrict__ u, double* __restrict__ blockpart) {
+    __shared__ double red[256];
+    const int64_t N = (int64_t)1 << prm.n;
+    const int64_t z = (int64_t)blockIdx.x * 256 + threadIdx.x;
+    double contrib = 0.0;
+    if (z < N) {
+        const int Iz = (int)(z >> 7);
+        const int pz = Iz / prm.s;
+        auto owned = [&](int pa, int pb) -> bool {
+            const int64_t k = panels_to_unit(pa, pb, prm.B) - prm.unit_offset;
+            return k >= 0 && k % prm.unit_stride == 0 && k / prm.unit_stride < prm.n_units;
+        };
+        double acc = 0.0;
+        for (int pb = pz; pb < prm.B; ++pb)
+            if (owned(pz, pb)) acc += RowPart[(size_t)pb * N + z];
+        for (int pa = 0; pa <= pz; ++pa)
+            if (owned(pa, pz) && (pa < pz || Iz > pz * prm.s)) acc += ColPart[(size_t)pa * N + z];
+        u[z] = acc;
+        contrib = (double)q[z] * acc;
+    }
+    red[threadIdx.x] = contrib;
+    __syncthreads();
+    for (int off = 128; off > 0; off >>= 1) {
+        if (threadIdx.x < off) red[threadIdx.x] += red[threadIdx.x + off];
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) blockpart[blockIdx.x] = red[0];
+}
+
+__global__ void __launch_bounds__(256)
+sym64_scalar_kernel(const double* __restrict__ blockpart, int64_t nblocks, double* __restrict__ out) {
+    __shared__ double red[256];
+    double acc = 0.0;
+    for (int64_t b = threadIdx.x; b < nblocks; b += 256) acc += blockpart[b];
+    red[threadIdx.x] = acc;
+    __syncthreads();
+    for (int off = 128; off > 0; off >>= 1) {
+        if (threadIdx.x < off) red[threadIdx.x] += red[threadIdx.x + off];
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) out[0] = red[0];
+}
+
+template <typename Q>
+__global__ void sym64_qpack_kernel(const Q* __restrict__ q, int64_t N, double* __restrict__ qT) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < N) qT[i] = (double)q[i];
+}
+
+struct Sym64Plan {
+    int64_t N, finish_blocks;
+    int T, B, s, units_total, n_units, np;
+    size_t off_q, off_row, off_col, off_block, total;
+};
+
+int make_plan64(int n, int unit_offset, int unit_stride, Sym64Plan* p) {
+    if (n < TNK_SYM64_MIN_LATENT || n > TNK_SYM64_MAX_LATENT || unit_stride < 1 || unit_offset < 0) return 1;
+    p->N = (int64_t)1 << n;
+    p->T = (int)(p->N / kTile);
+    int B = p->T < 128 ? p->T : 128;
+    // both slot arrays are B x N doubles: keep them within 16 GB (n = 23: 64 panels, n = 24: 32)
+    while (B > 1 && 2.0 * (double)B * (double)p->N * 8.0 > 16.0 * 1073741824.0) B /= 2;
+    p->B = B;
+    p->s = p->T / B;
+    p->units_total = B * (B + 1) / 2;
+    p->n_units = unit_offset < p->units_total ? (p->units_total - unit_offset + unit_stride - 1) / unit_stride : 0;
+    p->np = ((n + 3) / 4) * 4;
+    p->finish_blocks = (p->N + 255) / 256;
+    size_t off = 0;
+    auto take = [&](size_t bytes) { const size_t at = off; off += (bytes + 255) / 256 * 256; return at; };
+    p->off_q = take((size_t)p->N * sizeof(double));
+    p->off_row = take((size_t)B * p->N * sizeof(double));
+    p->off_col = take((size_t)B * p->N * sizeof(double));
+    p->off_block = take((size_t)(p->finish_blocks + 1) * sizeof(double));
+    p->total = off;
+    return 0;
+}
+
+template <int NP>
+int launch64(const Sym64Params& prm, int n_units, const double* ST, const double* Cst, const double* qT,
+             double* RowPart, double* ColPart, cudaStream_t st) {
+    using SM = Smem64<NP>;
+    auto kern = sym64_kernel<NP>;
+    TNK_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SM::total));
+    kern<<<(unsigned)n_units, kThreads, SM::total, st>>>(prm, ST, Cst, qT, RowPart, ColPart);
+    TNK_CUDA_OK(cudaGetLastError());
+    return 0;
+}
+
+}  // namespace
+
+extern "C" size_t tnk_ksd_sym64_workspace_bytes(int n_latent, int unit_offset, int unit_stride) {
+    Sym64Plan p;
+    if (make_plan64(n_latent, unit_offset, unit_stride, &p)) return 0;
+    return p.total;
+}
+
+extern "C" int tnk_ksd_sym64_units(int n_latent) {
+    Sym64Plan p;
+    if (make_plan64(n_latent, 0, 1, &p)) return 0;
+    return p.units_total;
+}
+
+extern "C" int tnk_ksd_sym64(int n_latent, double length_scale, const void* q, int q_dtype,
+                             const double* ST, const double* Cst, int unit_offset, int unit_stride,
+                             double* u_partial, double* ksd_part,
+                             void* workspace, size_t workspace_bytes, int* n_launch, void* stream) {
+    Sym64Plan p;
+    TNK_REQUIRE(make_plan64(n_latent, unit_offset, unit_stride, &p) == 0,
+                "tnk_ksd_sym64: bad arguments n=%d (supported %d..%d) unit_offset=%d unit_stride=%d", n_latent,
+                TNK_SYM64_MIN_LATENT, TNK_SYM64_MAX_LATENT, unit_offset, unit_stride);
+    TNK_REQUIRE(q && ST && Cst && u_partial && ksd_part && workspace, "tnk_ksd_sym64: NULL pointer argument");
+    TNK_REQUIRE(q_dtype == 0 || q_dtype == 1, "tnk_ksd_sym64: q_dtype must be 0 (double) or 1 (float)");
+    TNK_REQUIRE(workspace_bytes >= p.total, "tnk_ksd_sym64: workspace %zu < required %zu", workspace_bytes, p.total);
+    TNK_REQUIRE(((uintptr_t)workspace & 255) == 0, "tnk_ksd_sym64: workspace must be 256-byte aligned");
+    TNK_REQUIRE((double)n_latent * length_scale != 0.0, "tnk_ksd_sym64: num_vars*length_scale must be non-zero");
+    cudaStream_t st = (cudaStream_t)stream;
+    const int n = n_latent;
+    unsigned char* ws = (unsigned char*)workspace;
+    double* qT = (double*)(ws + p.off_q);
+    double* RowPart = (double*)(ws + p.off_row);
+    double* ColPart = (double*)(ws + p.off_col);
+    double* blockpart = (double*)(ws + p.off_block);
+    int launches = 0;
+
+    Sym64Params prm;
+    prm.n = n; prm.T = p.T; prm.B = p.B; prm.s = p.s;
+    prm.unit_offset = unit_offset; prm.unit_stride = unit_stride; prm.n_units = p.n_units;
+    prm.a = exp(-1.0 / ((double)n * length_scale));
+    prm.gamma = prm.a - 1.0 / prm.a;
+    for (int h = 0; h < 32; ++h) prm.wl[h] = (h <= n) ? exp(-(double)h / ((double)n * length_scale)) : 0.0;
+
+    const unsigned qblocks = (unsigned)((p.N + 255) / 256);
+    if (q_dtype == 0) sym64_qpack_kernel<double><<<qblocks, 256, 0, st>>>((const double*)q, p.N, qT);
+    else sym64_qpack_kernel<float><<<qblocks, 256, 0, st>>>((const float*)q, p.N, qT);
+    TNK_CUDA_OK(cudaGetLastError());
+    ++launches;
+
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    tnk_timing_events_get(&ev0, &ev1);
+    if (ev0) TNK_CUDA_OK(cudaEventRecord(ev0, st));
+    if (p.n_units > 0) {
+        int rc = 0;
+        switch (p.np) {
+            case 8:  rc = launch64<8>(prm, p.n_units, ST, Cst, qT, RowPart, ColPart, st); break;
+            case 12: rc = launch64<12>(prm, p.n_units, ST, Cst, qT, RowPart, ColPart, st); break;
+            case 16: rc = launch64<16>(prm, p.n_units, ST, Cst, qT, RowPart, ColPart, st); break;
+            case 20: rc = launch64<20>(prm, p.n_units, ST, Cst, qT, RowPart, ColPart, st); break;
+            case 24: rc = launch64<24>(prm, p.n_units, ST, Cst, qT, RowPart, ColPart, st); break;
+            default: tnk_set_error("tnk_ksd_sym64: no kernel instance for padded length %d", p.np); return 2;
+        }
+        if (rc) return rc;
+        ++launches;
+    }
+    if (ev1) TNK_CUDA_OK(cudaEventRecord(ev1, st));
+
+    if (q_dtype == 0)
+        sym64_finish_kernel<double><<<(unsigned)p.finish_blocks, 256, 0, st>>>(prm, RowPart, ColPart, (const double*)q, u_partial, blockpart);
+    else
+        sym64_finish_kernel<float><<<(unsigned)p.finish_blocks, 256, 0, st>>>(prm, RowPart, ColPart, (const float*)q, u_partial, blockpart);
+    TNK_CUDA_OK(cudaGetLastError());
+    sym64_scalar_kernel<<<1, 256, 0, st>>>(blockpart, p.finish_blocks, ksd_part);
+    TNK_CUDA_OK(cudaGetLastError());
+    launches += 2;
+    if (n_launch) *n_launch = launches;
+    return 0;
+}

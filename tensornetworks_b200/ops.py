@@ -184,6 +184,37 @@ class SteinTables:
             launch_counter["kernels"] += launched.value
         return u, part
 
+    def ksd_sym64(self, q, unit_offset=0, unit_stride=1):
+        """Symmetric fp64 evaluation (tnk_ksd_sym64): every unordered pair of 128-state tiles once, fp64 throughout
+        (the 1e-6 mode), bit-reproducible.  This call owns the work units unit_offset + k*unit_stride; returns
+        (u_partial [N] fp64, part [1] fp64) whose sums over all offsets of one stride are u = K_p q and KSD^2.
+        Needs the fp64 tables (precision "fp64") and 7 <= n <= 24."""
+        if self.dtype != torch.float64:
+            raise ValueError('the symmetric fp64 kernel reads the fp64 tables: build SteinTables with precision "fp64"')
+        if q.device != self.device or q.dim() != 1 or q.numel() != self.N:
+            raise ValueError(f"q must be a 1-D tensor of {self.N} entries on {self.device}")
+        if q.dtype not in (torch.float32, torch.float64):
+            raise ValueError("q must be float32 or float64")
+        q = q.contiguous()
+        lib = _lib.load()
+        with torch.cuda.device(self.device):
+            key = ("sym64", unit_offset, unit_stride)
+            if key not in self._ws:
+                nbytes = lib.tnk_ksd_sym64_workspace_bytes(self.n, unit_offset, unit_stride)
+                if nbytes == 0:
+                    raise RuntimeError(f"tnk_ksd_sym64_workspace_bytes rejected n={self.n}, units ({unit_offset}, {unit_stride})")
+                self._ws[key] = torch.empty(nbytes, dtype=torch.uint8, device=self.device)
+            ws = self._ws[key]
+            u = torch.empty(self.N, dtype=torch.float64, device=self.device)
+            part = torch.empty(1, dtype=torch.float64, device=self.device)
+            launched = ctypes.c_int(0)
+            _lib.check(lib.tnk_ksd_sym64(self.n, self.length_scale, _ptr(q), 0 if q.dtype == torch.float64 else 1,
+                                         _ptr(self.ST), _ptr(self.Cst), unit_offset, unit_stride, _ptr(u), _ptr(part),
+                                         _ptr(ws), ws.numel(), ctypes.byref(launched), _stream_ptr(self.device)),
+                       "tnk_ksd_sym64")
+            launch_counter["kernels"] += launched.value
+        return u, part
+
     def _st64(self):
         """fp64 packed score table [n_pad, np] (bit order) for the mode-product path; the fp64-mode
         tables already hold it, fp32-mode tables build it on first use."""

@@ -102,3 +102,49 @@ def test_dense_vs_modeproduct_n11():
     K2, g2 = orc.ksd_modeproduct(q, S, 11)
     assert np.isclose(K1, K2, rtol=1e-10)
     assert np.max(np.abs(g1 - g2)) <= 1e-10 * np.max(np.abs(g1))
+
+
+# ---- the C mode-product oracle (oracle/ksd_oracle.c:orc_ksd_modeproduct), the checker of the n = 20 / 24 GPU tests
+@pytest.mark.parametrize("n,seed,nh", RANDOM_CASES)
+def test_c_modeproduct_against_reference_loop(golden, n, seed, nh):
+    from oracle import c_oracle
+    tag = f"rnd_n{n}_s{seed}_h{nh}"
+    K, g = c_oracle.ksd_modeproduct(golden[tag + "_q"], golden[tag + "_P"], n)
+    assert np.isclose(K, golden[tag + "_K"], rtol=1e-11)
+    gref = golden[tag + "_g"]
+    assert np.max(np.abs(g - gref)) <= 1e-11 * np.max(np.abs(gref))
+
+
+def test_c_modeproduct_sprinkler_and_length_scales(golden):
+    from oracle import c_oracle
+    P = golden["spr_P"]
+    for name in ("uniform", "ramp"):
+        K, g = c_oracle.ksd_modeproduct(golden[f"spr_q_{name}"], P, 3)
+        assert np.isclose(K, golden[f"spr_K_{name}"], rtol=1e-12)
+        assert np.max(np.abs(g - golden[f"spr_g_{name}"])) <= 1e-12 * np.max(np.abs(golden[f"spr_g_{name}"]))
+    for ls in (0.5, 2.0):
+        K, g = c_oracle.ksd_modeproduct(golden["spr_q_ramp"], P, 3, length_scale=ls)
+        assert np.isclose(K, golden[f"spr_K_ramp_ls{ls}"], rtol=1e-12)
+    K, g = c_oracle.ksd_modeproduct(np.ones(1), np.ones(1), 0)
+    assert K == 0.0 and g[0] == 0.0                     # n = 0: k_p = 0 (stein_utils.py:151-152)
+
+
+@pytest.mark.parametrize("n,threads", [(9, 1), (12, 3), (13, 8), (15, 5)])
+def test_c_modeproduct_vs_numpy_forms_and_literal_rows(n, threads):
+    """Sizes on both sides of the cache-blocking threshold (2^12 states), odd thread counts, dead rows."""
+    from oracle import c_oracle
+    from tensornetworks_b200.flatten import flatten_bn
+    from tensornetworks_b200.synthetic import illconditioned_binary_bn, random_q
+    gen = illconditioned_binary_bn if n % 2 else random_binary_bn
+    bn, lat, obs, x = gen(n, seed=n)
+    P = c_oracle.joint_table(flatten_bn(bn, x, lat))
+    assert np.array_equal(P, orc.joint_table(bn, x, lat))
+    S = orc.score_table(P, n)
+    q = random_q(1 << n, seed=n).numpy()
+    K0, g0 = orc.ksd_dense(q, S, n) if n <= 12 else orc.ksd_modeproduct(q, S, n)
+    K1, g1 = c_oracle.ksd_modeproduct(q, P, n, nthreads=threads)
+    assert np.isclose(K0, K1, rtol=1e-11)
+    assert np.max(np.abs(g0 - g1)) <= 1e-11 * np.max(np.abs(g0))
+    rows = (1 << n) - 5
+    u, _ = c_oracle.ksd_rows(q, S, n, rows, rows + 5)
+    assert np.max(np.abs(2 * u - g1[rows:rows + 5])) <= 1e-11 * np.max(np.abs(g1))
