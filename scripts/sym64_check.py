@@ -1,6 +1,6 @@
 """Symmetric fp64 kernel (tnk_ksd_sym64) against the fp64 all-pairs kernel: errors, unit stripes, reproducibility, times."""
-import sys
-import time
+import os, sys
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
 from tensornetworks_b200 import ops
 from tensornetworks_b200.synthetic import random_binary_bn, random_q

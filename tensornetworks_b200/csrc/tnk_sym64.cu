@@ -86,18 +86,19 @@ __host__ __device__ inline int64_t panels_to_unit(int pa, int pb, int B) {
 template <int NP>
 struct Smem64 {
     static constexpr int DOT = NP / 4;                  // K-steps of the score dot product
+    static constexpr int STAGES = 3;                    // column-tile buffers: computing t, tables of t+1, copy of t+2 in flight
     static constexpr size_t raw_bytes = (size_t)kTile * NP * sizeof(double);
     static constexpr size_t buf_bytes = raw_bytes + 2 * kTile * sizeof(double);      // raw | Cst | q
-    static constexpr size_t off_buf = 0;                                              // [2] buffers
-    static constexpr size_t off_stage = off_buf + 2 * buf_bytes;                      // [32][kStageStride]
-    static constexpr size_t off_rowg = off_stage + (size_t)32 * kStageStride * sizeof(double);   // [24][128]
-    static constexpr size_t off_colA = off_rowg + (size_t)24 * kTile * sizeof(double);           // [4][128]
-    static constexpr size_t off_colB = off_colA + (size_t)4 * kTile * sizeof(double);            // [8][128]
-    static constexpr size_t off_colG = off_colB + (size_t)8 * kTile * sizeof(double);            // [128][2]
-    static constexpr size_t off_rowred = off_colG + (size_t)2 * kTile * sizeof(double);          // [2][128]
-    static constexpr size_t off_wl = off_rowred + (size_t)2 * kTile * sizeof(double);            // [32]
+    static constexpr size_t tab_bytes = (size_t)(4 + 8 + 2) * kTile * sizeof(double); // colA [4][128] | colB [8][128] | colG [128][2]
+    static constexpr size_t stage_bytes = (size_t)32 * kStageStride * sizeof(double); // [32 row groups][kStageStride]
+    static constexpr size_t off_buf = 0;
+    static constexpr size_t off_stage = off_buf + STAGES * buf_bytes;                 // [2] stages
+    static constexpr size_t off_tab = off_stage + 2 * stage_bytes;                    // [2] table sets
+    static constexpr size_t off_rowg = off_tab + 2 * tab_bytes;                       // [24][128]
+    static constexpr size_t off_rowred = off_rowg + (size_t)24 * kTile * sizeof(double);   // [2][128]
+    static constexpr size_t off_wl = off_rowred + (size_t)2 * kTile * sizeof(double);      // [32]
     static constexpr size_t off_bar = off_wl + 32 * sizeof(double);
-    static constexpr size_t total = off_bar + 16;
+    static constexpr size_t total = off_bar + 8 * STAGES;
 };
 
 // physical score component a lane supplies to dot K-step `t` (the same permutation on the A and the B side):
@@ -113,13 +114,9 @@ __global__ void __launch_bounds__(kThreads, 1)
 sym64_kernel(const Sym64Params prm, const double* __restrict__ ST, const double* __restrict__ Cst,
              const double* __restrict__ qT, double* __restrict__ RowPart, double* __restrict__ ColPart) {
     using SM = Smem64<NP>;
-    constexpr int DOT = SM::DOT, PAIRS = DOT / 2;
+    constexpr int DOT = SM::DOT, PAIRS = DOT / 2, STAGES = SM::STAGES;
     extern __shared__ __align__(128) unsigned char smem[];
-    double* stage = reinterpret_cast<double*>(smem + SM::off_stage);
     double* rowg = reinterpret_cast<double*>(smem + SM::off_rowg);
-    double* colA = reinterpret_cast<double*>(smem + SM::off_colA);
-    double* colB = reinterpret_cast<double*>(smem + SM::off_colB);
-    double* colG = reinterpret_cast<double*>(smem + SM::off_colG);
     double* rowred = reinterpret_cast<double*>(smem + SM::off_rowred);
     double* sWl = reinterpret_cast<double*>(smem + SM::off_wl);
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + SM::off_bar);
@@ -134,38 +131,70 @@ sym64_kernel(const Sym64Params prm, const double* __restrict__ ST, const double*
     int pa, pb;
     unit_to_panels(prm.unit_offset + (int)blockIdx.x * prm.unit_stride, prm.B, &pa, &pb);
     const int s = prm.s;
-    const int I_begin = pa * s, J_end = (pb + 1) * s;
+    const int I_begin = pa * s, I_end = I_begin + s, J_end = (pb + 1) * s;
     const bool diag = pa == pb;
     double* rowpart = RowPart + (size_t)pb * N;
     double* colpart = ColPart + (size_t)pa * N;
+    const uint32_t n_tiles = diag ? (uint32_t)(s * (s + 1) / 2) : (uint32_t)(s * s);
 
     if (tid < 32) sWl[tid] = prm.wl[tid];
     if (tid == 0) {
-        mbar_init(&bars[0], 1);
-        mbar_init(&bars[1], 1);
+#pragma unroll
+        for (int b = 0; b < STAGES; ++b) mbar_init(&bars[b], 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncthreads();
 
-    auto issue_tile = [&](int J, int buf) {          // one thread: three bulk copies on the buffer's barrier
+    // the CTA's tile sequence: row tiles of panel pa in order, each sweeping the column tiles of panel pb (J >= I on the diagonal)
+    auto advance = [&](int& I, int& J) {
+        if (++J == J_end) { ++I; J = diag ? I : pb * s; }
+    };
+    auto issue_tile = [&](int J, uint32_t t) {      // one thread: three bulk copies on the buffer's barrier
+        const int buf = (int)(t % STAGES);
         unsigned char* dst = smem + SM::off_buf + (size_t)buf * SM::buf_bytes;
         mbar_expect_tx(&bars[buf], (uint32_t)SM::buf_bytes);
         bulk_g2s(dst, ST + (size_t)J * kTile * NP, (uint32_t)SM::raw_bytes, &bars[buf]);
         bulk_g2s(dst + SM::raw_bytes, Cst + (size_t)J * kTile, kTile * sizeof(double), &bars[buf]);
         bulk_g2s(dst + SM::raw_bytes + kTile * sizeof(double), qT + (size_t)J * kTile, kTile * sizeof(double), &bars[buf]);
     };
-
-    // thread constants of the Hamming weight: bits 1,2 of i^j, and the e-dependent bit 0
-    const double wt = (__popc(((r >> 1) & 3) ^ k4) == 0) ? 1.0 : (__popc(((r >> 1) & 3) ^ k4) == 1 ? av : av * av);
-    const double we0 = (r & 1) ? av : 1.0, we1 = (r & 1) ? 1.0 : av;     // a^((r&1)^e)
-    const double w1 = av, w2 = av * av;
-
-    uint32_t t_iter = 0;                             // tiles issued so far by this CTA (buffer = t&1, parity = (t>>1)&1)
-    int pend_J = -1;                                 // column tile whose stage still has to be flushed
-    bool pend_first = false;
-
-    auto flush_stage = [&](int J, bool first) {      // threads 0..127: fixed-order sum of the 32 row groups, then global
+    // per-tile column tables of tile (I, J) = sequence number t:  colA[wr][c] = C(c) + sum_{p>=7} b_p(I) g_p(c) + bits 5,6 of
+    // the row block;  colB[r][c] = sum_{p<3} b_p(r) g_p(c);  colG[c][0..1] = g_3(c), g_4(c)
+    auto build_tables = [&](int I, int J, uint32_t t) {
+        const int buf = (int)(t % STAGES);
+        mbar_wait(&bars[buf], (t / STAGES) & 1);
+        const unsigned char* bufp = smem + SM::off_buf + (size_t)buf * SM::buf_bytes;
+        const double* raw = reinterpret_cast<const double*>(bufp);
+        const double* cC = reinterpret_cast<const double*>(bufp + SM::raw_bytes);
+        double* colA = reinterpret_cast<double*>(smem + SM::off_tab + (size_t)(t & 1) * SM::tab_bytes);
+        double* colB = colA + 4 * kTile;
+        double* colG = colB + 8 * kTile;
+        const int c = tid & (kTile - 1), half = tid >> 7;
+        const int64_t j = (int64_t)J * kTile + c;
+        const double* sc = raw + c * NP;
+        auto gcol = [&](int p) -> double {
+            const double v = gam * (1.0 - sc[p]);
+            return ((j >> p) & 1) ? -v : v;
+        };
+        if (half == 0) {
+            double e = cC[c];
+            for (uint32_t x = (uint32_t)I; x; x &= x - 1) e += gcol(7 + (__ffs(x) - 1));
+            const double c5 = gcol(5), c6 = gcol(6);
+            colA[0 * kTile + c] = e;
+            colA[1 * kTile + c] = e + c5;
+            colA[2 * kTile + c] = e + c6;
+            colA[3 * kTile + c] = (e + c5) + c6;
+        } else {
+            const double c0 = gcol(0), c1 = gcol(1), c2 = gcol(2);
+#pragma unroll
+            for (int rr = 0; rr < 8; ++rr)
+                colB[rr * kTile + c] = ((rr & 1) ? c0 : 0.0) + ((rr & 2) ? c1 : 0.0) + ((rr & 4) ? c2 : 0.0);
+            colG[2 * c] = gcol(3);
+            colG[2 * c + 1] = gcol(4);
+        }
+    };
+    auto flush_stage = [&](uint32_t t, int J, bool first) {   // threads 0..127: fixed-order sum of the 32 row groups, then global
         if (tid < kTile) {
+            const double* stage = reinterpret_cast<const double*>(smem + SM::off_stage + (size_t)(t & 1) * SM::stage_bytes);
             double acc = 0.0;
 #pragma unroll 8
             for (int g = 0; g < 32; ++g) acc += stage[g * kStageStride + tid];
@@ -174,192 +203,193 @@ sym64_kernel(const Sym64Params prm, const double* __restrict__ ST, const double*
         }
     };
 
-    for (int I = I_begin; I < I_begin + s; ++I) {
-        const int J_begin = diag ? I : pb * s;
-        const int64_t i_base = (int64_t)I * kTile + wr * 32 + r;     // + 8a
+    // thread constants of the Hamming weight: bits 1,2 of i^j, and the e-dependent bit 0
+    const int pt = __popc((uint32_t)(((r >> 1) & 3) ^ k4));
+    const double wt = pt == 0 ? 1.0 : (pt == 1 ? av : av * av);
+    const double we0 = (r & 1) ? av : 1.0, we1 = (r & 1) ? 1.0 : av;     // a^((r&1)^e)
+    const double w1 = av, w2 = av * av;
 
-        __syncthreads();                             // previous row tile fully consumed (rowg, stage, buffers)
-        if (pend_J >= 0) { flush_stage(pend_J, pend_first); pend_J = -1; }
-        if (tid == 0) issue_tile(J_begin, (int)(t_iter & 1));
+    // ---- prologue: copies of tiles 0 and 1 in flight, tables of tile 0
+    int I = I_begin, J = diag ? I_begin : pb * s;     // tile t
+    int I1 = I, J1 = J;                               // tile t+1
+    advance(I1, J1);
+    if (tid == 0) {
+        issue_tile(J, 0);
+        if (n_tiles > 1) issue_tile(J1, 1);
+    }
+    build_tables(I, J, 0);
 
-        // ---- row operands of tile I: A fragments, per-row constants, shared table of g_p(i) for p >= 7
-        double Af[DOT + 1][4];
-        double qi[4], g0[4], g5[4], g6[4], rbase[4];
-#pragma unroll
-        for (int a = 0; a < 4; ++a) {
-            const int64_t i = i_base + 8 * a;
-            const double* si = ST + i * NP;
-#pragma unroll
-            for (int m = 0; m < PAIRS; ++m) {
-                const double2 v = *reinterpret_cast<const double2*>(si + 8 * m + 2 * k4);
-                Af[2 * m][a] = v.x;
-                Af[2 * m + 1][a] = v.y;
-            }
-            if (DOT & 1) Af[DOT - 1][a] = si[NP - 4 + k4];
-            auto grow = [&](int p) -> double {       // g_p(i)
-                const double v = gam * (1.0 - si[p]);
-                return ((i >> p) & 1) ? -v : v;
-            };
-            // K-step DOT: [g_3(i), g_4(i), b_3(i), b_4(i)] . [b_3(j), b_4(j), g_3(j), g_4(j)]
-            Af[DOT][a] = k4 == 0 ? grow(3) : k4 == 1 ? grow(4) : k4 == 2 ? (double)(a & 1) : (double)(a >> 1);
-            qi[a] = qT[i];
-            g0[a] = grow(0);
-            g5[a] = grow(5);
-            g6[a] = grow(6);
-            // C(i) + column bits 1,2 (thread constants) + column bit 6 (warp constant)
-            rbase[a] = Cst[i] + ((k4 & 1) ? grow(1) : 0.0) + ((k4 & 2) ? grow(2) : 0.0) + (wc ? g6[a] : 0.0);
-        }
-        for (int item = tid; item < kTile * (n - 7); item += kThreads) {
-            const int row = item & (kTile - 1), p = 7 + (item >> 7);
-            const int64_t i = (int64_t)I * kTile + row;
-            const double v = gam * (1.0 - ST[i * NP + p]);
-            rowg[(p - 7) * kTile + row] = ((i >> p) & 1) ? -v : v;
-        }
-        double rsum[4] = {0.0, 0.0, 0.0, 0.0};
+    double Af[DOT + 1][4];
+    double qi[4], g0[4], g5[4], rbase[4];
+    double rsum[4] = {0.0, 0.0, 0.0, 0.0};
+    int I_loaded = -1;
+    int pend_J = -1;                                 // column tile whose stage still has to be flushed
+    bool pend_first = false;
 
-        for (int J = J_begin; J < J_end; ++J, ++t_iter) {
-            const int buf = (int)(t_iter & 1);
-            const unsigned char* bufp = smem + SM::off_buf + (size_t)buf * SM::buf_bytes;
-            const double* raw = reinterpret_cast<const double*>(bufp);
-            const double* cC = reinterpret_cast<const double*>(bufp + SM::raw_bytes);
-            const double* cq = cC + kTile;
-            const bool mirrored = J != I;
+    for (uint32_t t = 0; t < n_tiles; ++t) {
+        __syncthreads();      // S_t: tile t-1 fully consumed; stage (t-1)&1 complete; tables of t visible; buffer (t+2)%3 free
+        if (pend_J >= 0) { flush_stage(t - 1, pend_J, pend_first); pend_J = -1; }
+        int I2 = I1, J2 = J1;                         // tile t+2
+        advance(I2, J2);
+        if (tid == 0 && t + 2 < n_tiles) issue_tile(J2, t + 2);
 
-            __syncthreads();      // (A) tile t-1 fully consumed: tables, stage (complete), buffer buf^1 free; rowg visible
-            if (pend_J >= 0) { flush_stage(pend_J, pend_first); pend_J = -1; }
-            if (tid == 0 && J + 1 < J_end) issue_tile(J + 1, buf ^ 1);
-            mbar_wait(&bars[buf], (t_iter >> 1) & 1);
-
-            // ---- per-tile column tables: colA[wr][c] = C(c) + sum_{p>=7} b_p(I) g_p(c) + bits 5,6 of the row block;
-            //      colB[r][c] = sum_{p<3} b_p(r) g_p(c);  colG[c][0..1] = g_3(c), g_4(c)
-            {
-                const int c = tid & (kTile - 1), half = tid >> 7;
-                const int64_t j = (int64_t)J * kTile + c;
-                const double* sc = raw + c * NP;
-                auto gcol = [&](int p) -> double {
-                    const double v = gam * (1.0 - sc[p]);
-                    return ((j >> p) & 1) ? -v : v;
-                };
-                if (half == 0) {
-                    double e = cC[c];
-                    for (uint32_t x = (uint32_t)I; x; x &= x - 1) e += gcol(7 + (__ffs(x) - 1));
-                    const double c5 = gcol(5), c6 = gcol(6);
-                    colA[0 * kTile + c] = e;
-                    colA[1 * kTile + c] = e + c5;
-                    colA[2 * kTile + c] = e + c6;
-                    colA[3 * kTile + c] = (e + c5) + c6;
-                } else {
-                    const double c0 = gcol(0), c1 = gcol(1), c2 = gcol(2);
-#pragma unroll
-                    for (int rr = 0; rr < 8; ++rr)
-                        colB[rr * kTile + c] = ((rr & 1) ? c0 : 0.0) + ((rr & 2) ? c1 : 0.0) + ((rr & 4) ? c2 : 0.0);
-                    colG[2 * c] = gcol(3);
-                    colG[2 * c + 1] = gcol(4);
-                }
-            }
-            // row side of the tile: rbase + sum_{p>=7} g_p(i) b_p(J)
-            double trow[4];
-#pragma unroll
-            for (int a = 0; a < 4; ++a) trow[a] = rbase[a];
-            for (uint32_t x = (uint32_t)J; x; x &= x - 1) {
-                const double* gp = rowg + (__ffs(x) - 1) * kTile + wr * 32 + r;
-#pragma unroll
-                for (int a = 0; a < 4; ++a) trow[a] += gp[8 * a];
-            }
-            const int hh = __popc((uint32_t)(I ^ J));
-            __syncthreads();      // (B) tables built
-
-#pragma unroll 1
-            for (int cbi = 0; cbi < 2; ++cbi) {
-                const int cb = 2 * wc + cbi;                           // 32-column block of the tile
-                const double wb = sWl[hh + __popc((uint32_t)(wr ^ cb))] * wt;
-                double er[4][2];                                       // row part of the seed
+        if (I != I_loaded) {
+            // ---- row tile switch: store the finished row sums, then load the row operands of tile I
+            if (I_loaded >= 0) {
 #pragma unroll
                 for (int a = 0; a < 4; ++a) {
-                    er[a][0] = cbi ? trow[a] + g5[a] : trow[a];
-                    er[a][1] = er[a][0] + g0[a];
+                    double v = rsum[a];
+                    v += __shfl_xor_sync(0xffffffffu, v, 1);
+                    v += __shfl_xor_sync(0xffffffffu, v, 2);
+                    if (k4 == 0) rowred[wc * kTile + wr * 32 + 8 * a + r] = v;
+                    rsum[a] = 0.0;
                 }
-                double racc[4] = {0.0, 0.0, 0.0, 0.0};
-#pragma unroll
-                for (int hb = 0; hb < 2; ++hb) {                       // batch: 16 columns (b = 2hb, 2hb+1)
-                    double acc[4][2][2];
-                    double qe[2][2];
-                    double Bf[DOT + 1][2];
-#pragma unroll
-                    for (int bb = 0; bb < 2; ++bb) {
-                        const int b = 2 * hb + bb;
-                        const int cfrag = cb * 32 + 8 * b + r;         // column this lane supplies to the B fragment
-                        const double* sc = raw + cfrag * NP;
-#pragma unroll
-                        for (int m = 0; m < PAIRS; ++m) {
-                            const double2 v = *reinterpret_cast<const double2*>(sc + 8 * m + 2 * k4);
-                            Bf[2 * m][bb] = v.x;
-                            Bf[2 * m + 1][bb] = v.y;
-                        }
-                        if (DOT & 1) Bf[DOT - 1][bb] = sc[NP - 4 + k4];
-                        const double gsel = colG[2 * cfrag + (k4 & 1)];
-                        Bf[DOT][bb] = k4 == 0 ? (double)(b & 1) : k4 == 1 ? (double)(b >> 1) : gsel;
-                        const int cacc = cb * 32 + 8 * b + 2 * k4;     // first of the two columns of the accumulator
-                        const double2 ea = *reinterpret_cast<const double2*>(colA + wr * kTile + cacc);
-                        const double2 eb = *reinterpret_cast<const double2*>(colB + r * kTile + cacc);
-                        const double2 qv = *reinterpret_cast<const double2*>(cq + cacc);
-                        const double ec0 = ea.x + eb.x, ec1 = ea.y + eb.y;
-                        qe[bb][0] = qv.x * we0;
-                        qe[bb][1] = qv.y * we1;
-#pragma unroll
-                        for (int a = 0; a < 4; ++a) {
-                            acc[a][bb][0] = er[a][0] + ec0;
-                            acc[a][bb][1] = er[a][1] + ec1;
-                        }
-                    }
-#pragma unroll
-                    for (int t = 0; t <= DOT; ++t)
-#pragma unroll
-                        for (int a = 0; a < 4; ++a)
-#pragma unroll
-                            for (int bb = 0; bb < 2; ++bb) dmma(acc[a][bb][0], acc[a][bb][1], Af[t][a], Bf[t][bb]);
-                    double cs[2][2] = {{0.0, 0.0}, {0.0, 0.0}};
-#pragma unroll
-                    for (int a = 0; a < 4; ++a)
-#pragma unroll
-                        for (int bb = 0; bb < 2; ++bb) {
-                            const int x = a ^ (2 * hb + bb);           // bits 3,4 of i^j
-                            const int pc = (x & 1) + (x >> 1);
-#pragma unroll
-                            for (int e = 0; e < 2; ++e) {
-                                const double v = pc == 0 ? acc[a][bb][e] : acc[a][bb][e] * (pc == 1 ? w1 : w2);
-                                racc[a] = fma(v, qe[bb][e], racc[a]);
-                                cs[bb][e] = fma(v, qi[a], cs[bb][e]);
-                            }
-                        }
-                    if (mirrored) {
-#pragma unroll
-                        for (int bb = 0; bb < 2; ++bb) {
-                            const int cacc = cb * 32 + 8 * (2 * hb + bb) + 2 * k4;
-                            *reinterpret_cast<double2*>(stage + (wr * 8 + r) * kStageStride + cacc) =
-                                make_double2(cs[bb][0] * (wb * we0), cs[bb][1] * (wb * we1));
-                        }
-                    }
-                }
-#pragma unroll
-                for (int a = 0; a < 4; ++a) rsum[a] = fma(wb, racc[a], rsum[a]);
             }
-            if (mirrored) { pend_J = J; pend_first = (I == I_begin); }   // a column tile is first met by the panel's first row tile
+            const int64_t i_base = (int64_t)I * kTile + wr * 32 + r;     // + 8a
+#pragma unroll
+            for (int a = 0; a < 4; ++a) {
+                const int64_t i = i_base + 8 * a;
+                const double* si = ST + i * NP;
+#pragma unroll
+                for (int m = 0; m < PAIRS; ++m) {
+                    const double2 v = *reinterpret_cast<const double2*>(si + 8 * m + 2 * k4);
+                    Af[2 * m][a] = v.x;
+                    Af[2 * m + 1][a] = v.y;
+                }
+                if (DOT & 1) Af[DOT - 1][a] = si[NP - 4 + k4];
+                auto grow = [&](int p) -> double {       // g_p(i)
+                    const double v = gam * (1.0 - si[p]);
+                    return ((i >> p) & 1) ? -v : v;
+                };
+                // K-step DOT: [g_3(i), g_4(i), b_3(i), b_4(i)] . [b_3(j), b_4(j), g_3(j), g_4(j)]
+                Af[DOT][a] = k4 == 0 ? grow(3) : k4 == 1 ? grow(4) : k4 == 2 ? (double)(a & 1) : (double)(a >> 1);
+                qi[a] = qT[i];
+                g0[a] = grow(0);
+                g5[a] = grow(5);
+                // C(i) + column bits 1,2 (thread constants) + column bit 6 (warp constant)
+                rbase[a] = Cst[i] + ((k4 & 1) ? grow(1) : 0.0) + ((k4 & 2) ? grow(2) : 0.0) + (wc ? grow(6) : 0.0);
+            }
+            for (int item = tid; item < kTile * (n - 7); item += kThreads) {
+                const int row = item & (kTile - 1), p = 7 + (item >> 7);
+                const int64_t i = (int64_t)I * kTile + row;
+                const double v = gam * (1.0 - ST[i * NP + p]);
+                rowg[(p - 7) * kTile + row] = ((i >> p) & 1) ? -v : v;
+            }
+            __syncthreads();
+            if (I_loaded >= 0 && tid < kTile) rowpart[(size_t)I_loaded * kTile + tid] = rowred[tid] + rowred[kTile + tid];
+            I_loaded = I;
         }
 
-        // ---- row sums of tile I over this sweep: 4 lanes share a row, 2 warps share a row block
+        // tables of tile t+1 (its copy was issued one iteration ago), then this warp's part of tile t
+        if (t + 1 < n_tiles) build_tables(I1, J1, t + 1);
+
+        const unsigned char* bufp = smem + SM::off_buf + (size_t)(t % STAGES) * SM::buf_bytes;
+        const double* raw = reinterpret_cast<const double*>(bufp);
+        const double* cq = reinterpret_cast<const double*>(bufp + SM::raw_bytes) + kTile;
+        const double* colA = reinterpret_cast<const double*>(smem + SM::off_tab + (size_t)(t & 1) * SM::tab_bytes);
+        const double* colB = colA + 4 * kTile;
+        const double* colG = colB + 8 * kTile;
+        double* stage = reinterpret_cast<double*>(smem + SM::off_stage + (size_t)(t & 1) * SM::stage_bytes);
+        const bool mirrored = J != I;
+
+        // row side of the seed: rbase + sum_{p>=7} g_p(i) b_p(J); er[a][e] adds column bits 5 (second block) and 0 (e)
+        double er[4][2];
 #pragma unroll
-        for (int a = 0; a < 4; ++a) {
-            double v = rsum[a];
-            v += __shfl_xor_sync(0xffffffffu, v, 1);
-            v += __shfl_xor_sync(0xffffffffu, v, 2);
-            if (k4 == 0) rowred[wc * kTile + wr * 32 + 8 * a + r] = v;
+        for (int a = 0; a < 4; ++a) er[a][0] = rbase[a];
+        for (uint32_t x = (uint32_t)J; x; x &= x - 1) {
+            const double* gp = rowg + (__ffs(x) - 1) * kTile + wr * 32 + r;
+#pragma unroll
+            for (int a = 0; a < 4; ++a) er[a][0] += gp[8 * a];
         }
-        __syncthreads();
-        if (tid < kTile) rowpart[(size_t)I * kTile + tid] = rowred[tid] + rowred[kTile + tid];
+#pragma unroll
+        for (int a = 0; a < 4; ++a) er[a][1] = er[a][0] + g0[a];
+        const int hh = __popc((uint32_t)(I ^ J));
+        const double wb0 = sWl[hh + __popc((uint32_t)(wr ^ (2 * wc)))] * wt;
+        const double wb1 = sWl[hh + __popc((uint32_t)(wr ^ (2 * wc + 1)))] * wt;
+
+        // ---- 8 batches of 8 columns (b8 = 4*cbi + b), software-pipelined: the MMAs of batch b8+1 are issued before the
+        //      epilogue of batch b8, so that one warp alone keeps the fp64 pipe fed
+        double acc[2][4][2];
+        double qe[2][2];
+        double racc[4] = {0.0, 0.0, 0.0, 0.0};
+        auto start_batch = [&](int b8, double (&ac)[4][2], double (&qv2)[2]) {
+            const int cb = 2 * wc + (b8 >> 2), b = b8 & 3;
+            const int cfrag = cb * 32 + 8 * b + r;                     // column this lane supplies to the B fragment
+            const double* sc = raw + cfrag * NP;
+            double Bf[DOT + 1];
+#pragma unroll
+            for (int m = 0; m < PAIRS; ++m) {
+                const double2 v = *reinterpret_cast<const double2*>(sc + 8 * m + 2 * k4);
+                Bf[2 * m] = v.x;
+                Bf[2 * m + 1] = v.y;
+            }
+            if (DOT & 1) Bf[DOT - 1] = sc[NP - 4 + k4];
+            const double gsel = colG[2 * cfrag + (k4 & 1)];
+            Bf[DOT] = k4 == 0 ? (double)(b & 1) : k4 == 1 ? (double)(b >> 1) : gsel;
+            const int cacc = cb * 32 + 8 * b + 2 * k4;                 // first of the two columns of the accumulator
+            const double2 ea = *reinterpret_cast<const double2*>(colA + wr * kTile + cacc);
+            const double2 eb = *reinterpret_cast<const double2*>(colB + r * kTile + cacc);
+            const double2 qv = *reinterpret_cast<const double2*>(cq + cacc);
+            const double ec0 = ea.x + eb.x, ec1 = ea.y + eb.y;
+            qv2[0] = qv.x * we0;
+            qv2[1] = qv.y * we1;
+#pragma unroll
+            for (int a = 0; a < 4; ++a) {
+                ac[a][0] = er[a][0] + ec0;
+                ac[a][1] = er[a][1] + ec1;
+            }
+#pragma unroll
+            for (int tt = 0; tt <= DOT; ++tt)
+#pragma unroll
+                for (int a = 0; a < 4; ++a) dmma(ac[a][0], ac[a][1], Af[tt][a], Bf[tt]);
+        };
+        start_batch(0, acc[0], qe[0]);
+#pragma unroll
+        for (int b8 = 0; b8 < 8; ++b8) {
+            const int cur = b8 & 1, b = b8 & 3;
+            if (b8 == 3) {                                             // the next batch opens the second 32-column block
+#pragma unroll
+                for (int a = 0; a < 4; ++a) { er[a][0] += g5[a]; er[a][1] += g5[a]; }
+            }
+            if (b8 + 1 < 8) start_batch(b8 + 1, acc[cur ^ 1], qe[cur ^ 1]);
+            double cs0 = 0.0, cs1 = 0.0;
+#pragma unroll
+            for (int a = 0; a < 4; ++a) {
+                const int x = a ^ b;                                   // bits 3,4 of i^j
+                const int pc = (x & 1) + (x >> 1);
+                const double v0 = pc == 0 ? acc[cur][a][0] : acc[cur][a][0] * (pc == 1 ? w1 : w2);
+                const double v1 = pc == 0 ? acc[cur][a][1] : acc[cur][a][1] * (pc == 1 ? w1 : w2);
+                racc[a] = fma(v0, qe[cur][0], racc[a]);
+                racc[a] = fma(v1, qe[cur][1], racc[a]);
+                cs0 = fma(v0, qi[a], cs0);
+                cs1 = fma(v1, qi[a], cs1);
+            }
+            const double wb = (b8 >> 2) ? wb1 : wb0;
+            if (mirrored) {
+                const int cacc = (2 * wc + (b8 >> 2)) * 32 + 8 * b + 2 * k4;
+                *reinterpret_cast<double2*>(stage + (wr * 8 + r) * kStageStride + cacc) =
+                    make_double2(cs0 * (wb * we0), cs1 * (wb * we1));
+            }
+            if (b == 3) {
+#pragma unroll
+                for (int a = 0; a < 4; ++a) { rsum[a] = fma(wb, racc[a], rsum[a]); racc[a] = 0.0; }
+            }
+        }
+        if (mirrored) { pend_J = J; pend_first = (I == I_begin); }   // a column tile is first met by the panel's first row tile
+        I = I1; J = J1; I1 = I2; J1 = J2;
+    }
+
+    // ---- epilogue: the last row tile's sums and the last tile's column sums
+#pragma unroll
+    for (int a = 0; a < 4; ++a) {
+        double v = rsum[a];
+        v += __shfl_xor_sync(0xffffffffu, v, 1);
+        v += __shfl_xor_sync(0xffffffffu, v, 2);
+        if (k4 == 0) rowred[wc * kTile + wr * 32 + 8 * a + r] = v;
     }
     __syncthreads();
-    if (pend_J >= 0) flush_stage(pend_J, pend_first);
+    if (tid < kTile) rowpart[(size_t)I_loaded * kTile + tid] = rowred[tid] + rowred[kTile + tid];
+    if (pend_J >= 0) flush_stage(n_tiles - 1, pend_J, pend_first);
 }
 
 // u[z] = sum of the row-part and column-part slots of the units this launch owned (fixed order); block partials of q.u
