@@ -212,6 +212,40 @@ int tnk_ksd_sym64(int n_latent, double length_scale, const void* q, int q_dtype,
                   double* u_partial, double* ksd_part,
                   void* workspace, size_t workspace_bytes, int* n_launch, void* stream);
 
+/* ---- exchange step of the sharded evaluations: one process per GPU of one NVSwitch box ----
+ * Replaces what a host would otherwise issue after the sharded loop of reference ksd_vi.py:114-131 on every rank:
+ * the sum-all-reduce of the partial u = K_p q vectors and of the partial KSD^2 scalars.  No NCCL: every rank owns an
+ * exchange buffer (send region, recv region, barrier flags) exported as a CUDA IPC handle and mapped by all peers
+ * over NVLink; the all-reduce is barrier -> one reduce-scatter + all-gather kernel (slice g of every rank's send
+ * region summed in rank order by rank g and stored into every rank's recv region) -> barrier, all on `stream`.
+ * All ranks obtain bit-identical sums.
+ *   tnk_comm_create    allocates this rank's buffer on the current device (cudaMalloc: the one allocation the library
+ *                      makes) for vectors of up to max_doubles doubles and returns its IPC handle (64 bytes)
+ *   tnk_comm_connect   all_handles: the world x 64 handle bytes in rank order, all-gathered by the host (any transport)
+ *   tnk_comm_sendbuf   device double* [max_doubles]: the evaluation calls write their partial results here
+ *                      (pass it as u_partial / ksd_part), so nothing is copied before the exchange
+ *   tnk_comm_allreduce_sum   sums the first `count` doubles of all send regions; the result is in tnk_comm_recvbuf
+ *                      and, if out != NULL, copied to `out` (device).  The send region may be rewritten after the call
+ *                      is enqueued (stream order); the recv region is valid until the next all-reduce on this stream. */
+#define TNK_COMM_HANDLE_BYTES 64
+typedef struct tnk_comm tnk_comm;
+int tnk_comm_create(int rank, int world, int64_t max_doubles, tnk_comm** comm, unsigned char* handle_out);
+int tnk_comm_connect(tnk_comm* comm, const unsigned char* all_handles);
+int tnk_comm_destroy(tnk_comm* comm);
+int tnk_comm_rank(const tnk_comm* comm);
+int tnk_comm_world(const tnk_comm* comm);
+double* tnk_comm_sendbuf(tnk_comm* comm);
+double* tnk_comm_recvbuf(tnk_comm* comm);
+int tnk_comm_allreduce_sum(tnk_comm* comm, int64_t count, double* out, int* n_launch, void* stream);
+
+/* tnk_ksd_sym on rank tnk_comm_rank(comm) of tnk_comm_world(comm) (row tiles dealt round-robin) followed by the
+ * exchange: every rank receives the full u = K_p q [N] and KSD^2 [1].  The communicator must have been created with
+ * max_doubles >= 2^n + 1.  workspace: tnk_ksd_sym_workspace_bytes(n, split, rank, world). */
+int tnk_ksd_sym_allreduce(int n_latent, double length_scale, int split, const void* q, int q_dtype,
+                          const void* ST, const void* Cst, int reuse_table, tnk_comm* comm,
+                          double* u, double* ksd,
+                          void* workspace, size_t workspace_bytes, int* n_launch, void* stream);
+
 /* Measurement hook: when both are non-NULL cudaEvent_t handles, every following tnk_ksd_rows,
  * tnk_ksd_sym or tnk_ksd_sym64 call on this host thread records them on its stream immediately before and after the pair kernel
  * (K3) alone, so a benchmark can time the dominant kernel live.  Pass NULL, NULL to switch off. */

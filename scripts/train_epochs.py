@@ -37,7 +37,7 @@ def main():
     t0 = time.perf_counter()
     vi = KSDVariationalInference(bn, lat, obs, {"use_logits": True, "conditioning_dim": 0}, device=dev,
                                  precision=args.precision, compute_device=dev, algorithm=args.algorithm,
-                                 cuda_graph=args.cuda_graph)
+                                 cuda_graph=args.cuda_graph, distributed=world > 1)
     build_s = time.perf_counter() - t0
     t0 = time.perf_counter()
     hist = vi.train(x, num_epochs=1, lr_born_machine=0.05, verbose=False)      # warm-up epoch: tables, workspaces

@@ -16,7 +16,7 @@ REPO_DIR = os.path.dirname(PKG_DIR)
 CSRC = os.path.join(PKG_DIR, "csrc")
 INCLUDE = os.path.join(REPO_DIR, "include")
 LIB_PATH = os.path.join(PKG_DIR, "libtnk_b200.so")
-SOURCES = ["tnk_enum.cu", "tnk_ksd.cu", "tnk_peak.cu", "tnk_modeprod.cu", "tnk_tc.cu", "tnk_born.cu", "tnk_sym64.cu"]
+SOURCES = ["tnk_enum.cu", "tnk_ksd.cu", "tnk_peak.cu", "tnk_modeprod.cu", "tnk_tc.cu", "tnk_born.cu", "tnk_sym64.cu", "tnk_comm.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC", "-I", INCLUDE]
 
@@ -31,7 +31,9 @@ EXPORTS = ["tnk_last_error", "tnk_version", "tnk_bn_joint", "tnk_ksd_layout", "t
            "tnk_ksd_modeproduct_workspace_bytes", "tnk_modeproduct_tables", "tnk_modeproduct_plan_limit", "tnk_ksd_modeproduct", "tnk_tc_plan",
            "tnk_born_blocks", "tnk_born_forward", "tnk_born_backward",
            "tnk_ksd_sym_workspace_bytes", "tnk_ksd_sym",
-           "tnk_ksd_sym64_workspace_bytes", "tnk_ksd_sym64_units", "tnk_ksd_sym64"]
+           "tnk_ksd_sym64_workspace_bytes", "tnk_ksd_sym64_units", "tnk_ksd_sym64",
+           "tnk_comm_create", "tnk_comm_connect", "tnk_comm_destroy", "tnk_comm_rank", "tnk_comm_world",
+           "tnk_comm_sendbuf", "tnk_comm_recvbuf", "tnk_comm_allreduce_sum", "tnk_ksd_sym_allreduce"]
 
 
 def _nvcc():
@@ -118,6 +120,25 @@ def load():
     lib.tnk_ksd_sym64.restype = c_int
     lib.tnk_ksd_sym64.argtypes = [c_int, c_dbl, c_vp, c_int, c_vp, c_vp, c_int, c_int, c_vp, c_vp,
                                   c_vp, c_sz, ctypes.POINTER(c_int), c_vp]
+    lib.tnk_comm_create.restype = c_int
+    lib.tnk_comm_create.argtypes = [c_int, c_int, c_i64, ctypes.POINTER(c_vp), c_vp]
+    lib.tnk_comm_connect.restype = c_int
+    lib.tnk_comm_connect.argtypes = [c_vp, c_vp]
+    lib.tnk_comm_destroy.restype = c_int
+    lib.tnk_comm_destroy.argtypes = [c_vp]
+    lib.tnk_comm_rank.restype = c_int
+    lib.tnk_comm_rank.argtypes = [c_vp]
+    lib.tnk_comm_world.restype = c_int
+    lib.tnk_comm_world.argtypes = [c_vp]
+    lib.tnk_comm_sendbuf.restype = c_vp
+    lib.tnk_comm_sendbuf.argtypes = [c_vp]
+    lib.tnk_comm_recvbuf.restype = c_vp
+    lib.tnk_comm_recvbuf.argtypes = [c_vp]
+    lib.tnk_comm_allreduce_sum.restype = c_int
+    lib.tnk_comm_allreduce_sum.argtypes = [c_vp, c_i64, c_vp, ctypes.POINTER(c_int), c_vp]
+    lib.tnk_ksd_sym_allreduce.restype = c_int
+    lib.tnk_ksd_sym_allreduce.argtypes = [c_int, c_dbl, c_int, c_vp, c_int, c_vp, c_vp, c_int, c_vp, c_vp, c_vp,
+                                          c_vp, c_sz, ctypes.POINTER(c_int), c_vp]
     lib.tnk_ksd_modeproduct_workspace_bytes.restype = c_sz
     lib.tnk_ksd_modeproduct_workspace_bytes.argtypes = [c_int, c_int, c_int, c_int]
     lib.tnk_ksd_modeproduct.restype = c_int

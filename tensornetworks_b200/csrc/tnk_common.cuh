@@ -4,6 +4,7 @@
 #include <stdint.h>
 #include <stdio.h>
 #include <stdarg.h>
+#include <string.h>
 #include "tnk.h"
 
 #if defined(__CUDA_ARCH__) && (__CUDA_ARCH__ < 1000)

@@ -773,3 +773,27 @@ extern "C" int tnk_ksd_sym(int n_latent, double length_scale, int split, const v
     if (n_launch) *n_launch = launches;
     return 0;
 }
+
+// tnk_ksd_sym + exchange over the communicator's peer-mapped buffers (tnk_comm.cu): the partial u and the partial
+// KSD^2 are written straight into the send region, one all-reduce of N + 1 doubles follows on the same stream.
+extern "C" int tnk_ksd_sym_allreduce(int n_latent, double length_scale, int split, const void* q, int q_dtype,
+                                     const void* ST, const void* Cst, int reuse_table, tnk_comm* comm,
+                                     double* u, double* ksd,
+                                     void* workspace, size_t workspace_bytes, int* n_launch, void* stream) {
+    TNK_REQUIRE(comm && u && ksd, "tnk_ksd_sym_allreduce: NULL argument");
+    TNK_REQUIRE(n_latent >= TNK_TC_MIN_LATENT && n_latent <= TNK_TC_MAX_LATENT, "tnk_ksd_sym_allreduce: n=%d outside %d..%d",
+                n_latent, TNK_TC_MIN_LATENT, TNK_TC_MAX_LATENT);
+    const int64_t N = (int64_t)1 << n_latent;
+    double* send = tnk_comm_sendbuf(comm);
+    int l1 = 0, l2 = 0;
+    int rc = tnk_ksd_sym(n_latent, length_scale, split, q, q_dtype, ST, Cst, tnk_comm_rank(comm), tnk_comm_world(comm),
+                         reuse_table, send, send + N, workspace, workspace_bytes, &l1, stream);
+    if (rc) return rc;
+    rc = tnk_comm_allreduce_sum(comm, N + 1, nullptr, &l2, stream);
+    if (rc) return rc;
+    const double* recv = tnk_comm_recvbuf(comm);
+    TNK_CUDA_OK(cudaMemcpyAsync(u, recv, (size_t)N * sizeof(double), cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
+    TNK_CUDA_OK(cudaMemcpyAsync(ksd, recv + N, sizeof(double), cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
+    if (n_launch) *n_launch = l1 + l2;
+    return 0;
+}

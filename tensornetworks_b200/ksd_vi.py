@@ -80,7 +80,8 @@ def posterior_vector(true_posterior, num_latent_vars, device):
 class KSDVariationalInference:
     def __init__(self, bayesian_network, latent_vars_names, observed_vars_names,
                  born_machine_config, base_kernel_length_scale=1.0, device='cpu',
-                 *, precision="fp64", compute_device="cuda", algorithm="pairs", cuda_graph=False):
+                 *, precision="fp64", compute_device="cuda", algorithm="pairs", cuda_graph=False,
+                 distributed=False, group=None):
         self.bn = bayesian_network
         self.latent_vars_names = latent_vars_names
         self.observed_vars_names = observed_vars_names
@@ -100,6 +101,10 @@ class KSDVariationalInference:
         self.precision = precision
         self.compute_device = compute_device
         self.algorithm = algorithm
+        # Sharding the pair space over the ranks of a torch.distributed group is opt-in (every rank must train the same
+        # Born machine on the same evidence): distributed=True uses `group` (default: the WORLD group).
+        self.distributed = bool(distributed) or group is not None
+        self.group = group
         self._exchange = None
         self.tables = None
         self._score_function_cache = ScoreCache()
@@ -121,22 +126,50 @@ class KSDVariationalInference:
 
     def ksd_squared(self, q_probs_all_z):
         """K = sum_ij q_i q_j k_p(z_i,z_j) as a differentiable fp64 scalar (the hot loop)."""
-        return ops.ksd_quadratic_form(q_probs_all_z, self.tables, algorithm=self.algorithm,
-                                      exchange=self._peer_exchange())
+        group, exchange = self._sharding()
+        return ops.ksd_quadratic_form(q_probs_all_z, self.tables, group=group, algorithm=self.algorithm,
+                                      exchange=exchange)
 
-    def _peer_exchange(self):
-        """Under torch.distributed (one rank per GPU of a box) the row-sharded pair evaluation stores
-        its rows straight into every rank's symmetric-memory buffer (ops.PeerExchange); falls back to
-        the NCCL all_gather inside ops when symmetric memory cannot be set up."""
+    def _world(self):
         import torch.distributed as dist
-        if self.algorithm != "pairs" or not (dist.is_available() and dist.is_initialized()) or dist.get_world_size() == 1:
-            return None
+        if not self.distributed:
+            return 1
+        if not (dist.is_available() and dist.is_initialized()):
+            raise RuntimeError("distributed=True needs an initialised torch.distributed process group")
+        return dist.get_world_size(self.group)
+
+    def _sharding(self):
+        """(group, exchange) of the sharded evaluation, or (None, None) on a single process.  The exchange object is
+        ops.PeerComm (tnk_comm of include/tnk.h: our all-reduce kernels over peer-mapped buffers); its constructor is
+        collective and either succeeds on every rank or raises on every rank, and the fallback to the plain
+        NCCL/gloo collective is therefore taken by all ranks together."""
+        import torch.distributed as dist
+        if self._world() == 1:
+            return None, None
+        group = dist.group.WORLD if self.group is None else self.group
         if self._exchange is None:
             try:
-                self._exchange = ops.PeerExchange(self.tables.N, self.tables.device)
-            except Exception:
+                self._exchange = ops.PeerComm(self.tables.N + 1, self.tables.device, group=group)
+            except Exception as exc:
+                print(f"tnk_comm unavailable ({exc}); the exchange goes through torch.distributed collectives")
                 self._exchange = False
-        return self._exchange or None
+        return group, (self._exchange or None)
+
+    def _sync_replicas(self):
+        """Sharded training assumes identical replicas: parameters are broadcast from rank 0 of the group at the start
+        of train(); ksd_squared's inputs are then identical on every rank as long as the optimiser is deterministic."""
+        import torch.distributed as dist
+        if self._world() == 1:
+            return
+        group = dist.group.WORLD if self.group is None else self.group
+        src = dist.get_global_rank(group, 0)
+        backend = dist.get_backend(group)
+        with torch.no_grad():
+            for p in self.born_machine.parameters():
+                buf = p.data if (p.is_cuda or backend != "nccl") else p.data.to(self.tables.device)
+                dist.broadcast(buf, src=src, group=group)
+                if buf is not p.data:
+                    p.data.copy_(buf)
 
     def _graph_supported(self, params, optimizer_type):
         """The epoch can be replayed as CUDA graphs when everything it launches is on one CUDA device and
@@ -144,7 +177,7 @@ class KSDVariationalInference:
         import torch.distributed as dist
         if not (self.cuda_graph and params and optimizer_type == "adam" and self.born_machine.conditioning_dim == 0):
             return False
-        if dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1:
+        if self.distributed and dist.is_available() and dist.is_initialized() and dist.get_world_size(self.group) > 1:
             return False
         return all(p.is_cuda and p.device == self.tables.device for p in params)
 
@@ -214,6 +247,7 @@ class KSDVariationalInference:
             x_condition = x_obs_tensor
 
         self._precompute_all_s_p(x_observation_dict)
+        self._sync_replicas()
 
         params = list(self.born_machine.parameters())
         graphs = None

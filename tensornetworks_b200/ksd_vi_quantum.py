@@ -27,7 +27,7 @@ class KSDVariationalInference:
                  qbm_num_latent_vars, qbm_ansatz_layers=1, qbm_conditioning_dim=0,
                  qbm_pennylane_device_name="default.qubit", qbm_ansatz_type="hardware_efficient",
                  qbm_init_method="small_random", base_kernel_length_scale=1.0, pytorch_device='cpu',
-                 *, precision="fp64", compute_device="cuda", algorithm="pairs"):
+                 *, precision="fp64", compute_device="cuda", algorithm="pairs", group=None):
         self.bn = bayesian_network
         self.latent_vars_names = latent_vars_names
         self.observed_vars_names = observed_vars_names
@@ -44,6 +44,9 @@ class KSDVariationalInference:
         self.base_kernel_func = partial(base_hamming_kernel_torch, num_vars=self.num_latent_vars,
                                         length_scale=base_kernel_length_scale)
         self.precision, self.compute_device, self.algorithm = precision, compute_device, algorithm
+        # opt-in sharding of the pair space over a torch.distributed group whose ranks all train the same circuit
+        # (parameters broadcast from the group's rank 0 at the start of train())
+        self.group = group
         self.tables = None
         self._score_function_cache = ScoreCache()
 
@@ -78,6 +81,15 @@ class KSDVariationalInference:
         self._precompute_all_s_p(x_observation_dict)
 
         params = list(self.born_machine.parameters())
+        if self.group is not None:
+            import torch.distributed as dist
+            src = dist.get_global_rank(self.group, 0)
+            with torch.no_grad():
+                for p in params:
+                    buf = p.data.to(self.tables.device) if dist.get_backend(self.group) == "nccl" and not p.is_cuda else p.data
+                    dist.broadcast(buf, src=src, group=self.group)
+                    if buf is not p.data:
+                        p.data.copy_(buf)
         if optimizer_type == "adam":
             optimizer = optim.Adam(params, lr=lr_born_machine, betas=adam_betas)
         elif optimizer_type == "sgd":
@@ -104,7 +116,7 @@ class KSDVariationalInference:
             if q.shape[0] != self.num_possible_latent_states:
                 raise ValueError("Probabilities from Born machine have unexpected shape")
 
-            K = ops.ksd_quadratic_form(q, self.tables, algorithm=self.algorithm)   # ksd_vi_quantum.py:122-142
+            K = ops.ksd_quadratic_form(q, self.tables, group=self.group, algorithm=self.algorithm)   # ksd_vi_quantum.py:122-142
             loss = torch.sqrt(K.clamp(min=1e-12))                    # :144-145
             if torch.isnan(loss) or torch.isinf(loss):
                 print(f"Warning: NaN or Inf KSD loss: {loss.item()}. Skipping update.")

@@ -143,13 +143,14 @@ class SteinTables:
         return u, part
 
 
-    def ksd_sym(self, q, tile_offset=0, tile_stride=1, split="tf32"):
+    def ksd_sym(self, q, tile_offset=0, tile_stride=1, split="tf32", out=None):
         """Symmetric tensor-core evaluation (tnk_ksd_sym): every unordered pair of 128-state tiles is evaluated
         once and feeds both its row tile and, mirrored, its column tile.  This call owns the row tiles
         tile_offset + k*tile_stride; returns (u_partial [N] fp64, part [1] fp64) whose sums over all offsets of
         one stride are u = K_p q and KSD^2.  Needs the fp32 tables (precision "tc32" or "fp32"), 7 <= n <= 24.
         split: "tf32" = tf32 high parts + bf16 cross terms (errors of the tc32 kernel, ~1e-6), "bf16x2" = two bf16
-        pieces per factor (fewer MMA K-steps, errors ~1e-5)."""
+        pieces per factor (fewer MMA K-steps, errors ~1e-5).
+        out: optional (u [N], part [1]) fp64 device tensors to write into (e.g. views of PeerComm.sendbuf)."""
         if split not in _lib.SYM_SPLIT:
             raise ValueError(f"split must be one of {tuple(_lib.SYM_SPLIT)}")
         code = _lib.SYM_SPLIT[split]
@@ -173,8 +174,8 @@ class SteinTables:
                     raise RuntimeError(f"tnk_ksd_sym_workspace_bytes rejected n={self.n}, tiles ({tile_offset}, {tile_stride})")
                 self._ws[key] = torch.empty(nbytes, dtype=torch.uint8, device=self.device)
             ws = self._ws[key]
-            u = torch.empty(self.N, dtype=torch.float64, device=self.device)
-            part = torch.empty(1, dtype=torch.float64, device=self.device)
+            u, part = out if out is not None else (torch.empty(self.N, dtype=torch.float64, device=self.device),
+                                                   torch.empty(1, dtype=torch.float64, device=self.device))
             launched = ctypes.c_int(0)
             _lib.check(lib.tnk_ksd_sym(self.n, self.length_scale, code, _ptr(q), 0 if q.dtype == torch.float64 else 1,
                                        _ptr(self.ST), _ptr(self.Cst), tile_offset, tile_stride, 1 if reuse else 0,
@@ -184,7 +185,7 @@ class SteinTables:
             launch_counter["kernels"] += launched.value
         return u, part
 
-    def ksd_sym64(self, q, unit_offset=0, unit_stride=1):
+    def ksd_sym64(self, q, unit_offset=0, unit_stride=1, out=None):
         """Symmetric fp64 evaluation (tnk_ksd_sym64): every unordered pair of 128-state tiles once, fp64 throughout
         (the 1e-6 mode), bit-reproducible.  This call owns the work units unit_offset + k*unit_stride; returns
         (u_partial [N] fp64, part [1] fp64) whose sums over all offsets of one stride are u = K_p q and KSD^2.
@@ -205,8 +206,8 @@ class SteinTables:
                     raise RuntimeError(f"tnk_ksd_sym64_workspace_bytes rejected n={self.n}, units ({unit_offset}, {unit_stride})")
                 self._ws[key] = torch.empty(nbytes, dtype=torch.uint8, device=self.device)
             ws = self._ws[key]
-            u = torch.empty(self.N, dtype=torch.float64, device=self.device)
-            part = torch.empty(1, dtype=torch.float64, device=self.device)
+            u, part = out if out is not None else (torch.empty(self.N, dtype=torch.float64, device=self.device),
+                                                   torch.empty(1, dtype=torch.float64, device=self.device))
             launched = ctypes.c_int(0)
             _lib.check(lib.tnk_ksd_sym64(self.n, self.length_scale, _ptr(q), 0 if q.dtype == torch.float64 else 1,
                                          _ptr(self.ST), _ptr(self.Cst), unit_offset, unit_stride, _ptr(u), _ptr(part),
@@ -340,7 +341,6 @@ class PeerExchange:
         self.stride = (self.N + self.world + 31) // 32 * 32            # doubles per buffer, 256-byte multiple
         with torch.cuda.device(device):
             self.local = symm_mem.empty(self.buffers * self.stride, dtype=torch.float64, device=device)
-            self.local.zero_()
             self.handle = symm_mem.rendezvous(self.local, group)
         self.base = [int(p) for p in self.handle.buffer_ptrs]
         self.step = 0
@@ -389,6 +389,92 @@ def ksd_rows_fused(tables, q, exchange):
     return u, K
 
 
+class _DevicePointer:
+    """A raw device allocation as a CUDA array (torch.as_tensor wraps it without copying)."""
+
+    def __init__(self, ptr, count, typestr="<f8"):
+        self.__cuda_array_interface__ = {"shape": (int(count),), "typestr": typestr, "data": (int(ptr), False),
+                                         "version": 2, "strides": None}
+
+
+class PeerComm:
+    """tnk_comm of include/tnk.h: the sum-all-reduce of the sharded evaluations through our own kernels over
+    peer-mapped (CUDA IPC / NVLink) buffers - barrier, one reduce-scatter + all-gather kernel, barrier; no NCCL on
+    the data path.  torch.distributed only carries the 64-byte IPC handles once, at construction (collective over
+    `group`; raises on every rank if any rank fails, so the ranks cannot disagree about the exchange path).
+    sendbuf / recvbuf: fp64 device views [max_doubles] of this rank's send and receive regions."""
+
+    def __init__(self, max_doubles, device, group=None):
+        device = _require_cuda(device)
+        group = dist.group.WORLD if group is None else group
+        self.group, self.device = group, device
+        self.rank, self.world = dist.get_rank(group), dist.get_world_size(group)
+        if self.world > _lib.MAX_PEERS:
+            raise ValueError(f"tnk_comm covers one NVSwitch box (<= {_lib.MAX_PEERS} ranks)")
+        lib = _lib.load()
+        self._comm = ctypes.c_void_p()
+        handle = (ctypes.c_ubyte * 64)()
+        err = None
+        with torch.cuda.device(device):
+            try:
+                _lib.check(lib.tnk_comm_create(self.rank, self.world, int(max_doubles), ctypes.byref(self._comm), handle),
+                           "tnk_comm_create")
+            except RuntimeError as exc:
+                err = str(exc)
+            gathered = [None] * self.world
+            dist.all_gather_object(gathered, None if err else bytes(handle), group=group)
+            if any(h is None for h in gathered):
+                self.close()
+                raise RuntimeError(f"tnk_comm_create failed on some rank ({err or 'a peer'})")
+            try:
+                _lib.check(lib.tnk_comm_connect(self._comm, b"".join(gathered)), "tnk_comm_connect")
+            except RuntimeError as exc:
+                err = str(exc)
+            flags = [None] * self.world
+            dist.all_gather_object(flags, err, group=group)
+            if any(f is not None for f in flags):
+                self.close()
+                raise RuntimeError(f"tnk_comm_connect failed on some rank ({[f for f in flags if f][0]})")
+        self.max_doubles = int(max_doubles)
+        self.sendbuf = torch.as_tensor(_DevicePointer(lib.tnk_comm_sendbuf(self._comm), max_doubles), device=device)
+        self.recvbuf = torch.as_tensor(_DevicePointer(lib.tnk_comm_recvbuf(self._comm), max_doubles), device=device)
+
+    def allreduce_sum(self, count):
+        """Sum of the first `count` doubles of every rank's sendbuf; returns the view recvbuf[:count] (rewritten by
+        the next all-reduce: clone what has to live longer)."""
+        launched = ctypes.c_int(0)
+        with torch.cuda.device(self.device):
+            _lib.check(_lib.load().tnk_comm_allreduce_sum(self._comm, int(count), None, ctypes.byref(launched),
+                                                          _stream_ptr(self.device)), "tnk_comm_allreduce_sum")
+        launch_counter["kernels"] += launched.value
+        return self.recvbuf[:count]
+
+    def close(self):
+        if getattr(self, "_comm", None) is not None and self._comm.value:
+            with torch.cuda.device(self.device):
+                torch.cuda.synchronize(self.device)
+                _lib.load().tnk_comm_destroy(self._comm)
+            self._comm = ctypes.c_void_p()
+            self.sendbuf = self.recvbuf = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def _host_result(t, like):
+    """Device tensor -> CPU tensor of `like`'s dtype through pinned memory (torch's caching host allocator reuses the
+    block), or a device-to-device cast when the caller's tensor lives on a GPU."""
+    if like[1].type == "cuda":
+        return t.to(device=like[1], dtype=like[0])
+    host = torch.empty(t.shape, dtype=like[0], pin_memory=True)
+    host.copy_(t if t.dtype == like[0] else t.to(like[0]), non_blocking=True)
+    torch.cuda.current_stream(t.device).synchronize()
+    return host
+
+
 class _KsdQuadraticForm(torch.autograd.Function):
     """K(q) = q^T K_p q with dK/dq = 2 K_p q, one pass over the pair space for both."""
 
@@ -397,56 +483,74 @@ class _KsdQuadraticForm(torch.autograd.Function):
         q_dev = q.detach()
         if q_dev.dtype not in (torch.float32, torch.float64):
             q_dev = q_dev.to(torch.float64)
-        q_dev = q_dev.to(tables.device)
-        world = dist.get_world_size(group) if (dist.is_available() and dist.is_initialized()) else 1
+        q_dev = q_dev.to(tables.device, non_blocking=True)
+        # sharding is opt-in: an explicit group, or an exchange object that carries one
+        if group is None and exchange is not None:
+            group = exchange.group
+        world = dist.get_world_size(group) if group is not None else 1
         rank = dist.get_rank(group) if world > 1 else 0
+        comm = exchange if isinstance(exchange, PeerComm) and world > 1 else None
+        N = tables.N
         if algorithm == "modeproduct":
             b0, b1 = shard_rows(tables.n, rank, world)      # score components split over the ranks
             u, part = tables.ksd_modeproduct(q_dev, b0, b1)
-            if world > 1:
-                buf = torch.cat([u, part])
-                dist.all_reduce(buf, op=dist.ReduceOp.SUM, group=group)
-                u, part = buf[:-1], buf[-1:].clone()
-        elif algorithm == "pairs_sym":
-            u, part = tables.ksd_sym(q_dev, *sym_tile_stripe(rank, world))
-            if world > 1:
+            if comm is not None:
+                comm.sendbuf[:N].copy_(u)
+                comm.sendbuf[N:N + 1].copy_(part)
+                res = comm.allreduce_sum(N + 1).clone()
+                u, part = res[:N], res[N:]
+            elif world > 1:
                 u, part = combine_partial_sums(u, part, group)
-        elif exchange is not None and world > 1:
+        elif algorithm in ("pairs_sym", "pairs_sym64"):
+            out = (comm.sendbuf[:N], comm.sendbuf[N:N + 1]) if comm is not None else None
+            if algorithm == "pairs_sym":
+                u, part = tables.ksd_sym(q_dev, *sym_tile_stripe(rank, world), out=out)
+            else:
+                u, part = tables.ksd_sym64(q_dev, rank, world, out=out)
+            if comm is not None:
+                res = comm.allreduce_sum(N + 1).clone()     # the recv region is rewritten by the next evaluation
+                u, part = res[:N], res[N:]
+            elif world > 1:
+                u, part = combine_partial_sums(u, part, group)
+        elif isinstance(exchange, PeerExchange) and world > 1:
             u, part = ksd_rows_fused(tables, q_dev, exchange)
             u = u.clone()     # the symmetric buffer is rewritten two evaluations later
         else:
-            r0, r1 = shard_rows(tables.N, rank, world)
+            r0, r1 = shard_rows(N, rank, world)
             u, part = tables.ksd_rows(q_dev, r0, r1)
             if world > 1:
-                u, part = combine_row_shards(u[r0:r1], part, tables.N, rank, world, group)
+                u, part = combine_row_shards(u[r0:r1], part, N, rank, world, group)
         ctx.save_for_backward(u)
         ctx.q_meta = (q.dtype, q.device)
-        return part.reshape(()).to(q.device)
+        return _host_result(part.reshape(()), (torch.float64, q.device))
 
     @staticmethod
     def backward(ctx, grad_out):
         (u,) = ctx.saved_tensors
-        dtype, device = ctx.q_meta
-        grad = (2.0 * grad_out.to(u.device, torch.float64)) * u
-        return grad.to(device=device, dtype=dtype), None, None, None, None
+        scale = grad_out.to(u.device, torch.float64) if grad_out.is_cuda else float(grad_out) * 1.0
+        grad = u * (2.0 * scale)
+        return _host_result(grad, ctx.q_meta), None, None, None, None
 
 
-ALGORITHMS = ("pairs", "pairs_sym", "modeproduct")
+ALGORITHMS = ("pairs", "pairs_sym", "pairs_sym64", "modeproduct")
 
 
 def ksd_quadratic_form(q, tables, group=None, algorithm="pairs", exchange=None):
     """KSD^2 = sum_ij q_i q_j k_p(z_i, z_j) as an fp64 scalar tensor on q's device, differentiable
     w.r.t. q (any float dtype, CPU or CUDA; e.g. PennyLane probabilities).  Drop-in for the double
-    loop of reference ksd_vi.py:110-131 / ksd_vi_quantum.py:122-142.  When torch.distributed is
-    initialised the rows of the pair space are sharded over the ranks of `group`.
+    loop of reference ksd_vi.py:110-131 / ksd_vi_quantum.py:122-142.
     algorithm="pairs" evaluates all 4^n pairs on the fly (the reference's loop, tiled);
     algorithm="pairs_sym" evaluates every unordered pair of 128-state tiles once on the tensor cores and uses
-    k_p(z,z') = k_p(z',z) for the mirrored half (fp32-grade, tables of precision "tc32"; row tiles are dealt
-    round-robin over the ranks and u is sum-all-reduced);
+    k_p(z,z') = k_p(z',z) for the mirrored half (fp32-grade, tables of precision "tc32");
+    algorithm="pairs_sym64" is the same schedule in fp64 (tables of precision "fp64", the 1e-6 mode, bit-reproducible);
     algorithm="modeproduct" returns the same value through the Kronecker factorisation of the
-    Hamming kernel in O(n^2 2^n) (fp64), with the score components sharded over the ranks.
-    exchange: a PeerExchange makes the sharded "pairs" evaluation store its rows straight into every
-    rank's buffer over NVLink (tnk_ksd_rows_peers) instead of calling an NCCL collective."""
+    Hamming kernel in O(n^2 2^n) (fp64).
+    Sharding over several GPUs is OPT-IN: pass `group` (a torch.distributed process group whose ranks all call with
+    the same q - the caller's responsibility, see KSDVariationalInference(distributed=True)) and/or `exchange`:
+    a PeerComm (tnk_comm: our own all-reduce over peer-mapped buffers, every algorithm) or a PeerExchange (rows of
+    the "pairs" evaluation stored straight into every rank's buffer, tnk_ksd_rows_peers).  Without an exchange
+    object the partial results go through one NCCL/gloo collective.  With neither, the whole evaluation runs on
+    this process's GPU even when torch.distributed is initialised."""
     if algorithm not in ALGORITHMS:
         raise ValueError(f"algorithm must be one of {ALGORITHMS}")
     if q.dim() != 1 or q.numel() != tables.N:
