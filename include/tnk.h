@@ -40,6 +40,8 @@ extern "C" {
 #define TNK_MAX_LATENT 30
 #define TNK_MAX_PEERS 8   /* GPUs of one NVSwitch box (tnk_ksd_rows_peers) */
 
+#define TNK_ABI_VERSION 200   /* bumped whenever a signature below changes; tnk_version() returns the built value */
+
 const char* tnk_last_error(void);
 int tnk_version(void);
 

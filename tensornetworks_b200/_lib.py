@@ -48,12 +48,26 @@ def _stale():
     return any(os.path.getmtime(d) > built for d in deps)
 
 
+ABI_VERSION = 200   # tnk_version() of the library these ctypes signatures were written for (bumped with include/tnk.h)
+
+
 def build(force=False, verbose=False):
-    """Compile the CUDA sources for sm_100a and link the shared library (no GPU needed)."""
-    if not force and not _stale():
-        return LIB_PATH
+    """Compile the CUDA sources for sm_100a and link the shared library (no GPU needed).  Serialised across
+    processes with a file lock: under torchrun every rank may find the library stale at the same time."""
+    import fcntl
     obj_dir = os.path.join(PKG_DIR, "build")
     os.makedirs(obj_dir, exist_ok=True)
+    with open(os.path.join(obj_dir, ".lock"), "w") as lock:
+        fcntl.flock(lock, fcntl.LOCK_EX)
+        try:
+            if not force and not _stale():      # another process built it while this one waited
+                return LIB_PATH
+            return _build_locked(obj_dir, verbose)
+        finally:
+            fcntl.flock(lock, fcntl.LOCK_UN)
+
+
+def _build_locked(obj_dir, verbose=False):
 
     def compile_one(src):
         obj = os.path.join(obj_dir, src.replace(".cu", ".o"))
@@ -67,10 +81,12 @@ def build(force=False, verbose=False):
 
     with ThreadPoolExecutor(max_workers=len(SOURCES)) as pool:
         objs = list(pool.map(compile_one, SOURCES))
-    cmd = [_nvcc(), "-shared", "-o", LIB_PATH, *objs, "-lcudart"]
+    tmp = LIB_PATH + ".tmp"
+    cmd = [_nvcc(), "-shared", "-o", tmp, *objs, "-lcudart"]
     res = subprocess.run(cmd, capture_output=True, text=True)
     if res.returncode != 0:
         raise RuntimeError(f"link failed:\n{res.stdout}\n{res.stderr}")
+    os.replace(tmp, LIB_PATH)                  # readers never see a half-written library
     return LIB_PATH
 
 
@@ -88,7 +104,15 @@ def load():
         except Exception as exc:  # no toolchain: refuse loudly, never fall back
             if not os.path.exists(LIB_PATH):
                 raise RuntimeError(f"libtnk_b200.so is missing and could not be built: {exc}") from exc
+            import warnings
+            warnings.warn(f"libtnk_b200.so is older than its sources and could not be rebuilt ({exc}); "
+                          "using the existing library after checking its ABI version")
     lib = ctypes.CDLL(LIB_PATH)
+    missing = [name for name in EXPORTS if not hasattr(lib, name)]
+    lib.tnk_version.restype = ctypes.c_int
+    if missing or lib.tnk_version() != ABI_VERSION:
+        raise RuntimeError(f"libtnk_b200.so does not match include/tnk.h (version {lib.tnk_version()} vs {ABI_VERSION}, "
+                           f"missing symbols {missing}): rebuild it with python -c 'import __graft_entry__ as g; g.build()'")
     c_int, c_i64, c_dbl, c_vp, c_sz = ctypes.c_int, ctypes.c_int64, ctypes.c_double, ctypes.c_void_p, ctypes.c_size_t
     lib.tnk_last_error.restype = ctypes.c_char_p
     lib.tnk_last_error.argtypes = []

@@ -12,7 +12,7 @@ void tnk_set_error(const char* fmt, ...) {
 }
 
 extern "C" const char* tnk_last_error(void) { return g_err; }
-extern "C" int tnk_version(void) { return 100; }
+extern "C" int tnk_version(void) { return TNK_ABI_VERSION; }
 
 extern "C" int tnk_ksd_layout(int n_latent, int precision, int* np, int64_t* n_pad, int* elem) {
     TnkGeom g;
@@ -28,6 +28,8 @@ extern "C" int tnk_ksd_layout(int n_latent, int precision, int* np, int64_t* n_p
 // The network descriptor is tiny and identical for all threads: it is staged in shared
 // memory once per CTA; each thread then walks the nodes in bn.nodes order.
 // ------------------------------------------------------------------------------------
+constexpr int kJointPaSlots = 4096;   // 16 KB of dynamic shared memory for the parent lists
+
 struct BnDesc {
     int32_t kind[TNK_MAX_NODES];
     int32_t arg[TNK_MAX_NODES];
@@ -50,8 +52,13 @@ bn_joint_kernel(int n_latent, int n_hidden, int n_nodes,
     }
     for (int v = threadIdx.x; v <= n_nodes; v += blockDim.x) d.pa_off[v] = pa_off[v];
     __syncthreads();
+    // parent lists: staged in shared memory when they fit (kJointPaSlots entries), else read from global memory
     const int n_pa = d.pa_off[n_nodes];
-    for (int t = threadIdx.x; t < n_pa; t += blockDim.x) s_pa[t] = pa_idx[t];
+    const int32_t* pa = pa_idx;
+    if (n_pa <= kJointPaSlots) {
+        for (int t = threadIdx.x; t < n_pa; t += blockDim.x) s_pa[t] = pa_idx[t];
+        pa = s_pa;
+    }
     __syncthreads();
 
     const int64_t N = (int64_t)1 << n_latent;
@@ -78,7 +85,7 @@ bn_joint_kernel(int n_latent, int n_hidden, int n_nodes,
         for (int v = 0; v < n_nodes; ++v) {
             int cfg = 0;
             for (int t = d.pa_off[v]; t < d.pa_off[v + 1]; ++t)
-                cfg = (cfg << 1) | (int)((assign >> s_pa[t]) & 1u);
+                cfg = (cfg << 1) | (int)((assign >> pa[t]) & 1u);
             const int val = (int)((assign >> v) & 1u);
             prob = __dmul_rn(prob, __ldg(&cpt[2 * ((int64_t)d.cpt_off[v] + cfg) + val]));  // :144
         }
@@ -96,15 +103,9 @@ extern "C" int tnk_bn_joint(int n_latent, int n_hidden, int n_nodes,
     TNK_REQUIRE(n_hidden >= 0 && n_hidden <= 20, "tnk_bn_joint: n_hidden=%d out of range", n_hidden);
     TNK_REQUIRE(n_nodes >= 0 && n_nodes <= TNK_MAX_NODES, "tnk_bn_joint: n_nodes=%d exceeds %d", n_nodes, TNK_MAX_NODES);
     TNK_REQUIRE(P != nullptr, "tnk_bn_joint: P is NULL");
-    int32_t n_pa = 0;
-    if (n_nodes > 0) {
-        TNK_CUDA_OK(cudaMemcpyAsync(&n_pa, pa_off + n_nodes, sizeof(int32_t), cudaMemcpyDeviceToHost, (cudaStream_t)stream));
-        TNK_CUDA_OK(cudaStreamSynchronize((cudaStream_t)stream));
-    }
-    TNK_REQUIRE(n_pa >= 0 && n_pa <= 8192, "tnk_bn_joint: %d parent references exceed the 8192 limit", n_pa);
     const int64_t N = (int64_t)1 << n_latent;
     const unsigned blocks = (unsigned)((N + 255) / 256);
-    bn_joint_kernel<<<blocks, 256, (size_t)(n_pa + 1) * sizeof(int32_t), (cudaStream_t)stream>>>(
+    bn_joint_kernel<<<blocks, 256, (size_t)kJointPaSlots * sizeof(int32_t), (cudaStream_t)stream>>>(
         n_latent, n_hidden, n_nodes, node_kind, node_arg, pa_off, pa_idx, cpt_off, cpt, P);
     TNK_CUDA_OK(cudaGetLastError());
     return 0;

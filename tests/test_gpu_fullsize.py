@@ -50,8 +50,6 @@ def _run(tabs, kind, q, kw):
     elif kind == "sym":
         u, k = tabs.ksd_sym(q, **kw)
     elif kind == "sym64":
-        if not hasattr(tabs, "ksd_sym64"):
-            pytest.skip("ksd_sym64 not built yet")
         u, k = tabs.ksd_sym64(q)
     else:
         u, k = tabs.ksd_modeproduct(q, **kw)

@@ -379,3 +379,18 @@ def test_fused_peer_exchange_world2(ops):
     res = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
     assert res.returncode == 0, res.stdout[-2000:] + res.stderr[-4000:]
     assert '"fused_exchange": "ok"' in res.stdout
+
+
+def test_tnk_comm_world2(ops):
+    """tnk_comm (include/tnk.h) on 2 GPUs of the box: bit-identical to the NCCL all-reduce of the same partial vectors,
+    and the sharded pairs_sym / pairs_sym64 / modeproduct evaluations through it against the single-rank results."""
+    import os, subprocess, sys
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs on one box")
+    repo = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2",
+           "--master-addr", "127.0.0.1", "--master-port", "29533",
+           os.path.join(repo, "scripts", "check_comm.py"), "12"]
+    res = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+    assert res.returncode == 0, res.stdout[-2000:] + res.stderr[-4000:]
+    assert '"tnk_comm": "ok"' in res.stdout
