@@ -314,7 +314,7 @@ def run_ours(args):
         qh.grad = None
         K = ops.ksd_quadratic_form(qh, tables, group=group, exchange=exchange, algorithm=algorithm)   # H2D of q inside
         K.backward()                               # D2H of dK/dq inside
-        return float(K), qh.grad
+        return float(K.detach()), qh.grad
 
     # roofline denominators measured in this run: FMA-chain rate of the ALU kernels' arithmetic type
     probe_prec = "fp64" if args.precision == "fp64" else "fp32"
@@ -731,10 +731,10 @@ def main():
             # the timed CPU baseline: the literal four-term loop on rows of the first and of the last row tile
             half = args.cpu_seconds / 2.0
             first = cpu_sample(n, S, q, half, row_start=0)
-            last = cpu_sample(n, S, q, half, row_start=N - first["rows"])
+            last = cpu_sample(n, S, q, half, row_start=N - first["rows"])      # ends inside the last row tile
             rate = (first["pairs"] + last["pairs"]) / (first["seconds"] + last["seconds"])
             lit_err = max(float(np.max(np.abs(first["u"] - uref[:first["rows"]]))),
-                          float(np.max(np.abs(last["u"] - uref[N - last["rows"]:])))) / uscale
+                          float(np.max(np.abs(last["u"] - uref[last["row_start"]:last["row_start"] + last["rows"]])))) / uscale
             par["oracle_vs_literal_loop_rows_max_rel"] = lit_err
             line["parity"] = par
             line["cpu_baseline"] = {"value": rate, "unit": UNIT, "cores": first["threads"], "kind": "port",

@@ -176,8 +176,13 @@ sym64_kernel(const Sym64Params prm, const double* __restrict__ ST, const double*
             return ((j >> p) & 1) ? -v : v;
         };
         if (half == 0) {
+            // sum over the set bits of I with a fixed trip count: the loads do not wait for the adds
             double e = cC[c];
-            for (uint32_t x = (uint32_t)I; x; x &= x - 1) e += gcol(7 + (__ffs(x) - 1));
+#pragma unroll 4
+            for (int p = 7; p < n; ++p) {
+                const double gp = gcol(p);
+                e += ((I >> (p - 7)) & 1) ? gp : 0.0;
+            }
             const double c5 = gcol(5), c6 = gcol(6);
             colA[0 * kTile + c] = e;
             colA[1 * kTile + c] = e + c5;
@@ -192,14 +197,22 @@ sym64_kernel(const Sym64Params prm, const double* __restrict__ ST, const double*
             colG[2 * c + 1] = gcol(4);
         }
     };
-    auto flush_stage = [&](uint32_t t, int J, bool first) {   // threads 0..127: fixed-order sum of the 32 row groups, then global
-        if (tid < kTile) {
+    // Column sums of a finished tile: warps 4..7 (the table-building work of a tile sits mostly in warps 0..3), two
+    // threads per column, each adding 16 of the 32 row groups as four independent chains; fixed order -> deterministic.
+    auto flush_stage = [&](uint32_t t, int J, bool first) {
+        if (tid >= kTile) {
             const double* stage = reinterpret_cast<const double*>(smem + SM::off_stage + (size_t)(t & 1) * SM::stage_bytes);
-            double acc = 0.0;
-#pragma unroll 8
-            for (int g = 0; g < 32; ++g) acc += stage[g * kStageStride + tid];
-            double* dst = colpart + (size_t)J * kTile + tid;
-            if (first) *dst = acc; else red_add_f64(dst, acc);
+            const int col = (tid - kTile) >> 1, hf = tid & 1;
+            const double* src = stage + (16 * hf) * kStageStride + col;
+            double p4[4] = {0.0, 0.0, 0.0, 0.0};
+#pragma unroll
+            for (int g = 0; g < 16; ++g) p4[g & 3] += src[g * kStageStride];
+            double acc = (p4[0] + p4[1]) + (p4[2] + p4[3]);
+            acc += __shfl_xor_sync(0xffffffffu, acc, 1);
+            if (hf == 0) {
+                double* dst = colpart + (size_t)J * kTile + col;
+                if (first) *dst = acc; else red_add_f64(dst, acc);
+            }
         }
     };
 
@@ -296,10 +309,15 @@ sym64_kernel(const Sym64Params prm, const double* __restrict__ ST, const double*
         double er[4][2];
 #pragma unroll
         for (int a = 0; a < 4; ++a) er[a][0] = rbase[a];
-        for (uint32_t x = (uint32_t)J; x; x &= x - 1) {
-            const double* gp = rowg + (__ffs(x) - 1) * kTile + wr * 32 + r;
+#pragma unroll 2
+        for (int p = 7; p < n; ++p) {
+            const double* gp = rowg + (p - 7) * kTile + wr * 32 + r;
+            const bool on = (J >> (p - 7)) & 1;
 #pragma unroll
-            for (int a = 0; a < 4; ++a) er[a][0] += gp[8 * a];
+            for (int a = 0; a < 4; ++a) {
+                const double v = gp[8 * a];
+                er[a][0] += on ? v : 0.0;
+            }
         }
 #pragma unroll
         for (int a = 0; a < 4; ++a) er[a][1] = er[a][0] + g0[a];
