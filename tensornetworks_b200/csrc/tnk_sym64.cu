@@ -15,7 +15,7 @@
 // constant per thread, warp, block or tile, so the remaining T1/T2 terms and C(i) + C(j) arrive as ONE add per pair
 // (the accumulator seed Erow[a][e] + Ecol[b][e]) and the Hamming weight as one multiply by a^popc(a^b) (a compile-
 // time constant after unrolling) - the rest of the weight is folded into q_j, into the column sums and into one
-// factor per block.  Per executed pair: 4 (NP/4 + 1) DMMA lane-FMAs + 1 DADD + 0.75 DMUL + 2 DFMA.
+// factor per block.  Per executed pair: 4 (NP/4) DMMA lane-FMAs + ~2.75 DADD + 0.75 DMUL + 2 DFMA.
 //
 // Schedule and determinism.  The T = N/128 tiles are grouped into B <= 128 panels of s tiles; a work unit is a
 // panel pair (pa <= pb) handled by one CTA: for every row tile I of pa it sweeps the column tiles J of pb (J >= I on
@@ -95,7 +95,8 @@ struct Smem64 {
     static constexpr size_t off_stage = off_buf + STAGES * buf_bytes;                 // [2] stages
     static constexpr size_t off_tab = off_stage + 2 * stage_bytes;                    // [2] table sets
     static constexpr size_t off_rowg = off_tab + 2 * tab_bytes;                       // [24][128]
-    static constexpr size_t off_rowred = off_rowg + (size_t)24 * kTile * sizeof(double);   // [2][128]
+    static constexpr size_t off_rowc = off_rowg + (size_t)24 * kTile * sizeof(double);     // [4][128]: g_0, g_3, g_4, g_5 of the rows
+    static constexpr size_t off_rowred = off_rowc + (size_t)4 * kTile * sizeof(double);    // [2][128]
     static constexpr size_t off_wl = off_rowred + (size_t)2 * kTile * sizeof(double);      // [32]
     static constexpr size_t off_bar = off_wl + 32 * sizeof(double);
     static constexpr size_t total = off_bar + 8 * STAGES;
@@ -117,6 +118,7 @@ sym64_kernel(const Sym64Params prm, const double* __restrict__ ST, const double*
     constexpr int DOT = SM::DOT, PAIRS = DOT / 2, STAGES = SM::STAGES;
     extern __shared__ __align__(128) unsigned char smem[];
     double* rowg = reinterpret_cast<double*>(smem + SM::off_rowg);
+    double* rowc = reinterpret_cast<double*>(smem + SM::off_rowc);
     double* rowred = reinterpret_cast<double*>(smem + SM::off_rowred);
     double* sWl = reinterpret_cast<double*>(smem + SM::off_wl);
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + SM::off_bar);
@@ -131,7 +133,7 @@ sym64_kernel(const Sym64Params prm, const double* __restrict__ ST, const double*
     int pa, pb;
     unit_to_panels(prm.unit_offset + (int)blockIdx.x * prm.unit_stride, prm.B, &pa, &pb);
     const int s = prm.s;
-    const int I_begin = pa * s, I_end = I_begin + s, J_end = (pb + 1) * s;
+    const int I_begin = pa * s, J_end = (pb + 1) * s;
     const bool diag = pa == pb;
     double* rowpart = RowPart + (size_t)pb * N;
     double* colpart = ColPart + (size_t)pa * N;
@@ -197,12 +199,12 @@ sym64_kernel(const Sym64Params prm, const double* __restrict__ ST, const double*
             colG[2 * c + 1] = gcol(4);
         }
     };
-    // Column sums of a finished tile: warps 4..7 (the table-building work of a tile sits mostly in warps 0..3), two
-    // threads per column, each adding 16 of the 32 row groups as four independent chains; fixed order -> deterministic.
+    // Column sums of a finished tile: two threads per column, each adding 16 of the 32 row groups as four independent
+    // chains; fixed order -> deterministic.
     auto flush_stage = [&](uint32_t t, int J, bool first) {
-        if (tid >= kTile) {
+        {
             const double* stage = reinterpret_cast<const double*>(smem + SM::off_stage + (size_t)(t & 1) * SM::stage_bytes);
-            const int col = (tid - kTile) >> 1, hf = tid & 1;
+            const int col = tid >> 1, hf = tid & 1;
             const double* src = stage + (16 * hf) * kStageStride + col;
             double p4[4] = {0.0, 0.0, 0.0, 0.0};
 #pragma unroll
@@ -232,8 +234,8 @@ sym64_kernel(const Sym64Params prm, const double* __restrict__ ST, const double*
     }
     build_tables(I, J, 0);
 
-    double Af[DOT + 1][4];
-    double qi[4], g0[4], g5[4], rbase[4];
+    double Af[DOT][4];
+    double qi[4], rbase[4];
     double rsum[4] = {0.0, 0.0, 0.0, 0.0};
     int I_loaded = -1;
     int pend_J = -1;                                 // column tile whose stage still has to be flushed
@@ -274,13 +276,15 @@ sym64_kernel(const Sym64Params prm, const double* __restrict__ ST, const double*
                     const double v = gam * (1.0 - si[p]);
                     return ((i >> p) & 1) ? -v : v;
                 };
-                // K-step DOT: [g_3(i), g_4(i), b_3(i), b_4(i)] . [b_3(j), b_4(j), g_3(j), g_4(j)]
-                Af[DOT][a] = k4 == 0 ? grow(3) : k4 == 1 ? grow(4) : k4 == 2 ? (double)(a & 1) : (double)(a >> 1);
                 qi[a] = qT[i];
-                g0[a] = grow(0);
-                g5[a] = grow(5);
                 // C(i) + column bits 1,2 (thread constants) + column bit 6 (warp constant)
                 rbase[a] = Cst[i] + ((k4 & 1) ? grow(1) : 0.0) + ((k4 & 2) ? grow(2) : 0.0) + (wc ? grow(6) : 0.0);
+            }
+            for (int item = tid; item < kTile * 4; item += kThreads) {       // g_0, g_3, g_4, g_5 of every row of the tile
+                const int row = item & (kTile - 1), p = (item >> 7) == 0 ? 0 : 2 + (item >> 7);
+                const int64_t i = (int64_t)I * kTile + row;
+                const double v = gam * (1.0 - ST[i * NP + p]);
+                rowc[(item >> 7) * kTile + row] = ((i >> p) & 1) ? -v : v;
             }
             for (int item = tid; item < kTile * (n - 7); item += kThreads) {
                 const int row = item & (kTile - 1), p = 7 + (item >> 7);
@@ -319,8 +323,9 @@ sym64_kernel(const Sym64Params prm, const double* __restrict__ ST, const double*
                 er[a][0] += on ? v : 0.0;
             }
         }
+        const double* rc = rowc + wr * 32 + r;                            // + k*128 + 8a: g_0, g_3, g_4, g_5 of this thread's rows
 #pragma unroll
-        for (int a = 0; a < 4; ++a) er[a][1] = er[a][0] + g0[a];
+        for (int a = 0; a < 4; ++a) er[a][1] = er[a][0] + rc[8 * a];
         const int hh = __popc((uint32_t)(I ^ J));
         const double wb0 = sWl[hh + __popc((uint32_t)(wr ^ (2 * wc)))] * wt;
         const double wb1 = sWl[hh + __popc((uint32_t)(wr ^ (2 * wc + 1)))] * wt;
@@ -330,11 +335,13 @@ sym64_kernel(const Sym64Params prm, const double* __restrict__ ST, const double*
         double acc[2][4][2];
         double qe[2][2];
         double racc[4] = {0.0, 0.0, 0.0, 0.0};
+        // batch b8: 32-column block cbi = b8 >> 2, 8-column group b = gray(b8 & 3) = 0, 1, 3, 2 - one of the column bits
+        // 3, 4 changes per batch, so the row side of the seed follows with one add per value (g_3 or g_4 of the row)
         auto start_batch = [&](int b8, double (&ac)[4][2], double (&qv2)[2]) {
-            const int cb = 2 * wc + (b8 >> 2), b = b8 & 3;
+            const int cb = 2 * wc + (b8 >> 2), b = (b8 & 3) ^ ((b8 & 3) >> 1);
             const int cfrag = cb * 32 + 8 * b + r;                     // column this lane supplies to the B fragment
             const double* sc = raw + cfrag * NP;
-            double Bf[DOT + 1];
+            double Bf[DOT];
 #pragma unroll
             for (int m = 0; m < PAIRS; ++m) {
                 const double2 v = *reinterpret_cast<const double2*>(sc + 8 * m + 2 * k4);
@@ -342,33 +349,50 @@ sym64_kernel(const Sym64Params prm, const double* __restrict__ ST, const double*
                 Bf[2 * m + 1] = v.y;
             }
             if (DOT & 1) Bf[DOT - 1] = sc[NP - 4 + k4];
-            const double gsel = colG[2 * cfrag + (k4 & 1)];
-            Bf[DOT] = k4 == 0 ? (double)(b & 1) : k4 == 1 ? (double)(b >> 1) : gsel;
             const int cacc = cb * 32 + 8 * b + 2 * k4;                 // first of the two columns of the accumulator
             const double2 ea = *reinterpret_cast<const double2*>(colA + wr * kTile + cacc);
             const double2 eb = *reinterpret_cast<const double2*>(colB + r * kTile + cacc);
             const double2 qv = *reinterpret_cast<const double2*>(cq + cacc);
-            const double ec0 = ea.x + eb.x, ec1 = ea.y + eb.y;
+            const double4 g34 = *reinterpret_cast<const double4*>(colG + 2 * cacc);   // g_3, g_4 of column cacc; of cacc + 1
             qv2[0] = qv.x * we0;
             qv2[1] = qv.y * we1;
+            // row side: column bits 3,4 (b) and 5 (cbi) against the Gray walk
+            if ((b8 & 3) != 0 || b8 == 4) {
+                const int kk = b8 == 4 ? 3 : ((b8 & 3) == 2 ? 2 : 1);   // which row constant moves: g_5 (3), g_4 (2), g_3 (1)
+                const bool up = b8 == 4 || (b8 & 3) != 3;               // 0->1: +g3, 1->3: +g4, 3->2: -g3; block switch: +g5
+#pragma unroll
+                for (int a = 0; a < 4; ++a) {
+                    const double g = rc[kk * kTile + 8 * a];
+                    er[a][0] = up ? er[a][0] + g : er[a][0] - g;
+                    er[a][1] = up ? er[a][1] + g : er[a][1] - g;
+                }
+                if (b8 == 4) {                                          // ... and b returns from 2 to 0: -g4
+#pragma unroll
+                    for (int a = 0; a < 4; ++a) {
+                        const double g = rc[2 * kTile + 8 * a];
+                        er[a][0] -= g;
+                        er[a][1] -= g;
+                    }
+                }
+            }
+            // column side: C(j) + T2 terms, plus row bits 3,4 (a) against g_3, g_4 of the column
+            const double ec0 = ea.x + eb.x, ec1 = ea.y + eb.y;
+            const double ec0_3 = ec0 + g34.x, ec1_3 = ec1 + g34.z;
+            const double eca[4][2] = {{ec0, ec1}, {ec0_3, ec1_3}, {ec0 + g34.y, ec1 + g34.w}, {ec0_3 + g34.y, ec1_3 + g34.w}};
 #pragma unroll
             for (int a = 0; a < 4; ++a) {
-                ac[a][0] = er[a][0] + ec0;
-                ac[a][1] = er[a][1] + ec1;
+                ac[a][0] = er[a][0] + eca[a][0];
+                ac[a][1] = er[a][1] + eca[a][1];
             }
 #pragma unroll
-            for (int tt = 0; tt <= DOT; ++tt)
+            for (int tt = 0; tt < DOT; ++tt)
 #pragma unroll
                 for (int a = 0; a < 4; ++a) dmma(ac[a][0], ac[a][1], Af[tt][a], Bf[tt]);
         };
         start_batch(0, acc[0], qe[0]);
 #pragma unroll
         for (int b8 = 0; b8 < 8; ++b8) {
-            const int cur = b8 & 1, b = b8 & 3;
-            if (b8 == 3) {                                             // the next batch opens the second 32-column block
-#pragma unroll
-                for (int a = 0; a < 4; ++a) { er[a][0] += g5[a]; er[a][1] += g5[a]; }
-            }
+            const int cur = b8 & 1, b = (b8 & 3) ^ ((b8 & 3) >> 1);
             if (b8 + 1 < 8) start_batch(b8 + 1, acc[cur ^ 1], qe[cur ^ 1]);
             double cs0 = 0.0, cs1 = 0.0;
 #pragma unroll
@@ -388,7 +412,7 @@ sym64_kernel(const Sym64Params prm, const double* __restrict__ ST, const double*
                 *reinterpret_cast<double2*>(stage + (wr * 8 + r) * kStageStride + cacc) =
                     make_double2(cs0 * (wb * we0), cs1 * (wb * we1));
             }
-            if (b == 3) {
+            if ((b8 & 3) == 3) {
 #pragma unroll
                 for (int a = 0; a < 4; ++a) { rsum[a] = fma(wb, racc[a], rsum[a]); racc[a] = 0.0; }
             }
