@@ -25,11 +25,11 @@
 // red.global.add.f64 from that one thread: same-address program order).  tnk_sym64 finish kernel adds the slots in a
 // fixed order: the result is bit-reproducible run to run (the tcgen05 tile kernel's is not).
 #include "tnk_common.cuh"
+#include <stdlib.h>
 
 namespace {
 
 constexpr int kTile = 128;
-constexpr int kThreads = 256;
 constexpr int kStageStride = 136;      // doubles per row group of the column-sum stage (128 + 8: conflict-free STS.128)
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -42,6 +42,9 @@ __device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
 __device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
                  ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
     asm volatile(
@@ -83,40 +86,41 @@ __host__ __device__ inline int64_t panels_to_unit(int pa, int pb, int B) {
     return (int64_t)pa * B - (int64_t)pa * (pa - 1) / 2 + (pb - pa);
 }
 
-template <int NP>
+// Shared-memory layout.  RB = 8-row blocks per warp (4: 8 warps, 32 rows each; 2: 16 warps, 16 rows each).
+template <int NP, int RB>
 struct Smem64 {
     static constexpr int DOT = NP / 4;                  // K-steps of the score dot product
     static constexpr int STAGES = 3;                    // column-tile buffers: computing t, tables of t+1, copy of t+2 in flight
+    static constexpr int NWR = 16 / RB;                 // row groups (warps along the rows) of the 128-row tile
+    static constexpr int GROUPS = 8 * NWR;              // partial column sums per column: one per (row group, r)
     static constexpr size_t raw_bytes = (size_t)kTile * NP * sizeof(double);
     static constexpr size_t buf_bytes = raw_bytes + 2 * kTile * sizeof(double);      // raw | Cst | q
-    static constexpr size_t tab_bytes = (size_t)(4 + 8 + 2) * kTile * sizeof(double); // colA [4][128] | colB [8][128] | colG [128][2]
-    static constexpr size_t stage_bytes = (size_t)32 * kStageStride * sizeof(double); // [32 row groups][kStageStride]
+    // per-tile tables: colA [NWR][128] | colB [8][136] (rows padded: conflict-free 16-byte loads across r) | colG [128][2] | trow [128]
+    static constexpr size_t tab_bytes = ((size_t)(NWR + 2 + 1) * kTile + 8 * kStageStride) * sizeof(double);
+    static constexpr size_t stage_bytes = (size_t)GROUPS * kStageStride * sizeof(double);
     static constexpr size_t off_buf = 0;
-    static constexpr size_t off_stage = off_buf + STAGES * buf_bytes;                 // [2] stages
-    static constexpr size_t off_tab = off_stage + 2 * stage_bytes;                    // [2] table sets
-    static constexpr size_t off_rowg = off_tab + 2 * tab_bytes;                       // [24][128]
-    static constexpr size_t off_rowc = off_rowg + (size_t)24 * kTile * sizeof(double);     // [4][128]: g_0, g_3, g_4, g_5 of the rows
+    static constexpr size_t off_stage = off_buf + STAGES * buf_bytes;                 // one stage (arrive/sync protocol)
+    static constexpr size_t off_tab = off_stage + stage_bytes;                        // [2] table sets
+    static constexpr size_t off_rowg = off_tab + 2 * tab_bytes;                       // [17][128]: g_p of the rows, p >= 7
+    static constexpr size_t off_rowc = off_rowg + (size_t)17 * kTile * sizeof(double);     // [4][128]: g_0, g_3, g_4, g_5 of the rows
     static constexpr size_t off_rowred = off_rowc + (size_t)4 * kTile * sizeof(double);    // [2][128]
     static constexpr size_t off_wl = off_rowred + (size_t)2 * kTile * sizeof(double);      // [32]
     static constexpr size_t off_bar = off_wl + 32 * sizeof(double);
-    static constexpr size_t total = off_bar + 8 * STAGES;
+    static constexpr size_t total = off_bar + 8 * (STAGES + 1);
+    static_assert(total <= 227 * 1024, "shared memory of the symmetric fp64 kernel");
 };
 
-// physical score component a lane supplies to dot K-step `t` (the same permutation on the A and the B side):
-// steps come in pairs that split an 8-wide group so that one 16-byte load feeds two steps
-template <int NP>
-__device__ __forceinline__ int dot_component(int t, int k) {
-    constexpr int PAIRS = (NP / 4) / 2;
-    return (t < 2 * PAIRS) ? 8 * (t >> 1) + 2 * k + (t & 1) : NP - 4 + k;
-}
-
-template <int NP>
-__global__ void __launch_bounds__(kThreads, 1)
+template <int NP, int RB>
+__global__ void __launch_bounds__(64 * (16 / RB), 1)
 sym64_kernel(const Sym64Params prm, const double* __restrict__ ST, const double* __restrict__ Cst,
              const double* __restrict__ qT, double* __restrict__ RowPart, double* __restrict__ ColPart) {
-    using SM = Smem64<NP>;
-    constexpr int DOT = SM::DOT, PAIRS = DOT / 2, STAGES = SM::STAGES;
+    using SM = Smem64<NP, RB>;
+    constexpr int DOT = SM::DOT, STAGES = SM::STAGES, NWR = SM::NWR, GROUPS = SM::GROUPS;
+    constexpr int THREADS = 64 * NWR;
+    constexpr int ABITS = RB == 4 ? 2 : 1;           // row bits 3.. held by the row-block index a; the rest belong to wr
+    static_assert(RB == 2 || RB == 4, "row blocks per warp");
     extern __shared__ __align__(128) unsigned char smem[];
+    double* stage = reinterpret_cast<double*>(smem + SM::off_stage);
     double* rowg = reinterpret_cast<double*>(smem + SM::off_rowg);
     double* rowc = reinterpret_cast<double*>(smem + SM::off_rowc);
     double* rowred = reinterpret_cast<double*>(smem + SM::off_rowred);
@@ -124,8 +128,9 @@ sym64_kernel(const Sym64Params prm, const double* __restrict__ ST, const double*
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + SM::off_bar);
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int wr = warp >> 1, wc = warp & 1;       // row block (32 rows) and column half (64 columns) of the warp
-    const int r = lane >> 2, k4 = lane & 3;        // row inside an 8-row group; K index / column pair of the fragments
+    const int wr = warp >> 1, wc = warp & 1;       // row group (8 RB rows) and column half (64 columns) of the warp
+    const int r = lane >> 2, k4 = lane & 3;        // row inside an 8-row block; K index / column pair of the fragments
+    const int rowbase = wr * 8 * RB + r;           // + 8a: this thread's rows inside the tile
     const int n = prm.n;
     const int64_t N = (int64_t)1 << n;
     const double gam = prm.gamma, av = prm.a;
@@ -143,6 +148,7 @@ sym64_kernel(const Sym64Params prm, const double* __restrict__ ST, const double*
     if (tid == 0) {
 #pragma unroll
         for (int b = 0; b < STAGES; ++b) mbar_init(&bars[b], 1);
+        mbar_init(&bars[STAGES], THREADS);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncthreads();
@@ -159,64 +165,83 @@ sym64_kernel(const Sym64Params prm, const double* __restrict__ ST, const double*
         bulk_g2s(dst + SM::raw_bytes, Cst + (size_t)J * kTile, kTile * sizeof(double), &bars[buf]);
         bulk_g2s(dst + SM::raw_bytes + kTile * sizeof(double), qT + (size_t)J * kTile, kTile * sizeof(double), &bars[buf]);
     };
-    // per-tile column tables of tile (I, J) = sequence number t:  colA[wr][c] = C(c) + sum_{p>=7} b_p(I) g_p(c) + bits 5,6 of
-    // the row block;  colB[r][c] = sum_{p<3} b_p(r) g_p(c);  colG[c][0..1] = g_3(c), g_4(c)
-    auto build_tables = [&](int I, int J, uint32_t t) {
+    // Per-tile tables of tile (I, J) = sequence number t, built one tile ahead by 128-thread parts:
+    //   colA[w][c] = C(c) + sum_{p>=7} b_p(I) g_p(c) + sum over the row bits held by the row group w (bits 3+ABITS..6) of g_p(c)
+    //   colB[r][c] = sum_{p<3} b_p(r) g_p(c);   colG[c][0..1] = g_3(c), g_4(c)
+    //   trow[row]  = C(row) + sum_{p>=7} g_p(row) b_p(J)     (from the row tile's rowg table; Ic = row tile it belongs to)
+    auto build_tables = [&](int I, int J, uint32_t t, bool rows_ready) {
         const int buf = (int)(t % STAGES);
         mbar_wait(&bars[buf], (t / STAGES) & 1);
         const unsigned char* bufp = smem + SM::off_buf + (size_t)buf * SM::buf_bytes;
         const double* raw = reinterpret_cast<const double*>(bufp);
         const double* cC = reinterpret_cast<const double*>(bufp + SM::raw_bytes);
         double* colA = reinterpret_cast<double*>(smem + SM::off_tab + (size_t)(t & 1) * SM::tab_bytes);
-        double* colB = colA + 4 * kTile;
-        double* colG = colB + 8 * kTile;
-        const int c = tid & (kTile - 1), half = tid >> 7;
+        double* colB = colA + NWR * kTile;
+        double* colG = colB + 8 * kStageStride;
+        double* trow = colG + 2 * kTile;
+        const int c = tid & (kTile - 1), part = tid >> 7;
         const int64_t j = (int64_t)J * kTile + c;
         const double* sc = raw + c * NP;
         auto gcol = [&](int p) -> double {
             const double v = gam * (1.0 - sc[p]);
             return ((j >> p) & 1) ? -v : v;
         };
-        if (half == 0) {
-            // sum over the set bits of I with a fixed trip count: the loads do not wait for the adds
+        if (part == 0) {
             double e = cC[c];
 #pragma unroll 4
-            for (int p = 7; p < n; ++p) {
+            for (int p = 7; p < n; ++p) {          // fixed trip count: the loads do not wait for the adds
                 const double gp = gcol(p);
                 e += ((I >> (p - 7)) & 1) ? gp : 0.0;
             }
-            const double c5 = gcol(5), c6 = gcol(6);
-            colA[0 * kTile + c] = e;
-            colA[1 * kTile + c] = e + c5;
-            colA[2 * kTile + c] = e + c6;
-            colA[3 * kTile + c] = (e + c5) + c6;
-        } else {
+            if (RB == 4) {
+                const double c5 = gcol(5), c6 = gcol(6);
+                colA[0 * kTile + c] = e;
+                colA[1 * kTile + c] = e + c5;
+                colA[2 * kTile + c] = e + c6;
+                colA[3 * kTile + c] = (e + c5) + c6;
+            } else {
+                const double c4 = gcol(4), c5 = gcol(5), c6 = gcol(6);
+#pragma unroll
+                for (int w = 0; w < 8; ++w)
+                    colA[w * kTile + c] = ((e + ((w & 1) ? c4 : 0.0)) + ((w & 2) ? c5 : 0.0)) + ((w & 4) ? c6 : 0.0);
+            }
+        }
+        if (part == 1) {
             const double c0 = gcol(0), c1 = gcol(1), c2 = gcol(2);
 #pragma unroll
             for (int rr = 0; rr < 8; ++rr)
-                colB[rr * kTile + c] = ((rr & 1) ? c0 : 0.0) + ((rr & 2) ? c1 : 0.0) + ((rr & 4) ? c2 : 0.0);
+                colB[rr * kStageStride + c] = ((rr & 1) ? c0 : 0.0) + ((rr & 2) ? c1 : 0.0) + ((rr & 4) ? c2 : 0.0);
             colG[2 * c] = gcol(3);
             colG[2 * c + 1] = gcol(4);
         }
-    };
-    // Column sums of a finished tile: two threads per column, each adding 16 of the 32 row groups as four independent
-    // chains; fixed order -> deterministic.
-    auto flush_stage = [&](uint32_t t, int J, bool first) {
-        {
-            const double* stage = reinterpret_cast<const double*>(smem + SM::off_stage + (size_t)(t & 1) * SM::stage_bytes);
-            const int col = tid >> 1, hf = tid & 1;
-            const double* src = stage + (16 * hf) * kStageStride + col;
-            double p4[4] = {0.0, 0.0, 0.0, 0.0};
-#pragma unroll
-            for (int g = 0; g < 16; ++g) p4[g & 3] += src[g * kStageStride];
-            double acc = (p4[0] + p4[1]) + (p4[2] + p4[3]);
-            acc += __shfl_xor_sync(0xffffffffu, acc, 1);
-            if (hf == 0) {
-                double* dst = colpart + (size_t)J * kTile + col;
-                if (first) *dst = acc; else red_add_f64(dst, acc);
+        if (part == (THREADS > 256 ? 2 : 1) && rows_ready) {
+            double e = Cst[(int64_t)I * kTile + c];
+#pragma unroll 4
+            for (int p = 7; p < n; ++p) {
+                const double gp = rowg[(p - 7) * kTile + c];
+                e += ((J >> (p - 7)) & 1) ? gp : 0.0;
             }
+            trow[c] = e;
         }
     };
+    // Column sums of a finished tile: THREADS/128 threads per column, each adding 16 of the GROUPS row groups as four
+    // independent chains; fixed order -> deterministic.
+    auto flush_stage = [&](int J, bool first) {
+        constexpr int TPC = THREADS / kTile;                          // 2 or 4 threads per column
+        const int col = tid / TPC, part = tid % TPC;
+        const double* src = stage + (16 * part) * kStageStride + col;
+        double p4[4] = {0.0, 0.0, 0.0, 0.0};
+#pragma unroll
+        for (int g = 0; g < 16; ++g) p4[g & 3] += src[g * kStageStride];
+        double acc = (p4[0] + p4[1]) + (p4[2] + p4[3]);
+        acc += __shfl_xor_sync(0xffffffffu, acc, 1);
+        if (TPC == 4) acc += __shfl_xor_sync(0xffffffffu, acc, 2);
+        if (part == 0) {
+            double* dst = colpart + (size_t)J * kTile + col;
+            if (first) *dst = acc; else red_add_f64(dst, acc);
+        }
+    };
+    static_assert(GROUPS == 16 * (THREADS / kTile), "flush covers every row group");
 
     // thread constants of the Hamming weight: bits 1,2 of i^j, and the e-dependent bit 0
     const int pt = __popc((uint32_t)(((r >> 1) & 3) ^ k4));
@@ -224,7 +249,7 @@ sym64_kernel(const Sym64Params prm, const double* __restrict__ ST, const double*
     const double we0 = (r & 1) ? av : 1.0, we1 = (r & 1) ? 1.0 : av;     // a^((r&1)^e)
     const double w1 = av, w2 = av * av;
 
-    // ---- prologue: copies of tiles 0 and 1 in flight, tables of tile 0
+    // ---- prologue: copies of tiles 0 and 1 in flight
     int I = I_begin, J = diag ? I_begin : pb * s;     // tile t
     int I1 = I, J1 = J;                               // tile t+1
     advance(I1, J1);
@@ -232,61 +257,58 @@ sym64_kernel(const Sym64Params prm, const double* __restrict__ ST, const double*
         issue_tile(J, 0);
         if (n_tiles > 1) issue_tile(J1, 1);
     }
-    build_tables(I, J, 0);
 
-    double Af[DOT][4];
-    double qi[4], rbase[4];
-    double rsum[4] = {0.0, 0.0, 0.0, 0.0};
+    double Af[DOT][RB];
+    double qi[RB], rbase[RB];
+    double rsum[RB];
+#pragma unroll
+    for (int a = 0; a < RB; ++a) rsum[a] = 0.0;
     int I_loaded = -1;
     int pend_J = -1;                                 // column tile whose stage still has to be flushed
     bool pend_first = false;
 
     for (uint32_t t = 0; t < n_tiles; ++t) {
-        __syncthreads();      // S_t: tile t-1 fully consumed; stage (t-1)&1 complete; tables of t visible; buffer (t+2)%3 free
-        if (pend_J >= 0) { flush_stage(t - 1, pend_J, pend_first); pend_J = -1; }
+        __syncthreads();      // S_t: tile t-1 fully consumed; its stage complete; tables of t visible; buffer (t+2)%3 free
+        if (pend_J >= 0) { flush_stage(pend_J, pend_first); pend_J = -1; }
+        mbar_arrive(&bars[STAGES]);                  // this thread no longer reads the stage (phase t of the stage barrier)
         int I2 = I1, J2 = J1;                         // tile t+2
         advance(I2, J2);
         if (tid == 0 && t + 2 < n_tiles) issue_tile(J2, t + 2);
 
-        if (I != I_loaded) {
+        const bool switch_rows = I != I_loaded;
+        if (switch_rows) {
             // ---- row tile switch: store the finished row sums, then load the row operands of tile I
             if (I_loaded >= 0) {
 #pragma unroll
-                for (int a = 0; a < 4; ++a) {
+                for (int a = 0; a < RB; ++a) {
                     double v = rsum[a];
                     v += __shfl_xor_sync(0xffffffffu, v, 1);
                     v += __shfl_xor_sync(0xffffffffu, v, 2);
-                    if (k4 == 0) rowred[wc * kTile + wr * 32 + 8 * a + r] = v;
+                    if (k4 == 0) rowred[wc * kTile + rowbase + 8 * a] = v;
                     rsum[a] = 0.0;
                 }
             }
-            const int64_t i_base = (int64_t)I * kTile + wr * 32 + r;     // + 8a
 #pragma unroll
-            for (int a = 0; a < 4; ++a) {
-                const int64_t i = i_base + 8 * a;
+            for (int a = 0; a < RB; ++a) {
+                const int64_t i = (int64_t)I * kTile + rowbase + 8 * a;
                 const double* si = ST + i * NP;
 #pragma unroll
-                for (int m = 0; m < PAIRS; ++m) {
-                    const double2 v = *reinterpret_cast<const double2*>(si + 8 * m + 2 * k4);
-                    Af[2 * m][a] = v.x;
-                    Af[2 * m + 1][a] = v.y;
-                }
-                if (DOT & 1) Af[DOT - 1][a] = si[NP - 4 + k4];
+                for (int tt = 0; tt < DOT; ++tt) Af[tt][a] = si[4 * tt + k4];
                 auto grow = [&](int p) -> double {       // g_p(i)
                     const double v = gam * (1.0 - si[p]);
                     return ((i >> p) & 1) ? -v : v;
                 };
                 qi[a] = qT[i];
-                // C(i) + column bits 1,2 (thread constants) + column bit 6 (warp constant)
-                rbase[a] = Cst[i] + ((k4 & 1) ? grow(1) : 0.0) + ((k4 & 2) ? grow(2) : 0.0) + (wc ? grow(6) : 0.0);
+                // column bits 1,2 (thread constants) and 6 (warp constant); C(i) and the bits >= 7 come from the trow table
+                rbase[a] = ((k4 & 1) ? grow(1) : 0.0) + ((k4 & 2) ? grow(2) : 0.0) + (wc ? grow(6) : 0.0);
             }
-            for (int item = tid; item < kTile * 4; item += kThreads) {       // g_0, g_3, g_4, g_5 of every row of the tile
+            for (int item = tid; item < kTile * 4; item += THREADS) {       // g_0, g_3, g_4, g_5 of every row of the tile
                 const int row = item & (kTile - 1), p = (item >> 7) == 0 ? 0 : 2 + (item >> 7);
                 const int64_t i = (int64_t)I * kTile + row;
                 const double v = gam * (1.0 - ST[i * NP + p]);
                 rowc[(item >> 7) * kTile + row] = ((i >> p) & 1) ? -v : v;
             }
-            for (int item = tid; item < kTile * (n - 7); item += kThreads) {
+            for (int item = tid; item < kTile * (n - 7); item += THREADS) {
                 const int row = item & (kTile - 1), p = 7 + (item >> 7);
                 const int64_t i = (int64_t)I * kTile + row;
                 const double v = gam * (1.0 - ST[i * NP + p]);
@@ -295,126 +317,116 @@ sym64_kernel(const Sym64Params prm, const double* __restrict__ ST, const double*
             __syncthreads();
             if (I_loaded >= 0 && tid < kTile) rowpart[(size_t)I_loaded * kTile + tid] = rowred[tid] + rowred[kTile + tid];
             I_loaded = I;
+            build_tables(I, J, t, true);               // tables of the first tile of the sweep (trow needs the new rowg)
+            __syncthreads();
         }
 
-        // tables of tile t+1 (its copy was issued one iteration ago), then this warp's part of tile t
-        if (t + 1 < n_tiles) build_tables(I1, J1, t + 1);
+        // tables of tile t+1 (its copy was issued one iteration ago); when t+1 opens a new row tile its trow is built there
+        if (t + 1 < n_tiles) build_tables(I1, J1, t + 1, I1 == I);
 
         const unsigned char* bufp = smem + SM::off_buf + (size_t)(t % STAGES) * SM::buf_bytes;
         const double* raw = reinterpret_cast<const double*>(bufp);
         const double* cq = reinterpret_cast<const double*>(bufp + SM::raw_bytes) + kTile;
         const double* colA = reinterpret_cast<const double*>(smem + SM::off_tab + (size_t)(t & 1) * SM::tab_bytes);
-        const double* colB = colA + 4 * kTile;
-        const double* colG = colB + 8 * kTile;
-        double* stage = reinterpret_cast<double*>(smem + SM::off_stage + (size_t)(t & 1) * SM::stage_bytes);
+        const double* colB = colA + NWR * kTile;
+        const double* colG = colB + 8 * kStageStride;
+        const double* trow = colG + 2 * kTile;
         const bool mirrored = J != I;
 
-        // row side of the seed: rbase + sum_{p>=7} g_p(i) b_p(J); er[a][e] adds column bits 5 (second block) and 0 (e)
-        double er[4][2];
+        // row side of the seed: er[a][e] = C(i) + T1 terms of every column bit except 3,4 at the first batch
+        const double* rc = rowc + rowbase;                                // + k*128 + 8a: g_0, g_3, g_4, g_5 of this thread's rows
+        double er[RB][2];
 #pragma unroll
-        for (int a = 0; a < 4; ++a) er[a][0] = rbase[a];
-#pragma unroll 2
-        for (int p = 7; p < n; ++p) {
-            const double* gp = rowg + (p - 7) * kTile + wr * 32 + r;
-            const bool on = (J >> (p - 7)) & 1;
-#pragma unroll
-            for (int a = 0; a < 4; ++a) {
-                const double v = gp[8 * a];
-                er[a][0] += on ? v : 0.0;
-            }
+        for (int a = 0; a < RB; ++a) {
+            er[a][0] = trow[rowbase + 8 * a] + rbase[a];
+            er[a][1] = er[a][0] + rc[8 * a];
         }
-        const double* rc = rowc + wr * 32 + r;                            // + k*128 + 8a: g_0, g_3, g_4, g_5 of this thread's rows
-#pragma unroll
-        for (int a = 0; a < 4; ++a) er[a][1] = er[a][0] + rc[8 * a];
         const int hh = __popc((uint32_t)(I ^ J));
-        const double wb0 = sWl[hh + __popc((uint32_t)(wr ^ (2 * wc)))] * wt;
-        const double wb1 = sWl[hh + __popc((uint32_t)(wr ^ (2 * wc + 1)))] * wt;
 
-        // ---- 8 batches of 8 columns (b8 = 4*cbi + b), software-pipelined: the MMAs of batch b8+1 are issued before the
-        //      epilogue of batch b8, so that one warp alone keeps the fp64 pipe fed
-        double acc[2][4][2];
+        // ---- 8 batches of 8 columns, software-pipelined: the MMAs of batch b8+1 are issued before the epilogue of batch b8.
+        //      batch b8: 32-column block cbi = b8 >> 2, 8-column group b = gray(b8 & 3) = 0, 1, 3, 2 - one of the column
+        //      bits 3, 4 changes per batch, so the row side of the seed follows with one add per value (g_3 or g_4 of the row)
+        double acc[2][RB][2];
         double qe[2][2];
-        double racc[4] = {0.0, 0.0, 0.0, 0.0};
-        // batch b8: 32-column block cbi = b8 >> 2, 8-column group b = gray(b8 & 3) = 0, 1, 3, 2 - one of the column bits
-        // 3, 4 changes per batch, so the row side of the seed follows with one add per value (g_3 or g_4 of the row)
-        auto start_batch = [&](int b8, double (&ac)[4][2], double (&qv2)[2]) {
+        double wst[2][2];                                                 // weights of the column sums of the batch in flight
+        auto start_batch = [&](int b8, double (&ac)[RB][2], double (&qv2)[2], double (&ws2)[2]) {
             const int cb = 2 * wc + (b8 >> 2), b = (b8 & 3) ^ ((b8 & 3) >> 1);
             const int cfrag = cb * 32 + 8 * b + r;                     // column this lane supplies to the B fragment
             const double* sc = raw + cfrag * NP;
             double Bf[DOT];
 #pragma unroll
-            for (int m = 0; m < PAIRS; ++m) {
-                const double2 v = *reinterpret_cast<const double2*>(sc + 8 * m + 2 * k4);
-                Bf[2 * m] = v.x;
-                Bf[2 * m + 1] = v.y;
-            }
-            if (DOT & 1) Bf[DOT - 1] = sc[NP - 4 + k4];
+            for (int tt = 0; tt < DOT; ++tt) Bf[tt] = sc[4 * tt + k4];
             const int cacc = cb * 32 + 8 * b + 2 * k4;                 // first of the two columns of the accumulator
             const double2 ea = *reinterpret_cast<const double2*>(colA + wr * kTile + cacc);
-            const double2 eb = *reinterpret_cast<const double2*>(colB + r * kTile + cacc);
+            const double2 eb = *reinterpret_cast<const double2*>(colB + r * kStageStride + cacc);
             const double2 qv = *reinterpret_cast<const double2*>(cq + cacc);
             const double4 g34 = *reinterpret_cast<const double4*>(colG + 2 * cacc);   // g_3, g_4 of column cacc; of cacc + 1
-            qv2[0] = qv.x * we0;
-            qv2[1] = qv.y * we1;
+            // weight of the warp-uniform bits of i^j: tile bits, bits 5,6 and (16-row warps) bit 4
+            const int hb = hh + (RB == 4 ? __popc((uint32_t)(wr ^ cb)) : __popc((uint32_t)((wr >> 1) ^ cb)) + ((wr & 1) ^ (b >> 1)));
+            const double wb = sWl[hb] * wt;
+            ws2[0] = wb * we0;                                          // weight of everything but the bits held by a
+            ws2[1] = wb * we1;
+            qv2[0] = qv.x * ws2[0];                                     // ... folded into q_j for the row sums
+            qv2[1] = qv.y * ws2[1];
             // row side: column bits 3,4 (b) and 5 (cbi) against the Gray walk
             if ((b8 & 3) != 0 || b8 == 4) {
                 const int kk = b8 == 4 ? 3 : ((b8 & 3) == 2 ? 2 : 1);   // which row constant moves: g_5 (3), g_4 (2), g_3 (1)
                 const bool up = b8 == 4 || (b8 & 3) != 3;               // 0->1: +g3, 1->3: +g4, 3->2: -g3; block switch: +g5
 #pragma unroll
-                for (int a = 0; a < 4; ++a) {
+                for (int a = 0; a < RB; ++a) {
                     const double g = rc[kk * kTile + 8 * a];
                     er[a][0] = up ? er[a][0] + g : er[a][0] - g;
                     er[a][1] = up ? er[a][1] + g : er[a][1] - g;
                 }
                 if (b8 == 4) {                                          // ... and b returns from 2 to 0: -g4
 #pragma unroll
-                    for (int a = 0; a < 4; ++a) {
+                    for (int a = 0; a < RB; ++a) {
                         const double g = rc[2 * kTile + 8 * a];
                         er[a][0] -= g;
                         er[a][1] -= g;
                     }
                 }
             }
-            // column side: C(j) + T2 terms, plus row bits 3,4 (a) against g_3, g_4 of the column
+            // column side: C(j) + T2 terms; the row bits held by a (bit 3, and bit 4 for 32-row warps) meet g_3, g_4 of the column
             const double ec0 = ea.x + eb.x, ec1 = ea.y + eb.y;
             const double ec0_3 = ec0 + g34.x, ec1_3 = ec1 + g34.z;
-            const double eca[4][2] = {{ec0, ec1}, {ec0_3, ec1_3}, {ec0 + g34.y, ec1 + g34.w}, {ec0_3 + g34.y, ec1_3 + g34.w}};
+            double eca[4][2] = {{ec0, ec1}, {ec0_3, ec1_3}, {0.0, 0.0}, {0.0, 0.0}};
+            if (RB == 4) {
+                eca[2][0] = ec0 + g34.y; eca[2][1] = ec1 + g34.w;
+                eca[3][0] = ec0_3 + g34.y; eca[3][1] = ec1_3 + g34.w;
+            }
 #pragma unroll
-            for (int a = 0; a < 4; ++a) {
+            for (int a = 0; a < RB; ++a) {
                 ac[a][0] = er[a][0] + eca[a][0];
                 ac[a][1] = er[a][1] + eca[a][1];
             }
 #pragma unroll
             for (int tt = 0; tt < DOT; ++tt)
 #pragma unroll
-                for (int a = 0; a < 4; ++a) dmma(ac[a][0], ac[a][1], Af[tt][a], Bf[tt]);
+                for (int a = 0; a < RB; ++a) dmma(ac[a][0], ac[a][1], Af[tt][a], Bf[tt]);
         };
-        start_batch(0, acc[0], qe[0]);
+        start_batch(0, acc[0], qe[0], wst[0]);
 #pragma unroll
         for (int b8 = 0; b8 < 8; ++b8) {
             const int cur = b8 & 1, b = (b8 & 3) ^ ((b8 & 3) >> 1);
-            if (b8 + 1 < 8) start_batch(b8 + 1, acc[cur ^ 1], qe[cur ^ 1]);
+            if (b8 + 1 < 8) start_batch(b8 + 1, acc[cur ^ 1], qe[cur ^ 1], wst[cur ^ 1]);
             double cs0 = 0.0, cs1 = 0.0;
 #pragma unroll
-            for (int a = 0; a < 4; ++a) {
-                const int x = a ^ b;                                   // bits 3,4 of i^j
+            for (int a = 0; a < RB; ++a) {
+                const int x = RB == 4 ? (a ^ b) : (a ^ (b & 1));      // the row bits held by a against column bits 3(,4)
                 const int pc = (x & 1) + (x >> 1);
                 const double v0 = pc == 0 ? acc[cur][a][0] : acc[cur][a][0] * (pc == 1 ? w1 : w2);
                 const double v1 = pc == 0 ? acc[cur][a][1] : acc[cur][a][1] * (pc == 1 ? w1 : w2);
-                racc[a] = fma(v0, qe[cur][0], racc[a]);
-                racc[a] = fma(v1, qe[cur][1], racc[a]);
+                rsum[a] = fma(v0, qe[cur][0], rsum[a]);
+                rsum[a] = fma(v1, qe[cur][1], rsum[a]);
                 cs0 = fma(v0, qi[a], cs0);
                 cs1 = fma(v1, qi[a], cs1);
             }
-            const double wb = (b8 >> 2) ? wb1 : wb0;
             if (mirrored) {
+                if (b8 == 0) mbar_wait(&bars[STAGES], t & 1);     // every thread has flushed tile t-1 (long since: no stall)
                 const int cacc = (2 * wc + (b8 >> 2)) * 32 + 8 * b + 2 * k4;
                 *reinterpret_cast<double2*>(stage + (wr * 8 + r) * kStageStride + cacc) =
-                    make_double2(cs0 * (wb * we0), cs1 * (wb * we1));
-            }
-            if ((b8 & 3) == 3) {
-#pragma unroll
-                for (int a = 0; a < 4; ++a) { rsum[a] = fma(wb, racc[a], rsum[a]); racc[a] = 0.0; }
+                    make_double2(cs0 * wst[cur][0], cs1 * wst[cur][1]);
             }
         }
         if (mirrored) { pend_J = J; pend_first = (I == I_begin); }   // a column tile is first met by the panel's first row tile
@@ -423,15 +435,15 @@ sym64_kernel(const Sym64Params prm, const double* __restrict__ ST, const double*
 
     // ---- epilogue: the last row tile's sums and the last tile's column sums
 #pragma unroll
-    for (int a = 0; a < 4; ++a) {
+    for (int a = 0; a < RB; ++a) {
         double v = rsum[a];
         v += __shfl_xor_sync(0xffffffffu, v, 1);
         v += __shfl_xor_sync(0xffffffffu, v, 2);
-        if (k4 == 0) rowred[wc * kTile + wr * 32 + 8 * a + r] = v;
+        if (k4 == 0) rowred[wc * kTile + rowbase + 8 * a] = v;
     }
     __syncthreads();
     if (tid < kTile) rowpart[(size_t)I_loaded * kTile + tid] = rowred[tid] + rowred[kTile + tid];
-    if (pend_J >= 0) flush_stage(n_tiles - 1, pend_J, pend_first);
+    if (pend_J >= 0) flush_stage(pend_J, pend_first);
 }
 
 // u[z] = sum of the row-part and column-part slots of the units this launch owned (fixed order); block partials of q.u
@@ -516,15 +528,34 @@ int make_plan64(int n, int unit_offset, int unit_stride, Sym64Plan* p) {
     return 0;
 }
 
-template <int NP>
+template <int NP, int RB>
 int launch64(const Sym64Params& prm, int n_units, const double* ST, const double* Cst, const double* qT,
              double* RowPart, double* ColPart, cudaStream_t st) {
-    using SM = Smem64<NP>;
-    auto kern = sym64_kernel<NP>;
+    using SM = Smem64<NP, RB>;
+    auto kern = sym64_kernel<NP, RB>;
     TNK_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SM::total));
-    kern<<<(unsigned)n_units, kThreads, SM::total, st>>>(prm, ST, Cst, qT, RowPart, ColPart);
+    kern<<<(unsigned)n_units, 64 * (16 / RB), SM::total, st>>>(prm, ST, Cst, qT, RowPart, ColPart);
     TNK_CUDA_OK(cudaGetLastError());
     return 0;
+}
+
+// warps per CTA: 8 (32 rows per warp, 255 registers) by default; TNK_SYM64_WARPS=16 selects the 16-rows-per-warp instance
+// (128 registers, twice the warps: measured slower - every B fragment then feeds two MMAs instead of four and the
+// shared-memory pipe saturates; kept for A/B runs)
+int sym64_row_blocks() {
+    static int rb = 0;
+    if (rb == 0) {
+        const char* e = getenv("TNK_SYM64_WARPS");
+        rb = (e && atoi(e) == 16) ? 2 : 4;
+    }
+    return rb;
+}
+
+template <int NP>
+int dispatch64(const Sym64Params& prm, int n_units, const double* ST, const double* Cst, const double* qT,
+               double* RowPart, double* ColPart, cudaStream_t st) {
+    return sym64_row_blocks() == 4 ? launch64<NP, 4>(prm, n_units, ST, Cst, qT, RowPart, ColPart, st)
+                                   : launch64<NP, 2>(prm, n_units, ST, Cst, qT, RowPart, ColPart, st);
 }
 
 }  // namespace
@@ -582,11 +613,11 @@ extern "C" int tnk_ksd_sym64(int n_latent, double length_scale, const void* q, i
     if (p.n_units > 0) {
         int rc = 0;
         switch (p.np) {
-            case 8:  rc = launch64<8>(prm, p.n_units, ST, Cst, qT, RowPart, ColPart, st); break;
-            case 12: rc = launch64<12>(prm, p.n_units, ST, Cst, qT, RowPart, ColPart, st); break;
-            case 16: rc = launch64<16>(prm, p.n_units, ST, Cst, qT, RowPart, ColPart, st); break;
-            case 20: rc = launch64<20>(prm, p.n_units, ST, Cst, qT, RowPart, ColPart, st); break;
-            case 24: rc = launch64<24>(prm, p.n_units, ST, Cst, qT, RowPart, ColPart, st); break;
+            case 8:  rc = dispatch64<8>(prm, p.n_units, ST, Cst, qT, RowPart, ColPart, st); break;
+            case 12: rc = dispatch64<12>(prm, p.n_units, ST, Cst, qT, RowPart, ColPart, st); break;
+            case 16: rc = dispatch64<16>(prm, p.n_units, ST, Cst, qT, RowPart, ColPart, st); break;
+            case 20: rc = dispatch64<20>(prm, p.n_units, ST, Cst, qT, RowPart, ColPart, st); break;
+            case 24: rc = dispatch64<24>(prm, p.n_units, ST, Cst, qT, RowPart, ColPart, st); break;
             default: tnk_set_error("tnk_ksd_sym64: no kernel instance for padded length %d", p.np); return 2;
         }
         if (rc) return rc;

@@ -1,5 +1,7 @@
 """CPU check of the decomposition the symmetric fp64 kernel uses (csrc/tnk_sym64.cu, "K3-S64"): per pair the bracket
-is   DMMA part (score dot product + T1/T2 terms of bit positions 3,4)  +  row seed  +  column seed,
+is   DMMA part (score dot product)  +  row seed  +  column seed  +  the T1/T2 terms of bit positions 3,4 (held by the
+row-block / column-group indices a, b of the accumulator fragment: a Gray walk on the row side, g_3, g_4 of the column
+on the other),
 and the Hamming weight is  LUT[tile and block bits] * thread constant * a^popc(a^b) * a^((r&1)^e).
 A numpy restatement of those pieces, indexed by the same bit fields of i and j the kernel uses, must reproduce the
 oracle's dense K_p (reference stein_utils.py:138-197); the unit enumeration must be a bijection."""
@@ -43,7 +45,7 @@ def test_seed_and_weight_factorisation(n, gen):
     # column seed: colA[wr][c] + colB[r][c]
     col = (C[None, :] + sum(((I >> (p - 7)) & 1) * gj(p) for p in hi_bits) + (wr & 1) * gj(5) + (wr >> 1) * gj(6)
            + (r & 1) * gj(0) + ((r >> 1) & 1) * gj(1) + (r >> 2) * gj(2))
-    # DMMA: dot product + K-step [g3(i), g4(i), b3(i), b4(i)] . [b3(j), b4(j), g3(j), g4(j)]
+    # dot product (DMMA) + the bits-3,4 terms: g3(i) b3(j) + g4(i) b4(j) on the row seed, b3(i) g3(j) + b4(i) g4(j) on the column seed
     mma = s @ s.T + gi(3) * (b & 1) + gi(4) * (b >> 1) + (a & 1) * gj(3) + (a >> 1) * gj(4)
     weight = (wl[_popc(I ^ J) + _popc(wr ^ cb)] * a_ ** _popc(((r >> 1) & 3) ^ k4)
               * a_ ** _popc(a ^ b) * a_ ** ((r & 1) ^ e))
