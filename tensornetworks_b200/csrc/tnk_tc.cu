@@ -41,6 +41,7 @@
 //             in fp32 per tile / compensated fp32 across tiles / one fp64 add at the end
 #include <cuda_bf16.h>
 #include "tnk_common.cuh"
+#include <stdlib.h>
 #include "tnk_tc.cuh"
 
 namespace {
@@ -583,6 +584,7 @@ struct TcsParams {
     int tile_offset, tile_stride;  // row tile of blockIdx.x = tile_offset + tile_stride * blockIdx.x
     int64_t n_tiles;               // 2^n / 128
     int col_splits;                // gridDim.y
+    int ablate;                    // diagnostics only (TNK_TCS_ABLATE, wrong results): 1 = no mirrored part, 2 = mirrored sums not stored
     float gamma;
     float wl[32];
 };
@@ -961,7 +963,7 @@ tcs_tiles_kernel(const __grid_constant__ TcsParams prm, const float* __restrict_
                     uch[k] = 0.f;
                 }
             }
-            if (J != I32) {
+            if (J != I32 && !(prm.ablate & 1)) {
                 // mirrored part: sum over the warp's 32 rows (8 row groups = lane bits 2-4), exchanging halves of the
                 // column set per level; with 4 atoms per thread the last level is a plain exchange-add
                 auto xadd = [&](const float2 keep, const float2 send, const int mask) {
@@ -988,7 +990,7 @@ tcs_tiles_kernel(const __grid_constant__ TcsParams prm, const float* __restrict_
                 }
                 // one fp64 RED per column, warp and tile (fire and forget; the four lane quarters meet in L2 - measured
                 // faster than combining them in shared memory behind a named barrier)
-                if (MC == 8 || !b2) {
+                if ((MC == 8 || !b2) && !(prm.ablate & 2)) {
                     double* dst = ucol + (size_t)J * kTile + colbase + col;
                     atomicAdd(dst, (double)(wg * c3.x));
                     atomicAdd(dst + 1, (double)(wg * c3.y));
@@ -1162,6 +1164,10 @@ int tnk_tcs_launch(int n, int fmt, double gamma, const double* wl, const float* 
     TcsParams prm;
     prm.n = n; prm.tile_offset = tile_offset; prm.tile_stride = tile_stride; prm.n_tiles = col_tiles;
     prm.col_splits = splits; prm.gamma = (float)gamma;
+    {
+        const char* e = getenv("TNK_TCS_ABLATE");      // ablation runs of scripts/sym_ablate.py: results are WRONG when set
+        prm.ablate = e ? atoi(e) : 0;
+    }
     for (int h = 0; h < 32; ++h) prm.wl[h] = (float)wl[h];
     if (ev_start) TNK_CUDA_OK(cudaEventRecord(ev_start, st));
     dim3 grid((unsigned)row_tiles, (unsigned)splits, 1);

@@ -53,15 +53,6 @@ def test_seed_and_weight_factorisation(n, gen):
     assert np.max(np.abs(got - Kp)) <= 1e-12 * np.max(np.abs(Kp))
 
 
-def test_dot_component_permutation_covers_every_component():
-    """K-steps come in pairs that split an 8-wide group (one 16-byte load feeds two steps), plus a single step."""
-    for NP in (8, 12, 16, 20, 24):
-        dot, pairs = NP // 4, (NP // 4) // 2
-        seen = sorted((8 * (t >> 1) + 2 * k + (t & 1)) if t < 2 * pairs else NP - 4 + k
-                      for t in range(dot) for k in range(4))
-        assert seen == list(range(NP))
-
-
 def test_unit_enumeration_is_a_bijection():
     for B in (1, 2, 5, 32, 128):
         seen = set()
