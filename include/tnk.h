@@ -190,6 +190,12 @@ int tnk_tc_plan(int n_latent, int* np, int* k32, int* kb, int* nsteps, int* nste
  * The mirrored sums are accumulated with fp64 atomics: the last bits of u_partial depend on their order. */
 #define TNK_SYM_SPLIT_TF32 0
 #define TNK_SYM_SPLIT_BF16X2 1
+#define TNK_SYM_SPLIT_TF32_TILE 2   /* as TF32, with the T1/T2 terms of the bit positions >= 7 (constant over a 128-state tile
+                                       on one side) taken off the MMAs and folded into the row / column sums through four
+                                       128-point Kronecker transforms per tile: 9 instead of 13 MMA K-steps at n = 20, 10
+                                       instead of 16 at n = 24; same accuracy class */
+#define TNK_SYM_SPLIT_TF32_DOT 3    /* only the score dot product s(z).s(z') stays in the pair kernel (6 K-steps for every
+                                       n <= 24); C(z) + C(z') and all T1/T2 terms go through n + 2 fp64 Kronecker transforms */
 size_t tnk_ksd_sym_workspace_bytes(int n_latent, int split, int tile_offset, int tile_stride);
 int tnk_ksd_sym(int n_latent, double length_scale, int split, const void* q, int q_dtype,
                 const void* ST, const void* Cst, int tile_offset, int tile_stride, int reuse_table,

@@ -16,7 +16,9 @@ a.record(); b.record()
 out = {}
 for name, flag, split in (("full kernel (13 K-steps)", "0", "tf32"), ("no mirrored part", "1", "tf32"),
                           ("mirrored sums computed, not stored (no fp64 RED)", "2", "tf32"),
-                          ("bf16x2 operands (10 K-steps)", "0", "bf16x2"), ("bf16x2, no mirrored part", "1", "bf16x2")):
+                          ("bf16x2 operands (10 K-steps)", "0", "bf16x2"), ("bf16x2, no mirrored part", "1", "bf16x2"),
+                          ("tf32_tile operands (9 K-steps)", "0", "tf32_tile"), ("tf32_tile, no mirrored part", "1", "tf32_tile"),
+                          ("tf32_dot operands (6 K-steps)", "0", "tf32_dot"), ("tf32_dot, no mirrored part", "1", "tf32_dot")):
     os.environ["TNK_TCS_ABLATE"] = flag
     tc.ksd_sym(q, split=split)
     times = []

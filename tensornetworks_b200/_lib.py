@@ -23,7 +23,7 @@ NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", 
 PREC_FP64, PREC_FP32, PREC_FP64_SIMPLE, PREC_TC32 = 0, 1, 2, 4
 MAX_PEERS = 8  # TNK_MAX_PEERS
 MP_STORE = {"fp64": 0, "fp32": 1}  # TNK_MP_STORE_*
-SYM_SPLIT = {"tf32": 0, "bf16x2": 1}  # TNK_SYM_SPLIT_*
+SYM_SPLIT = {"tf32": 0, "bf16x2": 1, "tf32_tile": 2, "tf32_dot": 3}  # TNK_SYM_SPLIT_*
 
 # every symbol include/tnk.h declares
 EXPORTS = ["tnk_last_error", "tnk_version", "tnk_bn_joint", "tnk_ksd_layout", "tnk_score",

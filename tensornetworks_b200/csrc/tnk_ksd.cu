@@ -670,12 +670,12 @@ namespace {
 struct SymPlan {
     int64_t N, T, finish_blocks;
     int row_tiles, splits;
-    size_t off_q, off_col, off_block, off_b, total;
+    size_t off_q, off_col, off_block, off_b, off_hib, total;
 };
 
 int make_sym_plan(int n, int split, int tile_offset, int tile_stride, SymPlan* p) {
     if (n < TNK_TC_MIN_LATENT || n > TNK_TC_MAX_LATENT || tile_stride < 1 || tile_offset < 0) return 1;
-    if (split != TNK_SYM_SPLIT_TF32 && split != TNK_SYM_SPLIT_BF16X2) return 1;
+    if (split < TNK_SYM_SPLIT_TF32 || split > TNK_SYM_SPLIT_TF32_DOT) return 1;
     p->N = (int64_t)1 << n;
     p->T = p->N / TNK_TC_TILE;
     p->row_tiles = tile_offset < p->T ? (int)((p->T - tile_offset + tile_stride - 1) / tile_stride) : 0;
@@ -691,6 +691,9 @@ int make_sym_plan(int n, int split, int tile_offset, int tile_stride, SymPlan* p
     p->off_col = take((size_t)p->N * sizeof(double));
     p->off_block = take((size_t)(p->finish_blocks + 1) * sizeof(double));
     p->off_b = take(b_bytes);
+    p->off_hib = off;
+    if (split == TNK_SYM_SPLIT_TF32_TILE && tile_offset == 0) p->off_hib = take(tnk_hibits_ws_bytes(n, 7, 0));
+    if (split == TNK_SYM_SPLIT_TF32_DOT && tile_offset == 0) p->off_hib = take(tnk_hibits_ws_bytes(n, 0, 1));
     p->total = off;
     return 0;
 }
@@ -756,7 +759,7 @@ extern "C" int tnk_ksd_sym(int n_latent, double length_scale, int split, const v
     TNK_CUDA_OK(cudaGetLastError());
     ++launches;
     const int rc = tnk_tcs_launch(n, split, gamma, wl, (const float*)ST, (const float*)Cst, qT, tile_offset, tile_stride,
-                                  p.row_tiles, p.splits, (float*)(ws + p.off_b), reuse_table, ucol,
+                                  p.row_tiles, p.splits, (float*)(ws + p.off_b), reuse_table, ucol, (double*)(ws + p.off_hib),
                                   g_ev_start, g_ev_stop, &launches, st);
     if (rc) return rc;
     if (q_dtype == 0)

@@ -30,6 +30,7 @@
 // only for n > 24), mp_last (butterflies on the high bits, fold into u, block partials of q.u),
 // mp_scalar (fixed-order final sum).
 #include "tnk_common.cuh"
+#include "tnk_tc.cuh"
 
 namespace {
 
@@ -549,6 +550,88 @@ int mp_run(const MpPlan& p, int bit_begin, double a, const Q* q, const TS* S_col
 }
 
 }  // namespace
+
+// ------------------------------------------------------------------------------------
+// High-bit pass of the symmetric tile kernel's format 2 (tnk_tc.cu): for the bit positions p >= 7
+//   u[z] = sum_p [ g_p(z) K(b_p .* q)_z + b_p(z) K(g_p .* q)_z ],   g_p = gamma (1 - s_p)(1 - 2 b_p),  K = M^{(x)n}.
+// K(b_p .* q) needs no transform of its own: with w = K q and q'_1 = K_{-p} q restricted to b_p = 1,
+// w(b_p=0) = q'_0 + a q'_1, w(b_p=1) = a q'_0 + q'_1, so K(b_p .* q)_z = (b_p(z) ? 1 : a) (w[z|p] - a w[z&~p]) / (1 - a^2).
+// ------------------------------------------------------------------------------------
+namespace {
+
+// V[0] = q, V[1 + p - p_lo] = g_p .* q for p = p_lo..n-1, and (with_c) one more vector C .* q  (fp64 [nvec][N]);
+// g and C from the fp32 tables exactly as the tile kernel forms them
+__global__ void __launch_bounds__(256)
+hib_build_kernel(int n, int np, int p_lo, int with_c, int64_t N, float gamma, const float* __restrict__ ST,
+                 const float* __restrict__ Cst, const float* __restrict__ qT, double* __restrict__ V) {
+    const int64_t z = (int64_t)blockIdx.x * 256 + threadIdx.x;
+    if (z >= N) return;
+    const double q = (double)qT[z];
+    V[z] = q;
+    for (int p = p_lo; p < n; ++p) {
+        const float v = gamma * (1.f - ST[z * np + p]);
+        V[(int64_t)(1 + p - p_lo) * N + z] = (double)(((z >> p) & 1) ? -v : v) * q;
+    }
+    if (with_c) V[(int64_t)(1 + n - p_lo) * N + z] = (double)Cst[z] * q;
+}
+
+__global__ void __launch_bounds__(256)
+hib_fold_kernel(int n, int np, int p_lo, int with_c, int64_t N, float gamma, double a, const float* __restrict__ ST,
+                const float* __restrict__ Cst, const double* __restrict__ V, double* __restrict__ u) {
+    const int64_t z = (int64_t)blockIdx.x * 256 + threadIdx.x;
+    if (z >= N) return;
+    const double inv = 1.0 / (1.0 - a * a);
+    double acc = 0.0;
+    for (int p = p_lo; p < n; ++p) {
+        const int64_t bitp = (int64_t)1 << p;
+        const bool on = (z & bitp) != 0;
+        const float v = gamma * (1.f - ST[z * np + p]);
+        const double g = (double)(on ? -v : v);
+        const double A = (on ? 1.0 : a) * (V[z | bitp] - a * V[z & ~bitp]) * inv;      // K(b_p .* q)_z from w = V[0]
+        acc += g * A;
+        if (on) acc += V[(int64_t)(1 + p - p_lo) * N + z];                            // b_p(z) K(g_p .* q)_z
+    }
+    if (with_c) acc += (double)Cst[z] * V[z] + V[(int64_t)(1 + n - p_lo) * N + z];     // sum_j a^h (C_z + C_j) q_j
+    u[z] = acc;
+}
+
+}  // namespace
+
+size_t tnk_hibits_ws_bytes(int n, int p_lo, int with_c) {
+    if (n <= p_lo && !with_c) return 0;
+    return (size_t)(1 + n - p_lo + (with_c ? 1 : 0)) * ((size_t)1 << n) * sizeof(double);
+}
+
+int tnk_hibits_pass(int n, int p_lo, int with_c, double a, double gamma, const float* ST, const float* Cst, const float* qT,
+                    double* u, double* ws, int* launches, cudaStream_t st) {
+    const int64_t N = (int64_t)1 << n;
+    const int np = ((n + 3) / 4) * 4;
+    const int nvec = 1 + n - p_lo + (with_c ? 1 : 0);
+    TNK_REQUIRE(n >= 7 && n <= 24 && p_lo >= 0 && p_lo <= n && ws, "tnk_hibits_pass: bad arguments n=%d p_lo=%d", n, p_lo);
+    const unsigned blocks = (unsigned)((N + 255) / 256);
+    hib_build_kernel<<<blocks, 256, 0, st>>>(n, np, p_lo, with_c, N, (float)gamma, ST, Cst, qT, ws);
+    TNK_CUDA_OK(cudaGetLastError());
+    TNK_CUDA_OK(cudaFuncSetAttribute(mp_transform_kernel<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMpSmem));
+    // all n bits of every vector: bits [0, min(n,13)) on contiguous tiles, the rest on 2^g x 2^(13-g) tiles
+    const int low = n < kTileLog ? n : kTileLog;
+    {
+        dim3 grid((unsigned)(N >> low), (unsigned)nvec, 1);
+        mp_transform_kernel<double><<<grid, kMpThreads, kMpSmem, st>>>(ws, N, 0, low, 0, a);
+        TNK_CUDA_OK(cudaGetLastError());
+    }
+    int nl = 2;
+    if (n > kTileLog) {
+        const int g = n - kTileLog;
+        dim3 grid((unsigned)(N >> kTileLog), (unsigned)nvec, 1);
+        mp_transform_kernel<double><<<grid, kMpThreads, kMpSmem, st>>>(ws, N, kTileLog, g, kTileLog - g, a);
+        TNK_CUDA_OK(cudaGetLastError());
+        ++nl;
+    }
+    hib_fold_kernel<<<blocks, 256, 0, st>>>(n, np, p_lo, with_c, N, (float)gamma, a, ST, Cst, ws, u);
+    TNK_CUDA_OK(cudaGetLastError());
+    if (launches) *launches += nl + 1;
+    return 0;
+}
 
 extern "C" int tnk_modeproduct_plan_limit(int max_row_bits) {
     const int prev = g_max_row_bits;

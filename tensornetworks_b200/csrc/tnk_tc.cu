@@ -572,9 +572,23 @@ tc_rows_kernel(const __grid_constant__ TcParams prm, const float* __restrict__ B
 //   A16 (rows):    s1 | s1 | s2 | g1 | g2 | bits | bits | c1 c2 c3 1 1 1        (g = gamma rho, c = C in three pieces)
 //   B16 (columns): s1 | s2 | s1 | bits | bits | g1 | g2 | 1 1 1 c1 c2 c3
 // 7 np + 6 values: 10 K-steps at n = 20 instead of 13, 320 instead of 416 table bytes per state, ~2^-17 per product.
-__host__ __device__ constexpr int tcs_k32(int nc, int fmt) { return fmt ? 0 : (3 * nc + 2) & ~1; }   // 3nc + 1 chunks, padded to even
+// Format 2 ("tile"): as format 0, but the T1/T2 terms of the bit positions p >= 7 - constant over a 128-state tile on
+// one side - leave the pair kernel altogether.  Summed over ALL columns they are Kronecker-structured,
+//     sum_j a^h(i,j) [ g_p(i) b_p(j) + b_p(i) g_p(j) ] q_j  =  g_p(i) K(b_p .* q)_i + b_p(i) K(g_p .* q)_i,     K = M^{(x)n},
+// and K(b_p .* q) follows elementwise from w = K q, so one pass of n - 6 fp64 Kronecker transforms (tnk_hibits_pass in
+// tnk_modeprod.cu, O(n^2 2^n): 0.1 ms at n = 20) seeds the accumulator u before the tile kernel adds the rest.
+//   A32: s_hi (nc) | g_hi[0..7] | bits[0..7] | [C_hi, C_lo, 1, 1]      B32: s_hi | bits[0..7] | g_hi[0..7] | [1, 1, C_hi, C_lo]
+//   A16: bf(s) | bf(s_lo) | bf(g_lo)[0..7] | bits[0..7]                B16: bf(s_lo) | bf(s) | bits[0..7] | bf(g_lo)[0..7]
+// (positions 7 of the low fields are zero).  n = 20: 5 tf32 + 4 bf16 = 9 K-steps instead of 13; n = 24: 10 instead of 16.
+// Format 3 ("dot"): only the score dot product stays: A32 = B32 = s_hi (nc), A16 = bf(s) | bf(s_lo), B16 = bf(s_lo) | bf(s);
+// C(i) + C(j) and the T1/T2 terms of every bit position go through the Kronecker pass (p_lo = 0, with_c).
+__host__ __device__ constexpr int tcs_k32(int nc, int fmt) {
+    return fmt == 1 ? 0 : fmt == 2 ? (nc + 5 + 1) & ~1 : fmt == 3 ? (nc + 1) & ~1 : (3 * nc + 2) & ~1;   // chunks, padded to even
+}
 __host__ __device__ constexpr int tcs_steps32(int nc, int fmt) { return tcs_k32(nc, fmt) / 2; }
-__host__ __device__ constexpr int tcs_steps16(int nc, int fmt) { return fmt ? (7 * 4 * nc + 6 + 15) / 16 : nc; }
+__host__ __device__ constexpr int tcs_steps16(int nc, int fmt) {
+    return fmt == 1 ? (7 * 4 * nc + 6 + 15) / 16 : fmt == 2 ? (2 * 4 * nc + 16 + 15) / 16 : fmt == 3 ? (2 * 4 * nc + 15) / 16 : nc;
+}
 __host__ __device__ constexpr int tcs_kb(int nc, int fmt) { return tcs_k32(nc, fmt) + 2 * tcs_steps16(nc, fmt); }
 
 __device__ __forceinline__ float bf_round(float x) { return __bfloat162float(__float2bfloat16_rn(x)); }
@@ -610,7 +624,59 @@ tcs_pack_kernel(int n, int np, int fmt, int64_t n_tiles, float gamma,
     };
     auto bit = [&](int p) -> float { return (p < n && ((z >> p) & 1)) ? 1.f : 0.f; };
     uint32_t w[4] = {0u, 0u, 0u, 0u};
-    if (fmt) {
+    if (fmt == 3) {
+        if (chunk < nc) {
+#pragma unroll
+            for (int e = 0; e < 4; ++e) w[e] = __float_as_uint(tf_hi(srow[4 * chunk + e]));
+        } else if (chunk >= K32) {
+            const int m = chunk - K32;
+            float v[8];
+#pragma unroll
+            for (int x = 0; x < 8; ++x) {
+                const int e = 8 * m + x;
+                v[x] = e < np ? tf_lo(srow[e]) : e < 2 * np ? srow[e - np] : 0.f;
+            }
+#pragma unroll
+            for (int e = 0; e < 4; ++e) w[e] = bf16_pack(v[2 * e], v[2 * e + 1]);
+        }
+    } else if (fmt == 2) {
+        auto low = [&](int p, bool want_bit) -> float {          // low fields: positions 0..6 only
+            if (p >= 7) return 0.f;
+            return want_bit ? bit(p) : grho(p);
+        };
+        if (chunk < nc) {
+#pragma unroll
+            for (int e = 0; e < 4; ++e) w[e] = __float_as_uint(tf_hi(srow[4 * chunk + e]));
+        } else if (chunk < nc + 4) {
+            const bool want_bit = chunk < nc + 2;
+            const int c2 = (chunk - nc) & 1;
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+                const float val = low(4 * c2 + e, want_bit);
+                w[e] = __float_as_uint(want_bit ? val : tf_hi(val));
+            }
+        } else if (chunk == nc + 4) {
+            const float C = Cst[z];
+            w[0] = w[1] = __float_as_uint(1.f);
+            w[2] = __float_as_uint(tf_hi(C));
+            w[3] = __float_as_uint(tf_lo(C));
+        } else if (chunk >= K32) {
+            const int m = chunk - K32;
+            float v[8];
+#pragma unroll
+            for (int x = 0; x < 8; ++x) {
+                const int e = 8 * m + x;
+                float val = 0.f;
+                if (e < np) val = tf_lo(srow[e]);
+                else if (e < 2 * np) val = srow[e - np];
+                else if (e < 2 * np + 8) val = low(e - 2 * np, true);
+                else if (e < 2 * np + 16) val = tf_lo(low(e - 2 * np - 8, false));
+                v[x] = val;
+            }
+#pragma unroll
+            for (int e = 0; e < 4; ++e) w[e] = bf16_pack(v[2 * e], v[2 * e + 1]);
+        }   // nc + 4 < chunk < K32: zero padding chunk
+    } else if (fmt) {
         float v[8];
 #pragma unroll
         for (int x = 0; x < 8; ++x) {
@@ -832,12 +898,31 @@ tcs_tiles_kernel(const __grid_constant__ TcsParams prm, const float* __restrict_
             const float Ci = Cst[i];
             auto bitf = [&](int p) -> float { return (p < n && ((i >> p) & 1)) ? 1.f : 0.f; };
             auto a32 = [&](int chunk, int e) -> float {
+                if (FMT == 3) return chunk < NC ? tf_hi(sv[4 * chunk + e]) : 0.f;
+                if (FMT == 2) {
+                    if (chunk < NC) return tf_hi(sv[4 * chunk + e]);
+                    if (chunk < NC + 4) {
+                        const int p = 4 * ((chunk - NC) & 1) + e;
+                        if (p >= 7) return 0.f;
+                        return chunk < NC + 2 ? tf_hi(gr[p]) : bitf(p);
+                    }
+                    if (chunk == NC + 4) return e == 0 ? tf_hi(Ci) : e == 1 ? tf_lo(Ci) : 1.f;
+                    return 0.f;
+                }
                 if (chunk > 3 * NC) return 0.f;
                 if (chunk == 3 * NC) return e == 0 ? tf_hi(Ci) : e == 1 ? tf_lo(Ci) : 1.f;
                 const int f = chunk / NC, p = 4 * (chunk - f * NC) + e;
                 return f == 0 ? tf_hi(sv[p]) : f == 1 ? tf_hi(gr[p]) : bitf(p);
             };
             auto a16 = [&](int e) -> float {
+                if (FMT == 3) return e < NP ? sv[e] : e < 2 * NP ? tf_lo(sv[e - NP]) : 0.f;
+                if (FMT == 2) {
+                    if (e < NP) return sv[e];
+                    if (e < 2 * NP) return tf_lo(sv[e - NP]);
+                    const int p = (e - 2 * NP) & 7;
+                    if (e >= 2 * NP + 16 || p >= 7) return 0.f;
+                    return e < 2 * NP + 8 ? tf_lo(gr[p]) : bitf(p);
+                }
                 const int f = e / NP, p = e - f * NP;
                 if (FMT == 0) return f == 0 ? sv[p] : f == 1 ? tf_lo(sv[p]) : f == 2 ? tf_lo(gr[p]) : bitf(p);
                 if (f < 7) {
@@ -1145,7 +1230,7 @@ int launch_sym(const TcsParams& prm, dim3 grid, const float* B_tab, const float*
 // launches the symmetric tile kernel for row tiles tile_offset + k*tile_stride, k < row_tiles.
 int tnk_tcs_launch(int n, int fmt, double gamma, const double* wl, const float* ST, const float* Cst, const float* qT,
                    int tile_offset, int tile_stride, int row_tiles, int splits, float* B_tab, int reuse_table,
-                   double* ucol, cudaEvent_t ev_start, cudaEvent_t ev_stop, int* launches,
+                   double* ucol, double* hibits_ws, cudaEvent_t ev_start, cudaEvent_t ev_stop, int* launches,
                    cudaStream_t st) {
     TNK_REQUIRE(n >= TNK_TC_MIN_LATENT && n <= TNK_TC_MAX_LATENT, "tnk_ksd_sym: n=%d outside %d..%d", n,
                 TNK_TC_MIN_LATENT, TNK_TC_MAX_LATENT);
@@ -1159,7 +1244,13 @@ int tnk_tcs_launch(int n, int fmt, double gamma, const double* wl, const float* 
         TNK_CUDA_OK(cudaGetLastError());
         if (launches) *launches += 1;
     }
-    TNK_CUDA_OK(cudaMemsetAsync(ucol, 0, (size_t)N * sizeof(double), st));
+    if ((fmt == 3 || (fmt == 2 && n > 7)) && tile_offset == 0) {
+        // the terms that left the pair kernel, for ALL rows, once (the call that owns row tile 0 adds them)
+        const int rc_hi = tnk_hibits_pass(n, fmt == 3 ? 0 : 7, fmt == 3, wl[1], gamma, ST, Cst, qT, ucol, hibits_ws, launches, st);
+        if (rc_hi) return rc_hi;
+    } else {
+        TNK_CUDA_OK(cudaMemsetAsync(ucol, 0, (size_t)N * sizeof(double), st));
+    }
     if (row_tiles <= 0) return 0;
     TcsParams prm;
     prm.n = n; prm.tile_offset = tile_offset; prm.tile_stride = tile_stride; prm.n_tiles = col_tiles;
@@ -1172,17 +1263,27 @@ int tnk_tcs_launch(int n, int fmt, double gamma, const double* wl, const float* 
     if (ev_start) TNK_CUDA_OK(cudaEventRecord(ev_start, st));
     dim3 grid((unsigned)row_tiles, (unsigned)splits, 1);
     int rc = 2;
-    switch (nc * 2 + (fmt ? 1 : 0)) {
-        case 4: rc = launch_sym<2, 0>(prm, grid, B_tab, ST, Cst, qT, ucol, st); break;
-        case 5: rc = launch_sym<2, 1>(prm, grid, B_tab, ST, Cst, qT, ucol, st); break;
-        case 6: rc = launch_sym<3, 0>(prm, grid, B_tab, ST, Cst, qT, ucol, st); break;
-        case 7: rc = launch_sym<3, 1>(prm, grid, B_tab, ST, Cst, qT, ucol, st); break;
-        case 8: rc = launch_sym<4, 0>(prm, grid, B_tab, ST, Cst, qT, ucol, st); break;
-        case 9: rc = launch_sym<4, 1>(prm, grid, B_tab, ST, Cst, qT, ucol, st); break;
-        case 10: rc = launch_sym<5, 0>(prm, grid, B_tab, ST, Cst, qT, ucol, st); break;
-        case 11: rc = launch_sym<5, 1>(prm, grid, B_tab, ST, Cst, qT, ucol, st); break;
-        case 12: rc = launch_sym<6, 0>(prm, grid, B_tab, ST, Cst, qT, ucol, st); break;
-        case 13: rc = launch_sym<6, 1>(prm, grid, B_tab, ST, Cst, qT, ucol, st); break;
+    switch (nc * 4 + fmt) {
+        case 8: rc = launch_sym<2, 0>(prm, grid, B_tab, ST, Cst, qT, ucol, st); break;
+        case 9: rc = launch_sym<2, 1>(prm, grid, B_tab, ST, Cst, qT, ucol, st); break;
+        case 10: rc = launch_sym<2, 2>(prm, grid, B_tab, ST, Cst, qT, ucol, st); break;
+        case 11: rc = launch_sym<2, 3>(prm, grid, B_tab, ST, Cst, qT, ucol, st); break;
+        case 12: rc = launch_sym<3, 0>(prm, grid, B_tab, ST, Cst, qT, ucol, st); break;
+        case 13: rc = launch_sym<3, 1>(prm, grid, B_tab, ST, Cst, qT, ucol, st); break;
+        case 14: rc = launch_sym<3, 2>(prm, grid, B_tab, ST, Cst, qT, ucol, st); break;
+        case 15: rc = launch_sym<3, 3>(prm, grid, B_tab, ST, Cst, qT, ucol, st); break;
+        case 16: rc = launch_sym<4, 0>(prm, grid, B_tab, ST, Cst, qT, ucol, st); break;
+        case 17: rc = launch_sym<4, 1>(prm, grid, B_tab, ST, Cst, qT, ucol, st); break;
+        case 18: rc = launch_sym<4, 2>(prm, grid, B_tab, ST, Cst, qT, ucol, st); break;
+        case 19: rc = launch_sym<4, 3>(prm, grid, B_tab, ST, Cst, qT, ucol, st); break;
+        case 20: rc = launch_sym<5, 0>(prm, grid, B_tab, ST, Cst, qT, ucol, st); break;
+        case 21: rc = launch_sym<5, 1>(prm, grid, B_tab, ST, Cst, qT, ucol, st); break;
+        case 22: rc = launch_sym<5, 2>(prm, grid, B_tab, ST, Cst, qT, ucol, st); break;
+        case 23: rc = launch_sym<5, 3>(prm, grid, B_tab, ST, Cst, qT, ucol, st); break;
+        case 24: rc = launch_sym<6, 0>(prm, grid, B_tab, ST, Cst, qT, ucol, st); break;
+        case 25: rc = launch_sym<6, 1>(prm, grid, B_tab, ST, Cst, qT, ucol, st); break;
+        case 26: rc = launch_sym<6, 2>(prm, grid, B_tab, ST, Cst, qT, ucol, st); break;
+        case 27: rc = launch_sym<6, 3>(prm, grid, B_tab, ST, Cst, qT, ucol, st); break;
         default: tnk_set_error("tnk_ksd_sym: no kernel instance for %d chunks", nc); break;
     }
     if (rc) return rc;

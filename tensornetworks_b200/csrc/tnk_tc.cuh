@@ -95,5 +95,13 @@ int tnk_tc_launch(int n, double a, double gamma, const double* wl, const float* 
 size_t tnk_tcs_table_bytes(int n, int fmt, int64_t states);
 int tnk_tcs_launch(int n, int fmt, double gamma, const double* wl, const float* ST, const float* Cst, const float* qT,
                    int tile_offset, int tile_stride, int row_tiles, int splits, float* B_tab, int reuse_table,
-                   double* ucol, cudaEvent_t ev_start, cudaEvent_t ev_stop, int* launches,
+                   double* ucol, double* hibits_ws, cudaEvent_t ev_start, cudaEvent_t ev_stop, int* launches,
                    cudaStream_t st);
+
+// Formats 2, 3 of the symmetric variant: u[z] = the terms of ALL pairs (z, j) that left the pair kernel - the T1/T2 terms of
+// the bit positions p >= p_lo, g_p(z) K(b_p .* q)_z + b_p(z) K(g_p .* q)_z, and (with_c) C(z) K(q)_z + K(C .* q)_z -
+// through 1 + n - p_lo (+1) fp64 Kronecker transforms (tnk_modeprod.cu).
+// ws: tnk_hibits_ws_bytes bytes.  Overwrites u (the tile kernel then adds the remaining terms).
+size_t tnk_hibits_ws_bytes(int n, int p_lo, int with_c);
+int tnk_hibits_pass(int n, int p_lo, int with_c, double a, double gamma, const float* ST, const float* Cst, const float* qT,
+                    double* u, double* ws, int* launches, cudaStream_t st);

@@ -31,6 +31,8 @@ PATHS = {
     "tc32-pairs": ("tc32", "rows", {}, 1e-4),
     "tc32-pairs_sym-tf32": ("tc32", "sym", {"split": "tf32"}, 1e-4),
     "tc32-pairs_sym-bf16x2": ("tc32", "sym", {"split": "bf16x2"}, 1e-4),
+    "tc32-pairs_sym-tf32_tile": ("tc32", "sym", {"split": "tf32_tile"}, 1e-4),
+    "tc32-pairs_sym-tf32_dot": ("tc32", "sym", {"split": "tf32_dot"}, 1e-4),
     "modeproduct-fp64": ("fp64", "mp", {"storage": "fp64"}, 1e-6),
     "modeproduct-fp32": ("tc32", "mp", {"storage": "fp32"}, 1e-4),
 }
@@ -157,6 +159,12 @@ def test_n24_symmetric_tiles_and_modeproduct_vs_cpu_oracle(ops, case24):
     K, u = _run(tabs, "sym", qd, {"split": "tf32"})
     _assert_close(K, u, Kref, uref, 1e-4)
     tabs._ws.clear()
+    tabs._sym_tables = set()
+    for split in ("tf32_tile", "tf32_dot"):
+        K, u = _run(tabs, "sym", qd, {"split": split})
+        _assert_close(K, u, Kref, uref, 1e-4)
+        tabs._ws.clear()
+        tabs._sym_tables = set()
     K, u = _run(tabs, "mp", qd, {"storage": "fp32"})
     _assert_close(K, u, Kref, uref, 1e-4)
     tabs._ws.clear()
@@ -184,7 +192,8 @@ def test_n24_pair_kernels_on_row_ranges_vs_cpu_oracle(ops, case24, precision, to
 
 
 # ------------------------------------------------------------------------------------------ ill-conditioned family
-ILL_PATHS = ["fp64-pairs", "fp64-pairs_sym64", "fp32-pairs", "tc32-pairs", "tc32-pairs_sym-tf32", "modeproduct-fp64"]
+ILL_PATHS = ["fp64-pairs", "fp64-pairs_sym64", "fp32-pairs", "tc32-pairs", "tc32-pairs_sym-tf32", "tc32-pairs_sym-tf32_tile",
+             "tc32-pairs_sym-tf32_dot", "modeproduct-fp64"]
 
 
 @pytest.mark.parametrize("path", ILL_PATHS)
@@ -226,7 +235,8 @@ def test_near_threshold_states_at_the_posterior(ops, path):
     _assert_close(K, u, Kref, uref, tol, Kscale=Kscale, uscale=uscale)
 
 
-@pytest.mark.parametrize("path", ["fp64-pairs", "fp64-pairs_sym64", "fp32-pairs", "tc32-pairs", "tc32-pairs_sym-tf32"])
+@pytest.mark.parametrize("path", ["fp64-pairs", "fp64-pairs_sym64", "fp32-pairs", "tc32-pairs", "tc32-pairs_sym-tf32",
+                                  "tc32-pairs_sym-tf32_tile", "tc32-pairs_sym-tf32_dot"])
 def test_posterior_n16(ops, path):
     """q = exact posterior at n = 16 (random family): K ~ 0 and u ~ 0 (Stein identity); compared on the scale of the
     uniform-q values, as the reference-golden Sprinkler test does."""

@@ -198,3 +198,29 @@ def test_sym_bf16x2_operands(ops, n, seed):
     assert (ua + ub - u1).abs().max().item() <= 1e-6 * scale        # fp32 chunk sums: the stripes round differently
     with pytest.raises(ValueError):
         tabs.ksd_sym(q, split="fp8")
+
+
+@pytest.mark.parametrize("split", ["tf32_tile", "tf32_dot"])
+@pytest.mark.parametrize("n,seed", [(7, 0), (8, 1), (9, 2), (10, 2), (12, 0), (13, 1), (14, 4), (16, 0), (17, 3), (18, 1)])
+def test_sym_tile_format(ops, n, seed, split):
+    """split="tf32_tile": the T1/T2 terms of the bit positions >= 7 leave the pair kernel (9 instead of 13 K-steps at
+    n = 20) and are added for all rows at once by a pass of fp64 Kronecker transforms; split="tf32_dot": only the score dot
+    product stays (6 K-steps).  Same 1e-4 mode, stripes add up, results within 5e-6 of the 13-step kernel's."""
+    bn, lat, obs, x = random_binary_bn(n, seed=seed)
+    tabs = ops.SteinTables.from_network(bn, x, lat, precision="tc32")
+    ref = ops.SteinTables.from_network(bn, x, lat, precision="fp64")
+    q = random_q(1 << n, seed=seed).cuda()
+    u0, k0 = ref.ksd_rows(q) if n <= 14 else ref.ksd_modeproduct(q)
+    u1, k1 = tabs.ksd_sym(q, split=split)
+    u2, k2 = tabs.ksd_sym(q, split="tf32")
+    parts = [tabs.ksd_sym(q, g, 3, split=split) for g in range(3)]
+    torch.cuda.synchronize()
+    scale = u0.abs().max().item()
+    assert abs(k1.item() - k0.item()) <= TOL * abs(k0.item())
+    assert (u1 - u0).abs().max().item() <= TOL * scale
+    assert (u1 - u2).abs().max().item() <= 5e-6 * scale
+    assert (sum(p[0] for p in parts) - u1).abs().max().item() <= 1e-6 * scale
+    assert abs(sum(p[1].item() for p in parts) - k1.item()) <= 1e-6 * abs(k1.item())
+    q32 = q.float()
+    u3, k3 = tabs.ksd_sym(q32, split=split)
+    assert (u3 - u1).abs().max().item() <= 1e-5 * scale

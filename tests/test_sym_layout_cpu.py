@@ -152,14 +152,82 @@ def test_transposing_exchange_lands_on_columns_2t():
 
 def test_workspace_query():
     lib = _lib.load()
-    for split in (0, 1):
+    for split in (0, 1, 2, 3):
         for n in range(7, 25):
             assert lib.tnk_ksd_sym_workspace_bytes(n, split, 0, 1) > 0
             assert lib.tnk_ksd_sym_workspace_bytes(n, split, 3, 8) > 0
         for n in (0, 6, 25, 30):
             assert lib.tnk_ksd_sym_workspace_bytes(n, split, 0, 1) == 0
     assert lib.tnk_ksd_sym_workspace_bytes(12, 0, 0, 0) == 0 and lib.tnk_ksd_sym_workspace_bytes(12, 0, -1, 2) == 0
-    assert lib.tnk_ksd_sym_workspace_bytes(12, 2, 0, 1) == 0                    # unknown operand split
+    assert lib.tnk_ksd_sym_workspace_bytes(12, 4, 0, 1) == 0                    # unknown operand split
     # n = 20: q (4 MB) + row partials + column sums (8 MB) + column table 2^20 * (26 | 20) chunks * 16 B
     assert lib.tnk_ksd_sym_workspace_bytes(20, 0, 0, 1) >= (1 << 20) * 26 * 16
     assert (1 << 20) * 20 * 16 <= lib.tnk_ksd_sym_workspace_bytes(20, 1, 0, 1) <= lib.tnk_ksd_sym_workspace_bytes(20, 0, 0, 1) - (1 << 20) * 6 * 16
+
+
+def _features_tile(S, n, length_scale=1.0):
+    """Operand format 2 ("tf32_tile"): only the T1/T2 terms of bit positions < 7 stay on the MMAs."""
+    N = 1 << n
+    np_ = (n + 3) // 4 * 4
+    a = np.exp(-1.0 / (n * length_scale))
+    alpha, gamma = 1.0 - a, a - 1.0 / a
+    z = np.arange(N)
+    s = np.zeros((N, np_), dtype=np.float32)
+    s[:, :n] = S[:, ::-1].astype(np.float32)
+    bit = np.zeros((N, np_), dtype=np.float32)
+    bit[:, :n] = (z[:, None] >> np.arange(n)[None, :]) & 1
+    valid = np.zeros(np_, dtype=np.float32)
+    valid[:n] = 1
+    g = (np.float32(gamma) * (1 - s)) * (1 - 2 * bit) * valid
+    C = (alpha * ((1 - s) * valid).sum(1) + gamma * ((1 - s) * bit).sum(1)).astype(np.float32)
+    hi, lo = _tf_hi, lambda v: np.asarray(v, dtype=np.float32) - _tf_hi(v)
+    one = np.ones(N, dtype=np.float32)
+    low = np.zeros(8, dtype=np.float32)
+    low[:7] = 1                                                   # positions 0..6 of the low fields
+    gl, bl = g[:, :8] * low, bit[:, :8] * low
+    nc = np_ // 4
+    k32 = (nc + 5 + 1) & ~1
+    pad32 = np.zeros((N, 4 * (k32 - nc - 5)), dtype=np.float32)
+    A32 = np.concatenate([hi(s), hi(gl), bl, np.stack([hi(C), lo(C), one, one], 1), pad32], 1)
+    B32 = np.concatenate([hi(s), bl, hi(gl), np.stack([one, one, hi(C), lo(C)], 1), pad32], 1)
+    s16 = (2 * np_ + 16 + 15) // 16
+    pad16 = np.zeros((N, 16 * s16 - 2 * np_ - 16), dtype=np.float32)
+    A16 = np.concatenate([_bf(s), _bf(lo(s)), _bf(lo(gl)), bl, pad16], 1)
+    B16 = np.concatenate([_bf(lo(s)), _bf(s), bl, _bf(lo(gl)), pad16], 1)
+    return A32, B32, A16, B16, g.astype(np.float64), a, k32 // 2 + s16
+
+
+@pytest.mark.parametrize("n", [8, 9, 10])
+def test_emulated_tile_format_matches_oracle(n):
+    """Format 2: MMA part (dot product, C, T terms of bits < 7) + the tile-constant terms R_i(J), c_j(I) folded into the
+    row and column sums through W q_J, W (c q_J), W q_I, W (R q_I) with W the in-tile Hamming weights."""
+    bn, lat, obs, x = random_binary_bn(n, seed=n)
+    S = orc.score_table(orc.joint_table(bn, x, lat), n)
+    q64 = random_q(1 << n, seed=n).numpy()
+    Kref, gref = orc.ksd_dense(q64, S, n)
+    N, T = 1 << n, (1 << n) // 128
+    A32, B32, A16, B16, g, a, steps = _features_tile(S, n)
+    assert steps == {8: 6, 9: 7, 10: 7}[n]                       # 13 at n = 20 becomes 9 (tnk_tc.cu: tcs_k32, tcs_steps16)
+    q = q64.astype(np.float32).astype(np.float64)
+    lowidx = np.arange(128)
+    W = a ** np.array([[bin(i ^ j).count("1") for j in lowidx] for i in lowidx], dtype=np.float64)
+    u = np.zeros(N)
+    for I in range(T):
+        ri = slice(128 * I, 128 * I + 128)
+        for J in range(I, T):
+            cj = slice(128 * J, 128 * J + 128)
+            wg = a ** bin(I ^ J).count("1")
+            D = A32[ri].astype(np.float64) @ B32[cj].astype(np.float64).T + A16[ri].astype(np.float64) @ B16[cj].astype(np.float64).T
+            Y = wg * W * D                                        # per-pair path of the epilogue
+            u[ri] += Y @ q[cj]
+            if J != I:
+                u[cj] += Y.T @ q[ri]
+            hib = [p for p in range(7, n)]
+            R = sum(((J >> (p - 7)) & 1) * g[ri, p] for p in hib) if hib else np.zeros(128)
+            c = sum(((I >> (p - 7)) & 1) * g[cj, p] for p in hib) if hib else np.zeros(128)
+            u[ri] += wg * (R * (W @ q[cj]) + W @ (c * q[cj]))     # helper warps: rows
+            if J != I:
+                u[cj] += wg * (c * (W @ q[ri]) + W @ (R * q[ri]))   # helper warps: mirrored columns
+    uref = gref / 2
+    assert np.max(np.abs(u - uref)) <= 1e-5 * np.max(np.abs(uref))
+    assert abs(q @ u - Kref) <= 1e-5 * abs(Kref)
