@@ -36,6 +36,8 @@ def parse_args():
     ap.add_argument("--algorithm", default="auto", choices=["auto", "pairs", "pairs_sym"],
                     help="pairs_sym evaluates every unordered pair of 128-state tiles once (tnk_ksd_sym / tnk_ksd_sym64); "
                          "pairs evaluates all 4^n ordered pairs (tnk_ksd_rows); auto = pairs_sym where it exists (7 <= n <= 24)")
+    ap.add_argument("--split", default=None, choices=["tf32", "bf16x2", "tf32_tile", "tf32_dot"],
+                    help="operand format of the symmetric tcgen05 kernel (default: ops.DEFAULT_SYM_SPLIT)")
     ap.add_argument("--seed", type=int, default=0)
     ap.add_argument("--exchange", default="fused", choices=["fused", "nccl"],
                     help="N>1: our own exchange over peer-mapped buffers (tnk_comm / tnk_ksd_rows_peers) or one NCCL collective")
@@ -206,6 +208,13 @@ def sym_tiles(n, rank, world):
     return sum(T - I for I in range(rank, T, world))
 
 
+def sym_steps(n, split):
+    """(tf32 K-steps, bf16 K-steps) per 128 x 128 tile of the symmetric tile kernel (csrc/tnk_tc.cu: tcs_k32, tcs_steps16)."""
+    nc = (n + 3) // 4
+    return {"tf32": (((3 * nc + 2) & ~1) // 2, nc), "bf16x2": (0, (28 * nc + 21) // 16),
+            "tf32_tile": (((nc + 6) & ~1) // 2, (8 * nc + 31) // 16), "tf32_dot": (((nc + 1) & ~1) // 2, (8 * nc + 15) // 16)}[split]
+
+
 def sym64_tiles(n, rank, world):
     """Tiles of the panel schedule of tnk_ksd_sym64 on `rank` (units dealt round-robin)."""
     from tensornetworks_b200 import _lib
@@ -273,6 +282,9 @@ def run_ours(args):
         raise SystemExit("--algorithm pairs_sym needs --precision tc32 or fp64 and 7 <= n <= 24")
     algorithm = {"tc32": "pairs_sym", "fp64": "pairs_sym64"}[args.precision] if sym_ok else "pairs"
     sym = algorithm != "pairs"
+    sym_split = args.split or ops.DEFAULT_SYM_SPLIT
+    if args.split:
+        ops.DEFAULT_SYM_SPLIT = args.split           # the public op (e2e) follows
 
     exchange, exchange_name = None, "none (single GPU)"
     if world > 1:
@@ -293,7 +305,7 @@ def run_ours(args):
         if sym:
             out = (exchange.sendbuf[:N], exchange.sendbuf[N:N + 1]) if exchange is not None else None
             if algorithm == "pairs_sym":
-                u, part = tables.ksd_sym(q_dev, *ops.sym_tile_stripe(rank, world), out=out)   # row tiles rank, rank + world, ...
+                u, part = tables.ksd_sym(q_dev, *ops.sym_tile_stripe(rank, world), split=sym_split, out=out)   # row tiles rank, rank + world, ...
             else:
                 u, part = tables.ksd_sym64(q_dev, rank, world, out=out)                        # units rank, rank + world, ...
             if exchange is not None:
@@ -353,8 +365,11 @@ def run_ours(args):
         e2e_step()
     barrier()
     t0 = time.perf_counter()
+    e2e_ms = []
     for _ in range(args.steps):
+        t_step = time.perf_counter()
         K_e2e, grad_host = e2e_step()
+        e2e_ms.append((time.perf_counter() - t_step) * 1e3)
     barrier()
     e2e_value = pairs / (max_over_ranks(time.perf_counter() - t0) / args.steps)
     clocks = sampler.stop(t_region_begin, time.time())   # samples under load: device-timed and end-to-end regions
@@ -377,6 +392,17 @@ def run_ours(args):
 
     ctx = {}
     if not args.no_context:
+        # ---- the other operand formats of the symmetric tile kernel on this rank's stripe
+        if algorithm == "pairs_sym":
+            variants = {}
+            for sp in ("tf32", "tf32_tile", "tf32_dot"):
+                if sp == sym_split:
+                    variants[sp] = kernel_ms
+                    continue
+                variants[sp], _ = time_kernel(lambda: tables.ksd_sym(q_dev, *ops.sym_tile_stripe(rank, world), split=sp))
+                tables._ws.pop(("sym", rank, world, sp), None)
+                tables._sym_tables.discard(("sym", rank, world, sp))
+            ctx["variants"] = variants
         # ---- the all-pairs tile kernel (tnk_ksd_rows, precision tc32) on this rank's rows
         if args.precision == "tc32" and sym:
             full_ms, (u_full, _) = time_kernel(lambda: tables.ksd_rows(q_dev, r0, r1))
@@ -468,8 +494,9 @@ def run_ours(args):
             torch.cuda.empty_cache()
             ctx["config5"] = bench_config5(device, world, rank, max_over_ranks)
     return dict(world=world, rank=rank, n=n, pairs=pairs, value=value, ms_per_step=ms_per_step, kernel_ms=kernel_ms,
-                K_value=K_value, u=u, e2e_value=e2e_value, launches=launches, clocks=clocks, peak_rate=peak_rate,
-                algorithm=algorithm, sym=sym, exchange_name=exchange_name, ctx=ctx, peaks=peaks, exchange=exchange)
+                K_value=K_value, u=u, e2e_value=e2e_value, e2e_ms=e2e_ms, step_ms=[a.elapsed_time(b) for a, b in ev], launches=launches, clocks=clocks, peak_rate=peak_rate,
+                algorithm=algorithm, sym=sym, sym_split=sym_split, exchange_name=exchange_name, ctx=ctx, peaks=peaks,
+                exchange=exchange)
 
 
 def bench_config3(ops, device, flush, time_kernel, args):
@@ -575,12 +602,10 @@ def main():
         hbm = peaks.get("hbm_gbs") or 6650.0
         if r["algorithm"] == "pairs_sym":
             tiles = sym_tiles(n, 0, world)
-            nc = (n + 3) // 4
-            s32, s16 = ((3 * nc + 2) & ~1) // 2, nc
+            s32, s16 = sym_steps(n, r["sym_split"])
             flops_tile = 128 * 128 * 2 * 8 * (s32 + s16)
             peak_tf, burst_tf, src = tensor_peak(peaks)
             ach_tf = tiles * flops_tile / kernel_s / 1e12
-            useful_tf = tiles * 128 * 128 * 2 * 8 * ((3 * n + 2 + 7) // 8) / kernel_s / 1e12
             roofline = {"bound": "tensor", "achieved": ach_tf, "peak": peak_tf, "unit": "TFLOP/s",
                         "frac": ach_tf / peak_tf, "traffic": None, "kernel": "tcs_tiles_kernel",
                         "kernel_ms": r["kernel_ms"], "executed_tiles_128x128": tiles,
@@ -588,8 +613,11 @@ def main():
                         "ordered_pairs_per_executed_pair": (pairs / world) / (tiles * 16384.0),
                         "k_steps_tf32": s32, "k_steps_bf16": s16, "peak_source": src,
                         "frac_of_burst_peak": ach_tf / burst_tf, "burst_peak": burst_tf,
-                        "algorithmic_frac": useful_tf / peak_tf,
-                        "algorithmic_note": f"rank 3n+2 = {3 * n + 2} bracket = {(3 * n + 2 + 7) // 8} tf32 K-steps of the {s32 + s16} issued"}
+                        "operand_format": r["sym_split"],
+                        "note": ("format tf32_dot keeps only the rank-n score dot product on the MMAs (3 tf32 + 3 bf16 K-steps: the 3xTF32 "
+                                 "split of ceil(n/8) algorithmic K-steps); C(z)+C(z') and the T1/T2 terms are added exactly by n+2 fp64 "
+                                 "Kronecker transforms before the tile kernel. With 6 K-steps the kernel is bound by the accumulator "
+                                 "read-out (tmem_readout below), not by the MMA rate: see tile_kernel_variants for the 13- and 9-step formats")}
             if roofline["frac"] > 1.0:
                 roofline["frac_note"] = "above 1: the sustained peak is a matmul-loop average; see frac_of_burst_peak"
             # second limit of the same kernel: every accumulator tile (64 KB of fp32) leaves TMEM once through
@@ -598,6 +626,7 @@ def main():
             if sm_mhz:
                 tmem_peak = 148 * 64.0 * sm_mhz * 1e6                      # B/s at the clock measured under load
                 tmem_ach = tiles * 65536.0 / kernel_s
+                roofline["binding_limit"] = "tmem_readout" if tmem_ach / tmem_peak > roofline["frac"] else "tensor"
                 roofline["tmem_readout"] = {"achieved_TB/s": tmem_ach / 1e12, "peak_TB/s": tmem_peak / 1e12,
                                             "frac": tmem_ach / tmem_peak, "bytes_per_tile": 65536,
                                             "peak_source": "148 SMs x 64 B/clk x median SM clock of this run"}
@@ -649,7 +678,7 @@ def main():
             "config": config_of(n),
             "run": {"precision_mode": {"fp32": "fp32-compute/fp64-accumulate", "fp64": "fp64",
                                        "tc32": "3xTF32 tensor-core tiles (fp32 accumulate per tile, fp64 across tiles)"}[args.precision],
-                    "algorithm": r["algorithm"],
+                    "algorithm": r["algorithm"] + (f" (operand format {r['sym_split']})" if r["algorithm"] == "pairs_sym" else ""),
                     "parallelism": ((f"row tiles / units dealt round-robin x{world}" if r["sym"] else f"row-sharded x{world}")
                                     if world > 1 else "single GPU"),
                     "exchange": r["exchange_name"],
@@ -660,9 +689,20 @@ def main():
             "executed_pairs_per_s": roofline.get("executed_pairs_per_s"),
             "roofline": roofline,
             "e2e": {"value": r["e2e_value"], "unit": UNIT, "h2d_bytes_per_step": 8 * N * world,
-                    "d2h_bytes_per_step": (8 * N + 8) * world, "frac_of_device_timed": r["e2e_value"] / r["value"]},
+                    "d2h_bytes_per_step": (8 * N + 8) * world, "frac_of_device_timed": r["e2e_value"] / r["value"],
+                    "ms_per_step_rank0": r["e2e_ms"], "device_timed_ms_per_step_rank0": r["step_ms"]},
             "gpu_launches": r["launches"], "clocks": r["clocks"], "ksd_sq": r["K_value"],
         }
+        if "variants" in ctx:
+            tiles_v = sym_tiles(n, 0, world)
+            pk, _, _ = tensor_peak(peaks)
+            line["tile_kernel_variants"] = {
+                sp: {"kernel_ms": ms, "k_steps": sum(sym_steps(n, sp)), "value": pairs / (ms * 1e-3),
+                     "issued_TFLOP/s": tiles_v * 128 * 128 * 16 * sum(sym_steps(n, sp)) / (ms * 1e-3) / 1e12,
+                     "frac_of_tensor_peak": tiles_v * 128 * 128 * 16 * sum(sym_steps(n, sp)) / (ms * 1e-3) / 1e12 / pk}
+                for sp, ms in ctx["variants"].items()}
+            line["tile_kernel_variants"]["note"] = ("tf32: whole bracket on the MMAs; tf32_tile: T1/T2 terms of bits >= 7 through the "
+                                                    "Kronecker pass; tf32_dot: only the score dot product on the MMAs (headline)")
         if "full_ms" in ctx:
             line["full_tile_kernel"] = {"kernel": "tc_rows_kernel (all 4^n ordered pairs, tnk_ksd_rows precision tc32)",
                                         "kernel_ms": ctx["full_ms"], "value": pairs / (ctx["full_ms"] * 1e-3), "unit": UNIT,

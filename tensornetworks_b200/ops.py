@@ -18,6 +18,7 @@ from .flatten import flatten_bn
 
 PRECISIONS = {"fp64": _lib.PREC_FP64, "fp32": _lib.PREC_FP32, "fp64_simple": _lib.PREC_FP64_SIMPLE,
               "tc32": _lib.PREC_TC32}
+DEFAULT_SYM_SPLIT = "tf32_dot"     # operand format of algorithm "pairs_sym" (SteinTables.ksd_sym)
 launch_counter = {"kernels": 0}  # kernels of ours enqueued since last reset (bench.py's gpu_launches)
 
 
@@ -143,14 +144,19 @@ class SteinTables:
         return u, part
 
 
-    def ksd_sym(self, q, tile_offset=0, tile_stride=1, split="tf32", out=None):
+    def ksd_sym(self, q, tile_offset=0, tile_stride=1, split=None, out=None):
         """Symmetric tensor-core evaluation (tnk_ksd_sym): every unordered pair of 128-state tiles is evaluated
         once and feeds both its row tile and, mirrored, its column tile.  This call owns the row tiles
         tile_offset + k*tile_stride; returns (u_partial [N] fp64, part [1] fp64) whose sums over all offsets of
         one stride are u = K_p q and KSD^2.  Needs the fp32 tables (precision "tc32" or "fp32"), 7 <= n <= 24.
-        split: "tf32" = tf32 high parts + bf16 cross terms (errors of the tc32 kernel, ~1e-6), "bf16x2" = two bf16
-        pieces per factor (fewer MMA K-steps, errors ~1e-5).
+        split: operand format of the tile kernel (default DEFAULT_SYM_SPLIT = "tf32_dot"):
+          "tf32"      the whole bracket on the MMAs, tf32 high parts + bf16 cross terms (13 K-steps at n = 20, errors ~1e-6)
+          "bf16x2"    the whole bracket, two bf16 pieces per factor (10 K-steps, errors ~1e-5)
+          "tf32_tile" the T1/T2 terms of the bit positions >= 7 leave the pair kernel (9 K-steps)
+          "tf32_dot"  only the score dot product stays in the pair kernel (6 K-steps); for both, the removed terms are
+                      added for all rows by a pass of fp64 Kronecker transforms (O(n^2 2^n), in the call owning tile 0).
         out: optional (u [N], part [1]) fp64 device tensors to write into (e.g. views of PeerComm.sendbuf)."""
+        split = DEFAULT_SYM_SPLIT if split is None else split
         if split not in _lib.SYM_SPLIT:
             raise ValueError(f"split must be one of {tuple(_lib.SYM_SPLIT)}")
         code = _lib.SYM_SPLIT[split]
