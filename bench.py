@@ -634,14 +634,15 @@ def main():
         elif r["algorithm"] == "pairs_sym64":
             tiles = sym64_tiles(n, 0, world)
             steps = (n + 3) // 4
-            lane_pair = 4 * steps + 5.5
+            lane_pair = 4 * steps + 2.75
             achieved = tiles * 16384.0 * lane_pair / kernel_s
             roofline = {"bound": "alu", "achieved": achieved / 1e12, "peak": r["peak_rate"] / 1e12, "unit": "Tlane-op/s",
                         "frac": achieved / r["peak_rate"], "traffic": None, "kernel": "sym64_kernel",
                         "kernel_ms": r["kernel_ms"], "executed_tiles_128x128": tiles,
                         "executed_pairs_per_s": tiles * 16384.0 / kernel_s,
                         "lane_ops_per_executed_pair": lane_pair,
-                        "lane_ops_note": f"{steps} DMMA K-steps x 4 + 2.75 DADD + 0.75 DMUL + 2 DFMA; DMMA and DFMA share one fp64 pipe (ncu pipe_shared)",
+                        "lane_ops_note": f"{steps} DMMA K-steps x 4 (score dot product) + 0.75 DMUL + 2 DFMA; DMMA and DFMA share one fp64 pipe (ncu pipe_shared); "
+                                         "C(z)+C(z') and the T1/T2 terms come from n+2 fp64 Kronecker transforms outside the pair kernel",
                         "frac_at_survey_w": tiles * 16384.0 * w_lane / kernel_s / r["peak_rate"],
                         "peak_source": "tnk_alu_peak DFMA-chain probe measured in this run (MEASURED_PEAKS.json has no fp64 peak)"}
             tag = "sym64"
@@ -718,7 +719,7 @@ def main():
         if "fp64_sym_ms" in ctx:
             tiles64 = sym64_tiles(n, 0, world)
             steps = (n + 3) // 4
-            lane_pair = 4 * steps + 5.5
+            lane_pair = 4 * steps + 2.75
             s64, r64 = ctx["fp64_sym_ms"] * 1e-3, ctx["fp64_rows_ms"] * 1e-3
             line["fp64_kernel"] = {
                 "mode": "fp64 (the north_star's 1e-6 mode)", "kernel": "sym64_kernel (tnk_ksd_sym64: symmetric tiles, DMMA score dot product, deterministic)",

@@ -560,24 +560,26 @@ int mp_run(const MpPlan& p, int bit_begin, double a, const Q* q, const TS* S_col
 namespace {
 
 // V[0] = q, V[1 + p - p_lo] = g_p .* q for p = p_lo..n-1, and (with_c) one more vector C .* q  (fp64 [nvec][N]);
-// g and C from the fp32 tables exactly as the tile kernel forms them
+// g and C from the packed tables in their own type (fp32: exactly as the tile kernel forms them; fp64 for tnk_ksd_sym64)
+template <typename TS>
 __global__ void __launch_bounds__(256)
-hib_build_kernel(int n, int np, int p_lo, int with_c, int64_t N, float gamma, const float* __restrict__ ST,
-                 const float* __restrict__ Cst, const float* __restrict__ qT, double* __restrict__ V) {
+hib_build_kernel(int n, int np, int p_lo, int with_c, int64_t N, TS gamma, const TS* __restrict__ ST,
+                 const TS* __restrict__ Cst, const TS* __restrict__ qT, double* __restrict__ V) {
     const int64_t z = (int64_t)blockIdx.x * 256 + threadIdx.x;
     if (z >= N) return;
     const double q = (double)qT[z];
     V[z] = q;
     for (int p = p_lo; p < n; ++p) {
-        const float v = gamma * (1.f - ST[z * np + p]);
+        const TS v = gamma * ((TS)1 - ST[z * np + p]);
         V[(int64_t)(1 + p - p_lo) * N + z] = (double)(((z >> p) & 1) ? -v : v) * q;
     }
     if (with_c) V[(int64_t)(1 + n - p_lo) * N + z] = (double)Cst[z] * q;
 }
 
+template <typename TS>
 __global__ void __launch_bounds__(256)
-hib_fold_kernel(int n, int np, int p_lo, int with_c, int64_t N, float gamma, double a, const float* __restrict__ ST,
-                const float* __restrict__ Cst, const double* __restrict__ V, double* __restrict__ u) {
+hib_fold_kernel(int n, int np, int p_lo, int with_c, int64_t N, TS gamma, double a, const TS* __restrict__ ST,
+                const TS* __restrict__ Cst, const double* __restrict__ V, double* __restrict__ u) {
     const int64_t z = (int64_t)blockIdx.x * 256 + threadIdx.x;
     if (z >= N) return;
     const double inv = 1.0 / (1.0 - a * a);
@@ -585,7 +587,7 @@ hib_fold_kernel(int n, int np, int p_lo, int with_c, int64_t N, float gamma, dou
     for (int p = p_lo; p < n; ++p) {
         const int64_t bitp = (int64_t)1 << p;
         const bool on = (z & bitp) != 0;
-        const float v = gamma * (1.f - ST[z * np + p]);
+        const TS v = gamma * ((TS)1 - ST[z * np + p]);
         const double g = (double)(on ? -v : v);
         const double A = (on ? 1.0 : a) * (V[z | bitp] - a * V[z & ~bitp]) * inv;      // K(b_p .* q)_z from w = V[0]
         acc += g * A;
@@ -602,14 +604,19 @@ size_t tnk_hibits_ws_bytes(int n, int p_lo, int with_c) {
     return (size_t)(1 + n - p_lo + (with_c ? 1 : 0)) * ((size_t)1 << n) * sizeof(double);
 }
 
-int tnk_hibits_pass(int n, int p_lo, int with_c, double a, double gamma, const float* ST, const float* Cst, const float* qT,
-                    double* u, double* ws, int* launches, cudaStream_t st) {
+int tnk_hibits_pass(int n, int p_lo, int with_c, double a, double gamma, const void* ST, const void* Cst, const void* qT,
+                    int elem_bytes, double* u, double* ws, int* launches, cudaStream_t st) {
     const int64_t N = (int64_t)1 << n;
     const int np = ((n + 3) / 4) * 4;
     const int nvec = 1 + n - p_lo + (with_c ? 1 : 0);
     TNK_REQUIRE(n >= 7 && n <= 24 && p_lo >= 0 && p_lo <= n && ws, "tnk_hibits_pass: bad arguments n=%d p_lo=%d", n, p_lo);
     const unsigned blocks = (unsigned)((N + 255) / 256);
-    hib_build_kernel<<<blocks, 256, 0, st>>>(n, np, p_lo, with_c, N, (float)gamma, ST, Cst, qT, ws);
+    if (elem_bytes == 4)
+        hib_build_kernel<float><<<blocks, 256, 0, st>>>(n, np, p_lo, with_c, N, (float)gamma, (const float*)ST, (const float*)Cst,
+                                                        (const float*)qT, ws);
+    else
+        hib_build_kernel<double><<<blocks, 256, 0, st>>>(n, np, p_lo, with_c, N, gamma, (const double*)ST, (const double*)Cst,
+                                                         (const double*)qT, ws);
     TNK_CUDA_OK(cudaGetLastError());
     TNK_CUDA_OK(cudaFuncSetAttribute(mp_transform_kernel<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMpSmem));
     // all n bits of every vector: bits [0, min(n,13)) on contiguous tiles, the rest on 2^g x 2^(13-g) tiles
@@ -627,7 +634,10 @@ int tnk_hibits_pass(int n, int p_lo, int with_c, double a, double gamma, const f
         TNK_CUDA_OK(cudaGetLastError());
         ++nl;
     }
-    hib_fold_kernel<<<blocks, 256, 0, st>>>(n, np, p_lo, with_c, N, (float)gamma, a, ST, Cst, ws, u);
+    if (elem_bytes == 4)
+        hib_fold_kernel<float><<<blocks, 256, 0, st>>>(n, np, p_lo, with_c, N, (float)gamma, a, (const float*)ST, (const float*)Cst, ws, u);
+    else
+        hib_fold_kernel<double><<<blocks, 256, 0, st>>>(n, np, p_lo, with_c, N, gamma, a, (const double*)ST, (const double*)Cst, ws, u);
     TNK_CUDA_OK(cudaGetLastError());
     if (launches) *launches += nl + 1;
     return 0;

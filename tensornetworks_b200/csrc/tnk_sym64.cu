@@ -4,27 +4,29 @@
 // into 128 x 128-state tiles and every unordered pair of tiles (I <= J) is evaluated once: its values feed the rows of
 // tile I and, mirrored, the rows of tile J.  Per pair (closed form of tnk_ksd.cu / DESIGN.md section 2)
 //     Y(i,j) = a^popc(i^j) * [ s(i).s(j) + C(i) + C(j) + T1(i,j) + T2(i,j) ],   T1 = sum_p g_p(i) b_p(j) = T2(j,i),
-// with g_p(z) = gamma * (1 - s_p(z)) * (1 - 2 b_p(z)).
+// with g_p(z) = gamma * (1 - s_p(z)) * (1 - 2 b_p(z)).  Only the rank-n term s(i).s(j) needs the pair space: summed over
+// all j, the other terms are Kronecker-structured (C(i) K(q)_i + K(C.q)_i + sum_p [g_p(i) K(b_p.q)_i + b_p(i) K(g_p.q)_i],
+// K = M^{(x)n}) and are added for all rows by n + 2 fp64 transforms before the pair kernel (tnk_hibits_pass,
+// tnk_modeprod.cu: O(n^2 2^n)).
 //
-// Arithmetic.  The score dot product and the T1/T2 terms of bit positions 3 and 4 run as fp64 tensor-core MMAs
-// (mma.sync.m8n8k4.f64 = DMMA: NP/4 + 1 K-steps per 8 x 8 pairs; the probe scripts/probes/dmma_rate.cu shows DMMA
-// and DFMA share one pipe at about the same FMA rate, so the gain is issue slots, register and shared-memory
-// traffic, not flops).  A warp owns 32 rows (A fragments resident in registers for a whole row tile) and walks
-// 32-column blocks in two batches of 16 columns; the accumulator fragment gives thread t the rows t/4 + 8a
-// (a = 0..3) and the columns 2(t%4) + e + 8b (e = 0,1; b = 0..3) of the block.  Every index bit that is not a/b is
-// constant per thread, warp, block or tile, so the remaining T1/T2 terms and C(i) + C(j) arrive as ONE add per pair
-// (the accumulator seed Erow[a][e] + Ecol[b][e]) and the Hamming weight as one multiply by a^popc(a^b) (a compile-
-// time constant after unrolling) - the rest of the weight is folded into q_j, into the column sums and into one
-// factor per block.  Per executed pair: 4 (NP/4) DMMA lane-FMAs + ~2.75 DADD + 0.75 DMUL + 2 DFMA.
+// Arithmetic of the pair kernel.  The score dot product runs as fp64 tensor-core MMAs (mma.sync.m8n8k4.f64 = DMMA:
+// NP/4 K-steps per 8 x 8 pairs; the probe scripts/probes/dmma_rate.cu and ncu's pipe_shared counter show DMMA and DFMA
+// share one pipe at about the same FMA rate, so the gain is issue slots, register and shared-memory traffic, not
+// flops).  A warp owns 32 rows (A fragments resident in registers for a whole row tile) and walks its 64 columns in
+// 8 batches of 8; the accumulator fragment gives thread t the rows t/4 + 8a (a = 0..3) and the columns 2(t%4) + e
+// + 8b of a 32-column block.  The Hamming weight is one multiply by a^popc(a^b) (a compile-time constant after
+// unrolling, 1 for a quarter of the pairs) - the rest of the weight is folded into q_j and into the column sums.
+// Per executed pair: 4 (NP/4) DMMA lane-FMAs + 0.75 DMUL + 2 DFMA.
 //
 // Schedule and determinism.  The T = N/128 tiles are grouped into B <= 128 panels of s tiles; a work unit is a
 // panel pair (pa <= pb) handled by one CTA: for every row tile I of pa it sweeps the column tiles J of pb (J >= I on
 // the diagonal).  Row sums stay in registers over a sweep and are stored once into RowPart[pb][rows of I]; the
 // mirrored column sums of a tile are added over the CTA's 32 row groups in shared memory in a fixed order and then
 // accumulated into ColPart[pa][cols of J] by the same thread every time (first a plain store, afterwards
-// red.global.add.f64 from that one thread: same-address program order).  tnk_sym64 finish kernel adds the slots in a
+// red.global.add.f64 from that one thread: same-address program order).  The finish kernel adds the slots in a
 // fixed order: the result is bit-reproducible run to run (the tcgen05 tile kernel's is not).
 #include "tnk_common.cuh"
+#include "tnk_tc.cuh"
 #include <stdlib.h>
 
 namespace {
@@ -90,20 +92,15 @@ __host__ __device__ inline int64_t panels_to_unit(int pa, int pb, int B) {
 template <int NP, int RB>
 struct Smem64 {
     static constexpr int DOT = NP / 4;                  // K-steps of the score dot product
-    static constexpr int STAGES = 3;                    // column-tile buffers: computing t, tables of t+1, copy of t+2 in flight
+    static constexpr int STAGES = 3;                    // column-tile buffers: computing t, copies of t+1 and t+2 in flight
     static constexpr int NWR = 16 / RB;                 // row groups (warps along the rows) of the 128-row tile
     static constexpr int GROUPS = 8 * NWR;              // partial column sums per column: one per (row group, r)
     static constexpr size_t raw_bytes = (size_t)kTile * NP * sizeof(double);
-    static constexpr size_t buf_bytes = raw_bytes + 2 * kTile * sizeof(double);      // raw | Cst | q
-    // per-tile tables: colA [NWR][128] | colB [8][136] (rows padded: conflict-free 16-byte loads across r) | colG [128][2] | trow [128]
-    static constexpr size_t tab_bytes = ((size_t)(NWR + 2 + 1) * kTile + 8 * kStageStride) * sizeof(double);
+    static constexpr size_t buf_bytes = raw_bytes + kTile * sizeof(double);          // raw | q
     static constexpr size_t stage_bytes = (size_t)GROUPS * kStageStride * sizeof(double);
     static constexpr size_t off_buf = 0;
-    static constexpr size_t off_stage = off_buf + STAGES * buf_bytes;                 // one stage (arrive/sync protocol)
-    static constexpr size_t off_tab = off_stage + stage_bytes;                        // [2] table sets
-    static constexpr size_t off_rowg = off_tab + 2 * tab_bytes;                       // [17][128]: g_p of the rows, p >= 7
-    static constexpr size_t off_rowc = off_rowg + (size_t)17 * kTile * sizeof(double);     // [4][128]: g_0, g_3, g_4, g_5 of the rows
-    static constexpr size_t off_rowred = off_rowc + (size_t)4 * kTile * sizeof(double);    // [2][128]
+    static constexpr size_t off_stage = off_buf + STAGES * buf_bytes;                 // one stage (arrive/wait protocol)
+    static constexpr size_t off_rowred = off_stage + stage_bytes;                     // [2][128]
     static constexpr size_t off_wl = off_rowred + (size_t)2 * kTile * sizeof(double);      // [32]
     static constexpr size_t off_bar = off_wl + 32 * sizeof(double);
     static constexpr size_t total = off_bar + 8 * (STAGES + 1);
@@ -112,17 +109,14 @@ struct Smem64 {
 
 template <int NP, int RB>
 __global__ void __launch_bounds__(64 * (16 / RB), 1)
-sym64_kernel(const Sym64Params prm, const double* __restrict__ ST, const double* __restrict__ Cst,
-             const double* __restrict__ qT, double* __restrict__ RowPart, double* __restrict__ ColPart) {
+sym64_kernel(const Sym64Params prm, const double* __restrict__ ST, const double* __restrict__ qT,
+             double* __restrict__ RowPart, double* __restrict__ ColPart) {
     using SM = Smem64<NP, RB>;
     constexpr int DOT = SM::DOT, STAGES = SM::STAGES, NWR = SM::NWR, GROUPS = SM::GROUPS;
     constexpr int THREADS = 64 * NWR;
-    constexpr int ABITS = RB == 4 ? 2 : 1;           // row bits 3.. held by the row-block index a; the rest belong to wr
     static_assert(RB == 2 || RB == 4, "row blocks per warp");
     extern __shared__ __align__(128) unsigned char smem[];
     double* stage = reinterpret_cast<double*>(smem + SM::off_stage);
-    double* rowg = reinterpret_cast<double*>(smem + SM::off_rowg);
-    double* rowc = reinterpret_cast<double*>(smem + SM::off_rowc);
     double* rowred = reinterpret_cast<double*>(smem + SM::off_rowred);
     double* sWl = reinterpret_cast<double*>(smem + SM::off_wl);
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + SM::off_bar);
@@ -133,7 +127,7 @@ sym64_kernel(const Sym64Params prm, const double* __restrict__ ST, const double*
     const int rowbase = wr * 8 * RB + r;           // + 8a: this thread's rows inside the tile
     const int n = prm.n;
     const int64_t N = (int64_t)1 << n;
-    const double gam = prm.gamma, av = prm.a;
+    const double av = prm.a;
 
     int pa, pb;
     unit_to_panels(prm.unit_offset + (int)blockIdx.x * prm.unit_stride, prm.B, &pa, &pb);
@@ -157,72 +151,12 @@ sym64_kernel(const Sym64Params prm, const double* __restrict__ ST, const double*
     auto advance = [&](int& I, int& J) {
         if (++J == J_end) { ++I; J = diag ? I : pb * s; }
     };
-    auto issue_tile = [&](int J, uint32_t t) {      // one thread: three bulk copies on the buffer's barrier
+    auto issue_tile = [&](int J, uint32_t t) {      // one thread: two bulk copies on the buffer's barrier
         const int buf = (int)(t % STAGES);
         unsigned char* dst = smem + SM::off_buf + (size_t)buf * SM::buf_bytes;
         mbar_expect_tx(&bars[buf], (uint32_t)SM::buf_bytes);
         bulk_g2s(dst, ST + (size_t)J * kTile * NP, (uint32_t)SM::raw_bytes, &bars[buf]);
-        bulk_g2s(dst + SM::raw_bytes, Cst + (size_t)J * kTile, kTile * sizeof(double), &bars[buf]);
-        bulk_g2s(dst + SM::raw_bytes + kTile * sizeof(double), qT + (size_t)J * kTile, kTile * sizeof(double), &bars[buf]);
-    };
-    // Per-tile tables of tile (I, J) = sequence number t, built one tile ahead by 128-thread parts:
-    //   colA[w][c] = C(c) + sum_{p>=7} b_p(I) g_p(c) + sum over the row bits held by the row group w (bits 3+ABITS..6) of g_p(c)
-    //   colB[r][c] = sum_{p<3} b_p(r) g_p(c);   colG[c][0..1] = g_3(c), g_4(c)
-    //   trow[row]  = C(row) + sum_{p>=7} g_p(row) b_p(J)     (from the row tile's rowg table; Ic = row tile it belongs to)
-    auto build_tables = [&](int I, int J, uint32_t t, bool rows_ready) {
-        const int buf = (int)(t % STAGES);
-        mbar_wait(&bars[buf], (t / STAGES) & 1);
-        const unsigned char* bufp = smem + SM::off_buf + (size_t)buf * SM::buf_bytes;
-        const double* raw = reinterpret_cast<const double*>(bufp);
-        const double* cC = reinterpret_cast<const double*>(bufp + SM::raw_bytes);
-        double* colA = reinterpret_cast<double*>(smem + SM::off_tab + (size_t)(t & 1) * SM::tab_bytes);
-        double* colB = colA + NWR * kTile;
-        double* colG = colB + 8 * kStageStride;
-        double* trow = colG + 2 * kTile;
-        const int c = tid & (kTile - 1), part = tid >> 7;
-        const int64_t j = (int64_t)J * kTile + c;
-        const double* sc = raw + c * NP;
-        auto gcol = [&](int p) -> double {
-            const double v = gam * (1.0 - sc[p]);
-            return ((j >> p) & 1) ? -v : v;
-        };
-        if (part == 0) {
-            double e = cC[c];
-#pragma unroll 4
-            for (int p = 7; p < n; ++p) {          // fixed trip count: the loads do not wait for the adds
-                const double gp = gcol(p);
-                e += ((I >> (p - 7)) & 1) ? gp : 0.0;
-            }
-            if (RB == 4) {
-                const double c5 = gcol(5), c6 = gcol(6);
-                colA[0 * kTile + c] = e;
-                colA[1 * kTile + c] = e + c5;
-                colA[2 * kTile + c] = e + c6;
-                colA[3 * kTile + c] = (e + c5) + c6;
-            } else {
-                const double c4 = gcol(4), c5 = gcol(5), c6 = gcol(6);
-#pragma unroll
-                for (int w = 0; w < 8; ++w)
-                    colA[w * kTile + c] = ((e + ((w & 1) ? c4 : 0.0)) + ((w & 2) ? c5 : 0.0)) + ((w & 4) ? c6 : 0.0);
-            }
-        }
-        if (part == 1) {
-            const double c0 = gcol(0), c1 = gcol(1), c2 = gcol(2);
-#pragma unroll
-            for (int rr = 0; rr < 8; ++rr)
-                colB[rr * kStageStride + c] = ((rr & 1) ? c0 : 0.0) + ((rr & 2) ? c1 : 0.0) + ((rr & 4) ? c2 : 0.0);
-            colG[2 * c] = gcol(3);
-            colG[2 * c + 1] = gcol(4);
-        }
-        if (part == (THREADS > 256 ? 2 : 1) && rows_ready) {
-            double e = Cst[(int64_t)I * kTile + c];
-#pragma unroll 4
-            for (int p = 7; p < n; ++p) {
-                const double gp = rowg[(p - 7) * kTile + c];
-                e += ((J >> (p - 7)) & 1) ? gp : 0.0;
-            }
-            trow[c] = e;
-        }
+        bulk_g2s(dst + SM::raw_bytes, qT + (size_t)J * kTile, kTile * sizeof(double), &bars[buf]);
     };
     // Column sums of a finished tile: THREADS/128 threads per column, each adding 16 of the GROUPS row groups as four
     // independent chains; fixed order -> deterministic.
@@ -259,7 +193,7 @@ sym64_kernel(const Sym64Params prm, const double* __restrict__ ST, const double*
     }
 
     double Af[DOT][RB];
-    double qi[RB], rbase[RB];
+    double qi[RB];
     double rsum[RB];
 #pragma unroll
     for (int a = 0; a < RB; ++a) rsum[a] = 0.0;
@@ -268,15 +202,14 @@ sym64_kernel(const Sym64Params prm, const double* __restrict__ ST, const double*
     bool pend_first = false;
 
     for (uint32_t t = 0; t < n_tiles; ++t) {
-        __syncthreads();      // S_t: tile t-1 fully consumed; its stage complete; tables of t visible; buffer (t+2)%3 free
+        __syncthreads();      // S_t: tile t-1 fully consumed; its stage complete; buffer (t+2)%3 free
         if (pend_J >= 0) { flush_stage(pend_J, pend_first); pend_J = -1; }
         mbar_arrive(&bars[STAGES]);                  // this thread no longer reads the stage (phase t of the stage barrier)
         int I2 = I1, J2 = J1;                         // tile t+2
         advance(I2, J2);
         if (tid == 0 && t + 2 < n_tiles) issue_tile(J2, t + 2);
 
-        const bool switch_rows = I != I_loaded;
-        if (switch_rows) {
+        if (I != I_loaded) {
             // ---- row tile switch: store the finished row sums, then load the row operands of tile I
             if (I_loaded >= 0) {
 #pragma unroll
@@ -294,73 +227,37 @@ sym64_kernel(const Sym64Params prm, const double* __restrict__ ST, const double*
                 const double* si = ST + i * NP;
 #pragma unroll
                 for (int tt = 0; tt < DOT; ++tt) Af[tt][a] = si[4 * tt + k4];
-                auto grow = [&](int p) -> double {       // g_p(i)
-                    const double v = gam * (1.0 - si[p]);
-                    return ((i >> p) & 1) ? -v : v;
-                };
                 qi[a] = qT[i];
-                // column bits 1,2 (thread constants) and 6 (warp constant); C(i) and the bits >= 7 come from the trow table
-                rbase[a] = ((k4 & 1) ? grow(1) : 0.0) + ((k4 & 2) ? grow(2) : 0.0) + (wc ? grow(6) : 0.0);
             }
-            for (int item = tid; item < kTile * 4; item += THREADS) {       // g_0, g_3, g_4, g_5 of every row of the tile
-                const int row = item & (kTile - 1), p = (item >> 7) == 0 ? 0 : 2 + (item >> 7);
-                const int64_t i = (int64_t)I * kTile + row;
-                const double v = gam * (1.0 - ST[i * NP + p]);
-                rowc[(item >> 7) * kTile + row] = ((i >> p) & 1) ? -v : v;
+            if (I_loaded >= 0) {
+                __syncthreads();
+                if (tid < kTile) rowpart[(size_t)I_loaded * kTile + tid] = rowred[tid] + rowred[kTile + tid];
             }
-            for (int item = tid; item < kTile * (n - 7); item += THREADS) {
-                const int row = item & (kTile - 1), p = 7 + (item >> 7);
-                const int64_t i = (int64_t)I * kTile + row;
-                const double v = gam * (1.0 - ST[i * NP + p]);
-                rowg[(p - 7) * kTile + row] = ((i >> p) & 1) ? -v : v;
-            }
-            __syncthreads();
-            if (I_loaded >= 0 && tid < kTile) rowpart[(size_t)I_loaded * kTile + tid] = rowred[tid] + rowred[kTile + tid];
             I_loaded = I;
-            build_tables(I, J, t, true);               // tables of the first tile of the sweep (trow needs the new rowg)
-            __syncthreads();
         }
 
-        // tables of tile t+1 (its copy was issued one iteration ago); when t+1 opens a new row tile its trow is built there
-        if (t + 1 < n_tiles) build_tables(I1, J1, t + 1, I1 == I);
-
-        const unsigned char* bufp = smem + SM::off_buf + (size_t)(t % STAGES) * SM::buf_bytes;
+        const int buf = (int)(t % STAGES);
+        mbar_wait(&bars[buf], (t / STAGES) & 1);
+        const unsigned char* bufp = smem + SM::off_buf + (size_t)buf * SM::buf_bytes;
         const double* raw = reinterpret_cast<const double*>(bufp);
-        const double* cq = reinterpret_cast<const double*>(bufp + SM::raw_bytes) + kTile;
-        const double* colA = reinterpret_cast<const double*>(smem + SM::off_tab + (size_t)(t & 1) * SM::tab_bytes);
-        const double* colB = colA + NWR * kTile;
-        const double* colG = colB + 8 * kStageStride;
-        const double* trow = colG + 2 * kTile;
+        const double* cq = reinterpret_cast<const double*>(bufp + SM::raw_bytes);
         const bool mirrored = J != I;
-
-        // row side of the seed: er[a][e] = C(i) + T1 terms of every column bit except 3,4 at the first batch
-        const double* rc = rowc + rowbase;                                // + k*128 + 8a: g_0, g_3, g_4, g_5 of this thread's rows
-        double er[RB][2];
-#pragma unroll
-        for (int a = 0; a < RB; ++a) {
-            er[a][0] = trow[rowbase + 8 * a] + rbase[a];
-            er[a][1] = er[a][0] + rc[8 * a];
-        }
         const int hh = __popc((uint32_t)(I ^ J));
 
         // ---- 8 batches of 8 columns, software-pipelined: the MMAs of batch b8+1 are issued before the epilogue of batch b8.
-        //      batch b8: 32-column block cbi = b8 >> 2, 8-column group b = gray(b8 & 3) = 0, 1, 3, 2 - one of the column
-        //      bits 3, 4 changes per batch, so the row side of the seed follows with one add per value (g_3 or g_4 of the row)
+        //      batch b8: 32-column block cbi = b8 >> 2, 8-column group b = b8 & 3
         double acc[2][RB][2];
         double qe[2][2];
         double wst[2][2];                                                 // weights of the column sums of the batch in flight
         auto start_batch = [&](int b8, double (&ac)[RB][2], double (&qv2)[2], double (&ws2)[2]) {
-            const int cb = 2 * wc + (b8 >> 2), b = (b8 & 3) ^ ((b8 & 3) >> 1);
+            const int cb = 2 * wc + (b8 >> 2), b = b8 & 3;
             const int cfrag = cb * 32 + 8 * b + r;                     // column this lane supplies to the B fragment
             const double* sc = raw + cfrag * NP;
             double Bf[DOT];
 #pragma unroll
             for (int tt = 0; tt < DOT; ++tt) Bf[tt] = sc[4 * tt + k4];
             const int cacc = cb * 32 + 8 * b + 2 * k4;                 // first of the two columns of the accumulator
-            const double2 ea = *reinterpret_cast<const double2*>(colA + wr * kTile + cacc);
-            const double2 eb = *reinterpret_cast<const double2*>(colB + r * kStageStride + cacc);
             const double2 qv = *reinterpret_cast<const double2*>(cq + cacc);
-            const double4 g34 = *reinterpret_cast<const double4*>(colG + 2 * cacc);   // g_3, g_4 of column cacc; of cacc + 1
             // weight of the warp-uniform bits of i^j: tile bits, bits 5,6 and (16-row warps) bit 4
             const int hb = hh + (RB == 4 ? __popc((uint32_t)(wr ^ cb)) : __popc((uint32_t)((wr >> 1) ^ cb)) + ((wr & 1) ^ (b >> 1)));
             const double wb = sWl[hb] * wt;
@@ -368,38 +265,8 @@ sym64_kernel(const Sym64Params prm, const double* __restrict__ ST, const double*
             ws2[1] = wb * we1;
             qv2[0] = qv.x * ws2[0];                                     // ... folded into q_j for the row sums
             qv2[1] = qv.y * ws2[1];
-            // row side: column bits 3,4 (b) and 5 (cbi) against the Gray walk
-            if ((b8 & 3) != 0 || b8 == 4) {
-                const int kk = b8 == 4 ? 3 : ((b8 & 3) == 2 ? 2 : 1);   // which row constant moves: g_5 (3), g_4 (2), g_3 (1)
-                const bool up = b8 == 4 || (b8 & 3) != 3;               // 0->1: +g3, 1->3: +g4, 3->2: -g3; block switch: +g5
 #pragma unroll
-                for (int a = 0; a < RB; ++a) {
-                    const double g = rc[kk * kTile + 8 * a];
-                    er[a][0] = up ? er[a][0] + g : er[a][0] - g;
-                    er[a][1] = up ? er[a][1] + g : er[a][1] - g;
-                }
-                if (b8 == 4) {                                          // ... and b returns from 2 to 0: -g4
-#pragma unroll
-                    for (int a = 0; a < RB; ++a) {
-                        const double g = rc[2 * kTile + 8 * a];
-                        er[a][0] -= g;
-                        er[a][1] -= g;
-                    }
-                }
-            }
-            // column side: C(j) + T2 terms; the row bits held by a (bit 3, and bit 4 for 32-row warps) meet g_3, g_4 of the column
-            const double ec0 = ea.x + eb.x, ec1 = ea.y + eb.y;
-            const double ec0_3 = ec0 + g34.x, ec1_3 = ec1 + g34.z;
-            double eca[4][2] = {{ec0, ec1}, {ec0_3, ec1_3}, {0.0, 0.0}, {0.0, 0.0}};
-            if (RB == 4) {
-                eca[2][0] = ec0 + g34.y; eca[2][1] = ec1 + g34.w;
-                eca[3][0] = ec0_3 + g34.y; eca[3][1] = ec1_3 + g34.w;
-            }
-#pragma unroll
-            for (int a = 0; a < RB; ++a) {
-                ac[a][0] = er[a][0] + eca[a][0];
-                ac[a][1] = er[a][1] + eca[a][1];
-            }
+            for (int a = 0; a < RB; ++a) { ac[a][0] = 0.0; ac[a][1] = 0.0; }
 #pragma unroll
             for (int tt = 0; tt < DOT; ++tt)
 #pragma unroll
@@ -408,7 +275,7 @@ sym64_kernel(const Sym64Params prm, const double* __restrict__ ST, const double*
         start_batch(0, acc[0], qe[0], wst[0]);
 #pragma unroll
         for (int b8 = 0; b8 < 8; ++b8) {
-            const int cur = b8 & 1, b = (b8 & 3) ^ ((b8 & 3) >> 1);
+            const int cur = b8 & 1, b = b8 & 3;
             if (b8 + 1 < 8) start_batch(b8 + 1, acc[cur ^ 1], qe[cur ^ 1], wst[cur ^ 1]);
             double cs0 = 0.0, cs1 = 0.0;
 #pragma unroll
@@ -450,7 +317,8 @@ sym64_kernel(const Sym64Params prm, const double* __restrict__ ST, const double*
 template <typename Q>
 __global__ void __launch_bounds__(256)
 sym64_finish_kernel(const Sym64Params prm, const double* __restrict__ RowPart, const double* __restrict__ ColPart,
-                    const Q* __restrict__ q, double* __restrict__ u, double* __restrict__ blockpart) {
+                    const double* __restrict__ extra, const Q* __restrict__ q, double* __restrict__ u,
+                    double* __restrict__ blockpart) {
     __shared__ double red[256];
     const int64_t N = (int64_t)1 << prm.n;
     const int64_t z = (int64_t)blockIdx.x * 256 + threadIdx.x;
@@ -462,7 +330,7 @@ sym64_finish_kernel(const Sym64Params prm, const double* __restrict__ RowPart, c
             const int64_t k = panels_to_unit(pa, pb, prm.B) - prm.unit_offset;
             return k >= 0 && k % prm.unit_stride == 0 && k / prm.unit_stride < prm.n_units;
         };
-        double acc = 0.0;
+        double acc = extra ? extra[z] : 0.0;     // C(z) + C(z') and the T1/T2 terms of all pairs (Kronecker pass), unit 0's owner
         for (int pb = pz; pb < prm.B; ++pb)
             if (owned(pz, pb)) acc += RowPart[(size_t)pb * N + z];
         for (int pa = 0; pa <= pz; ++pa)
@@ -502,7 +370,7 @@ __global__ void sym64_qpack_kernel(const Q* __restrict__ q, int64_t N, double* _
 struct Sym64Plan {
     int64_t N, finish_blocks;
     int T, B, s, units_total, n_units, np;
-    size_t off_q, off_row, off_col, off_block, total;
+    size_t off_q, off_row, off_col, off_block, off_extra, off_hib, total;
 };
 
 int make_plan64(int n, int unit_offset, int unit_stride, Sym64Plan* p) {
@@ -524,17 +392,22 @@ int make_plan64(int n, int unit_offset, int unit_stride, Sym64Plan* p) {
     p->off_row = take((size_t)B * p->N * sizeof(double));
     p->off_col = take((size_t)B * p->N * sizeof(double));
     p->off_block = take((size_t)(p->finish_blocks + 1) * sizeof(double));
+    p->off_extra = p->off_hib = off;
+    if (unit_offset == 0) {              // the call that owns unit 0 adds the terms that left the pair kernel
+        p->off_extra = take((size_t)p->N * sizeof(double));
+        p->off_hib = take(tnk_hibits_ws_bytes(n, 0, 1));
+    }
     p->total = off;
     return 0;
 }
 
 template <int NP, int RB>
-int launch64(const Sym64Params& prm, int n_units, const double* ST, const double* Cst, const double* qT,
+int launch64(const Sym64Params& prm, int n_units, const double* ST, const double* qT,
              double* RowPart, double* ColPart, cudaStream_t st) {
     using SM = Smem64<NP, RB>;
     auto kern = sym64_kernel<NP, RB>;
     TNK_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SM::total));
-    kern<<<(unsigned)n_units, 64 * (16 / RB), SM::total, st>>>(prm, ST, Cst, qT, RowPart, ColPart);
+    kern<<<(unsigned)n_units, 64 * (16 / RB), SM::total, st>>>(prm, ST, qT, RowPart, ColPart);
     TNK_CUDA_OK(cudaGetLastError());
     return 0;
 }
@@ -552,10 +425,10 @@ int sym64_row_blocks() {
 }
 
 template <int NP>
-int dispatch64(const Sym64Params& prm, int n_units, const double* ST, const double* Cst, const double* qT,
+int dispatch64(const Sym64Params& prm, int n_units, const double* ST, const double* qT,
                double* RowPart, double* ColPart, cudaStream_t st) {
-    return sym64_row_blocks() == 4 ? launch64<NP, 4>(prm, n_units, ST, Cst, qT, RowPart, ColPart, st)
-                                   : launch64<NP, 2>(prm, n_units, ST, Cst, qT, RowPart, ColPart, st);
+    return sym64_row_blocks() == 4 ? launch64<NP, 4>(prm, n_units, ST, qT, RowPart, ColPart, st)
+                                   : launch64<NP, 2>(prm, n_units, ST, qT, RowPart, ColPart, st);
 }
 
 }  // namespace
@@ -607,17 +480,23 @@ extern "C" int tnk_ksd_sym64(int n_latent, double length_scale, const void* q, i
     TNK_CUDA_OK(cudaGetLastError());
     ++launches;
 
+    double* extra = nullptr;
+    if (unit_offset == 0) {
+        extra = (double*)(ws + p.off_extra);
+        const int rc_hi = tnk_hibits_pass(n, 0, 1, prm.a, prm.gamma, ST, Cst, qT, 8, extra, (double*)(ws + p.off_hib), &launches, st);
+        if (rc_hi) return rc_hi;
+    }
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     tnk_timing_events_get(&ev0, &ev1);
     if (ev0) TNK_CUDA_OK(cudaEventRecord(ev0, st));
     if (p.n_units > 0) {
         int rc = 0;
         switch (p.np) {
-            case 8:  rc = dispatch64<8>(prm, p.n_units, ST, Cst, qT, RowPart, ColPart, st); break;
-            case 12: rc = dispatch64<12>(prm, p.n_units, ST, Cst, qT, RowPart, ColPart, st); break;
-            case 16: rc = dispatch64<16>(prm, p.n_units, ST, Cst, qT, RowPart, ColPart, st); break;
-            case 20: rc = dispatch64<20>(prm, p.n_units, ST, Cst, qT, RowPart, ColPart, st); break;
-            case 24: rc = dispatch64<24>(prm, p.n_units, ST, Cst, qT, RowPart, ColPart, st); break;
+            case 8:  rc = dispatch64<8>(prm, p.n_units, ST, qT, RowPart, ColPart, st); break;
+            case 12: rc = dispatch64<12>(prm, p.n_units, ST, qT, RowPart, ColPart, st); break;
+            case 16: rc = dispatch64<16>(prm, p.n_units, ST, qT, RowPart, ColPart, st); break;
+            case 20: rc = dispatch64<20>(prm, p.n_units, ST, qT, RowPart, ColPart, st); break;
+            case 24: rc = dispatch64<24>(prm, p.n_units, ST, qT, RowPart, ColPart, st); break;
             default: tnk_set_error("tnk_ksd_sym64: no kernel instance for padded length %d", p.np); return 2;
         }
         if (rc) return rc;
@@ -626,9 +505,9 @@ extern "C" int tnk_ksd_sym64(int n_latent, double length_scale, const void* q, i
     if (ev1) TNK_CUDA_OK(cudaEventRecord(ev1, st));
 
     if (q_dtype == 0)
-        sym64_finish_kernel<double><<<(unsigned)p.finish_blocks, 256, 0, st>>>(prm, RowPart, ColPart, (const double*)q, u_partial, blockpart);
+        sym64_finish_kernel<double><<<(unsigned)p.finish_blocks, 256, 0, st>>>(prm, RowPart, ColPart, extra, (const double*)q, u_partial, blockpart);
     else
-        sym64_finish_kernel<float><<<(unsigned)p.finish_blocks, 256, 0, st>>>(prm, RowPart, ColPart, (const float*)q, u_partial, blockpart);
+        sym64_finish_kernel<float><<<(unsigned)p.finish_blocks, 256, 0, st>>>(prm, RowPart, ColPart, extra, (const float*)q, u_partial, blockpart);
     TNK_CUDA_OK(cudaGetLastError());
     sym64_scalar_kernel<<<1, 256, 0, st>>>(blockpart, p.finish_blocks, ksd_part);
     TNK_CUDA_OK(cudaGetLastError());

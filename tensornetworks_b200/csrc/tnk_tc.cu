@@ -1246,7 +1246,7 @@ int tnk_tcs_launch(int n, int fmt, double gamma, const double* wl, const float* 
     }
     if ((fmt == 3 || (fmt == 2 && n > 7)) && tile_offset == 0) {
         // the terms that left the pair kernel, for ALL rows, once (the call that owns row tile 0 adds them)
-        const int rc_hi = tnk_hibits_pass(n, fmt == 3 ? 0 : 7, fmt == 3, wl[1], gamma, ST, Cst, qT, ucol, hibits_ws, launches, st);
+        const int rc_hi = tnk_hibits_pass(n, fmt == 3 ? 0 : 7, fmt == 3, wl[1], gamma, ST, Cst, qT, 4, ucol, hibits_ws, launches, st);
         if (rc_hi) return rc_hi;
     } else {
         TNK_CUDA_OK(cudaMemsetAsync(ucol, 0, (size_t)N * sizeof(double), st));

@@ -103,5 +103,5 @@ int tnk_tcs_launch(int n, int fmt, double gamma, const double* wl, const float* 
 // through 1 + n - p_lo (+1) fp64 Kronecker transforms (tnk_modeprod.cu).
 // ws: tnk_hibits_ws_bytes bytes.  Overwrites u (the tile kernel then adds the remaining terms).
 size_t tnk_hibits_ws_bytes(int n, int p_lo, int with_c);
-int tnk_hibits_pass(int n, int p_lo, int with_c, double a, double gamma, const float* ST, const float* Cst, const float* qT,
-                    double* u, double* ws, int* launches, cudaStream_t st);
+int tnk_hibits_pass(int n, int p_lo, int with_c, double a, double gamma, const void* ST, const void* Cst, const void* qT,
+                    int elem_bytes, double* u, double* ws, int* launches, cudaStream_t st);
