@@ -1,26 +1,27 @@
-"""CPU check of the decomposition the symmetric fp64 kernel uses (csrc/tnk_sym64.cu, "K3-S64"): per pair the bracket
-is   DMMA part (score dot product)  +  row seed  +  column seed  +  the T1/T2 terms of bit positions 3,4 (held by the
-row-block / column-group indices a, b of the accumulator fragment: a Gray walk on the row side, g_3, g_4 of the column
-on the other),
-and the Hamming weight is  LUT[tile and block bits] * thread constant * a^popc(a^b) * a^((r&1)^e).
-A numpy restatement of those pieces, indexed by the same bit fields of i and j the kernel uses, must reproduce the
-oracle's dense K_p (reference stein_utils.py:138-197); the unit enumeration must be a bijection."""
+"""CPU check of the decomposition behind the symmetric fp64 kernel (csrc/tnk_sym64.cu, "K3-S64") and the operand formats
+tf32_tile / tf32_dot of the symmetric tcgen05 kernel (csrc/tnk_tc.cu):
+
+  * the pair kernel keeps  a^popc(i^j) * s(i).s(j)  with the Hamming weight factorised over the bit fields of the
+    accumulator fragment:  LUT[tile and block bits] * thread constant * a^popc(a^b) * a^((r&1)^e);
+  * everything else of k_p (reference stein_utils.py:138-197), summed over all columns, is Kronecker-structured and is
+    what tnk_hibits_pass (csrc/tnk_modeprod.cu) adds:  C(i) K(q)_i + K(C.q)_i + sum_p [ g_p(i) K(b_p.q)_i + b_p(i) K(g_p.q)_i ],
+    with K(b_p.q) obtained elementwise from w = K q.
+
+Numpy restatements of both pieces must reproduce the oracle's dense K_p; the unit enumeration must be a bijection."""
 import numpy as np
 import pytest
 
 from oracle import ksd_oracle as orc
-from tensornetworks_b200.synthetic import illconditioned_binary_bn, random_binary_bn
+from tensornetworks_b200.synthetic import illconditioned_binary_bn, random_binary_bn, random_q
 
 
 def _popc(x):
     return np.array([bin(int(v)).count("1") for v in np.ravel(x)]).reshape(np.shape(x))
 
 
-@pytest.mark.parametrize("n,gen", [(8, random_binary_bn), (9, illconditioned_binary_bn)])
-def test_seed_and_weight_factorisation(n, gen):
+def _setup(n, gen):
     bn, lat, obs, x = gen(n, seed=n)
     S = orc.score_table(orc.joint_table(bn, x, lat), n)
-    Kp = orc.stein_matrix_dense(S, n)
     N = 1 << n
     a_ = np.exp(-1.0 / n)
     alpha, gamma = 1.0 - a_, a_ - 1.0 / a_
@@ -29,28 +30,49 @@ def test_seed_and_weight_factorisation(n, gen):
     bit = (z[:, None] >> np.arange(n)[None, :]) & 1
     g = gamma * (1.0 - s) * (1 - 2 * bit)                        # g_p(z)
     C = alpha * (1.0 - s).sum(1) + gamma * ((1.0 - s) * bit).sum(1)
-    wl = np.exp(-np.arange(n + 1) / n)
+    return S, N, a_, z, s, bit, g, C
 
+
+@pytest.mark.parametrize("n,gen", [(8, random_binary_bn), (9, illconditioned_binary_bn)])
+def test_weight_factorisation_and_split_of_the_bracket(n, gen):
+    S, N, a_, z, s, bit, g, C = _setup(n, gen)
+    Kp = orc.stein_matrix_dense(S, n)
+    wl = np.exp(-np.arange(n + 1) / n)
     i, j = z[:, None], z[None, :]
     I, J = i >> 7, j >> 7
     wr, a, r = (i >> 5) & 3, (i >> 3) & 3, i & 7
     cb, b, k4, e = (j >> 5) & 3, (j >> 3) & 3, (j >> 1) & 3, j & 1
-    wc = cb >> 1
-    gi = lambda p: g[:, p][:, None]
-    gj = lambda p: g[:, p][None, :]
-    hi_bits = range(7, n)
-    # row seed: C(i) + column bits 1,2 (k4), 6 (wc), >= 7 (J), 5 (cb & 1), 0 (e)
-    row = (C[:, None] + (k4 & 1) * gi(1) + (k4 >> 1) * gi(2) + wc * gi(6)
-           + sum(((J >> (p - 7)) & 1) * gi(p) for p in hi_bits) + (cb & 1) * gi(5) + e * gi(0))
-    # column seed: colA[wr][c] + colB[r][c]
-    col = (C[None, :] + sum(((I >> (p - 7)) & 1) * gj(p) for p in hi_bits) + (wr & 1) * gj(5) + (wr >> 1) * gj(6)
-           + (r & 1) * gj(0) + ((r >> 1) & 1) * gj(1) + (r >> 2) * gj(2))
-    # dot product (DMMA) + the bits-3,4 terms: g3(i) b3(j) + g4(i) b4(j) on the row seed, b3(i) g3(j) + b4(i) g4(j) on the column seed
-    mma = s @ s.T + gi(3) * (b & 1) + gi(4) * (b >> 1) + (a & 1) * gj(3) + (a >> 1) * gj(4)
     weight = (wl[_popc(I ^ J) + _popc(wr ^ cb)] * a_ ** _popc(((r >> 1) & 3) ^ k4)
               * a_ ** _popc(a ^ b) * a_ ** ((r & 1) ^ e))
-    got = weight * (mma + row + col)
+    assert np.max(np.abs(weight - wl[_popc(i ^ j)])) <= 1e-15
+    rest = C[:, None] + C[None, :] + g @ bit.T + bit @ g.T       # C(i) + C(j) + T1 + T2 (gamma inside g)
+    got = weight * (s @ s.T + rest)
     assert np.max(np.abs(got - Kp)) <= 1e-12 * np.max(np.abs(Kp))
+
+
+@pytest.mark.parametrize("n,gen,p_lo,with_c", [(8, random_binary_bn, 0, True), (9, illconditioned_binary_bn, 0, True),
+                                               (9, random_binary_bn, 7, False), (10, random_binary_bn, 7, False)])
+def test_kronecker_pass_identity(n, gen, p_lo, with_c):
+    """What hib_build / mp_transform / hib_fold compute: the terms of bit positions >= p_lo (and, with_c, the C terms)
+    for all rows at once, K(b_p.q) taken elementwise from w = K q."""
+    S, N, a_, z, s, bit, g, C = _setup(n, gen)
+    q = random_q(N, seed=n).numpy()
+    wl = np.exp(-np.arange(n + 1) / n)
+    Kb = wl[_popc(z[:, None] ^ z[None, :])]                      # the base kernel matrix K = M^{(x)n}
+    T = sum(np.outer(g[:, p], bit[:, p]) + np.outer(bit[:, p], g[:, p]) for p in range(p_lo, n))
+    if with_c:
+        T = T + C[:, None] + C[None, :]
+    want = (Kb * T) @ q
+    w = Kb @ q
+    got = np.zeros(N)
+    for p in range(p_lo, n):
+        on = bit[:, p].astype(bool)
+        A = np.where(on, 1.0, a_) * (w[z | (1 << p)] - a_ * w[z & ~(1 << p)]) / (1.0 - a_ * a_)
+        assert np.max(np.abs(A - Kb @ (bit[:, p] * q))) <= 1e-12 * np.max(np.abs(w))
+        got += g[:, p] * A + np.where(on, Kb @ (g[:, p] * q), 0.0)
+    if with_c:
+        got += C * w + Kb @ (C * q)
+    assert np.max(np.abs(got - want)) <= 1e-12 * np.max(np.abs(want))
 
 
 def test_unit_enumeration_is_a_bijection():
