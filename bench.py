@@ -361,8 +361,8 @@ def run_ours(args):
     K_value = float(part.item())
 
     # ---- timed region 2: end to end through the public op with HOST q and HOST gradient
-    for _ in range(2):
-        e2e_step()
+    for _ in range(3):
+        K_e2e, grad_host = e2e_step()               # held like in the timed loop: two pinned gradient blocks stay in rotation
     barrier()
     t0 = time.perf_counter()
     e2e_ms = []
