@@ -604,10 +604,16 @@ def main():
             tiles = sym_tiles(n, 0, world)
             s32, s16 = sym_steps(n, r["sym_split"])
             flops_tile = 128 * 128 * 2 * 8 * (s32 + s16)
+            # row tiles sharing one column-operand stage (tnk_tc.cu launch_sym): 4 when their A operands fit in TMEM
+            row_tiles_per_cta = 4 if 256 + 4 * 8 * (s32 + s16) <= 512 else 2
+            if os.environ.get("TNK_TCS_ROWTILES") in ("1", "2"):
+                row_tiles_per_cta = int(os.environ["TNK_TCS_ROWTILES"])
             peak_tf, burst_tf, src = tensor_peak(peaks)
             ach_tf = tiles * flops_tile / kernel_s / 1e12
             roofline = {"bound": "tensor", "achieved": ach_tf, "peak": peak_tf, "unit": "TFLOP/s",
-                        "frac": ach_tf / peak_tf, "traffic": None, "kernel": "tcs_tiles_kernel",
+                        "frac": ach_tf / peak_tf, "traffic": None,
+                        "kernel": "tcs_tiles_kernel" if row_tiles_per_cta == 1 else "tcs_tilesN_kernel",
+                        "row_tiles_per_cta": row_tiles_per_cta,
                         "kernel_ms": r["kernel_ms"], "executed_tiles_128x128": tiles,
                         "executed_pairs_per_s": tiles * 16384.0 / kernel_s,
                         "ordered_pairs_per_executed_pair": (pairs / world) / (tiles * 16384.0),
@@ -630,6 +636,10 @@ def main():
                 roofline["tmem_readout"] = {"achieved_TB/s": tmem_ach / 1e12, "peak_TB/s": tmem_peak / 1e12,
                                             "frac": tmem_ach / tmem_peak, "bytes_per_tile": 65536,
                                             "peak_source": "148 SMs x 64 B/clk x median SM clock of this run"}
+                if tmem_ach > tmem_peak:
+                    roofline["tmem_readout"]["frac_note"] = (
+                        "above 1: the 64 B/clk LDTM figure of B300_MICROARCH.md is not a hard limit for the .16x256b.x8 loads "
+                        "used here; the hardware's own figure is sm__mem_tensor_cycles_active in the ncu summary under profiles/")
             tag = "tcs_tiles"
         elif r["algorithm"] == "pairs_sym64":
             tiles = sym64_tiles(n, 0, world)

@@ -8,6 +8,7 @@ from tensornetworks_b200 import ops
 from tensornetworks_b200.synthetic import random_binary_bn, random_q
 
 n = int(sys.argv[1]) if len(sys.argv) > 1 else 20
+only = sys.argv[2].split(",") if len(sys.argv) > 2 else None      # e.g. tf32,tf32_dot
 bn, lat, obs, x = random_binary_bn(n, seed=0)
 q = random_q(1 << n, seed=0).cuda()
 tc = ops.SteinTables.from_network(bn, x, lat, precision="tc32")
@@ -19,6 +20,8 @@ for name, flag, split in (("full kernel (13 K-steps)", "0", "tf32"), ("no mirror
                           ("bf16x2 operands (10 K-steps)", "0", "bf16x2"), ("bf16x2, no mirrored part", "1", "bf16x2"),
                           ("tf32_tile operands (9 K-steps)", "0", "tf32_tile"), ("tf32_tile, no mirrored part", "1", "tf32_tile"),
                           ("tf32_dot operands (6 K-steps)", "0", "tf32_dot"), ("tf32_dot, no mirrored part", "1", "tf32_dot")):
+    if only is not None and split not in only:
+        continue
     os.environ["TNK_TCS_ABLATE"] = flag
     tc.ksd_sym(q, split=split)
     times = []

@@ -598,6 +598,7 @@ struct TcsParams {
     int tile_offset, tile_stride;  // row tile of blockIdx.x = tile_offset + tile_stride * blockIdx.x
     int64_t n_tiles;               // 2^n / 128
     int col_splits;                // gridDim.y
+    int row_tiles;                 // row tiles of this launch (tcs_tilesN_kernel: RT per CTA)
     int ablate;                    // diagnostics only (TNK_TCS_ABLATE, wrong results): 1 = no mirrored part, 2 = mirrored sums not stored
     float gamma;
     float wl[32];
@@ -738,7 +739,7 @@ struct TcsSmem {
     static constexpr uint32_t off_q = off_b + stages * b_bytes;           // [kQSlots][128] float: q of the column tile
     static constexpr uint32_t off_wl = off_q + kQSlots * kTile * 4;       // [32] float
     static constexpr uint32_t off_red = off_wl + 32 * 4;                  // [128] double
-    static constexpr uint32_t off_bar = off_red + 3 * kTile * 8;          // mbarriers (red: up to 3 column slices)
+    static constexpr uint32_t off_bar = off_red + 4 * kTile * 8;          // mbarriers (red: up to 3 column slices / 4 row tiles)
     static constexpr int n_bars = 1 + 2 * kMaxStages + 4 + kQSlots;
     static constexpr uint32_t off_tmem = off_bar + n_bars * 8;
     static constexpr uint32_t total = off_tmem + 16;
@@ -1115,6 +1116,373 @@ tcs_tiles_kernel(const __grid_constant__ TcsParams prm, const float* __restrict_
     }
 }
 
+
+// ---- RT row tiles per CTA.  A column tile's operand stage (B, 16 * K bytes per state) and q values are fetched once
+// and multiplied against the A operands of RT row tiles, all resident in TMEM (RT x 8 columns per K-step next to the
+// two accumulator stages): 1/RT of the shared-memory fills per executed tile, and the mirrored column sums of the RT
+// tiles are added in registers BEFORE the transposing exchange, so there is one exchange and one RED pair per column
+// tile and warp instead of one per executed tile.  Row tile r of CTA x is tile_offset + tile_stride * (RT x + r); the
+// tiles of a CTA are increasing, so the ones meeting column tile J (J >= I_r) are a prefix r < nact(J).
+template <int NC, int FMT, int RT>
+__global__ void __launch_bounds__(64 + 128 * 2, 1)
+tcs_tilesN_kernel(const __grid_constant__ TcsParams prm, const float* __restrict__ B_tab,
+                  const float* __restrict__ ST, const float* __restrict__ Cst, const float* __restrict__ qT,
+                  double* __restrict__ ucol) {
+    extern __shared__ __align__(1024) unsigned char smem[];
+    using SM = TcsSmem<NC, FMT>;
+    constexpr int NP = 4 * NC;
+    constexpr int CS = 2, MC = 8;        // 8 epilogue warps, 4 x 16 patches
+    constexpr int K32 = tcs_k32(NC, FMT), S32 = tcs_steps32(NC, FMT), S16 = tcs_steps16(NC, FMT);
+    constexpr int KS = S32 + S16;
+    constexpr int kStages = SM::stages;
+    constexpr uint32_t b_bytes = SM::b_bytes;
+    static_assert(RT >= 2 && RT <= 4, "row tiles per CTA");
+    static_assert(2 * kTile + RT * 8 * KS <= kTmemCols, "TMEM columns");
+
+    const int r_first = RT * (int)blockIdx.x;
+    const int nvalid = min(RT, prm.row_tiles - r_first);
+    const int64_t I0 = (int64_t)prm.tile_offset + (int64_t)prm.tile_stride * r_first;
+    const int64_t n_per = prm.n_tiles / prm.col_splits;
+    const int64_t j_split = (int64_t)blockIdx.y * n_per;
+    const int64_t j_begin = j_split > I0 ? j_split : I0;
+    const int64_t n_local = j_split + n_per - j_begin;
+    if (n_local <= 0) return;
+    // row tiles meeting column tile J: r < nvalid with I0 + stride r <= J; J only grows, so the count is kept
+    // incrementally (tile indices < 2^17: 32-bit arithmetic)
+    const uint32_t I0u = (uint32_t)I0, strideu = (uint32_t)prm.tile_stride;
+    auto grow_active = [&](int nact, uint32_t J) -> int {
+        while (nact < nvalid && I0u + strideu * (uint32_t)nact <= J) ++nact;
+        return nact;
+    };
+
+    unsigned char* sB = smem + SM::off_b;
+    float* sQ = reinterpret_cast<float*>(smem + SM::off_q);
+    float* sWl = reinterpret_cast<float*>(smem + SM::off_wl);
+    double* sRed = reinterpret_cast<double*>(smem + SM::off_red);
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + SM::off_bar);
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + SM::off_tmem);
+    uint64_t* bar_aready = bars;
+    uint64_t* bar_full = bars + 1;
+    uint64_t* bar_empty = bar_full + kMaxStages;
+    uint64_t* bar_tfull = bar_empty + kMaxStages;
+    uint64_t* bar_tempty = bar_tfull + 2;
+    uint64_t* bar_qfull = bar_tempty + 2;
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (threadIdx.x < 32) sWl[threadIdx.x] = prm.wl[threadIdx.x];
+    if (threadIdx.x == 0) {
+        mbar_init(bar_aready, 4 * CS);
+        for (int s = 0; s < kStages; ++s) { mbar_init(bar_full + s, 1); mbar_init(bar_empty + s, 1); }
+        for (int s = 0; s < 2; ++s) { mbar_init(bar_tfull + s, 1); mbar_init(bar_tempty + s, 4 * CS); }
+        for (int s = 0; s < kQSlots; ++s) mbar_init(bar_qfull + s, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 1) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(kTmemCols) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            // ===== producer: one operand stage and one q tile per COLUMN tile
+            int s = 0;
+            uint32_t ph = 0;
+            for (int64_t it = 0; it < n_local; ++it) {
+                const int64_t J = j_begin + it;
+                mbar_wait(bar_empty + s, ph ^ 1u);
+                const int qs = (int)(it & (kQSlots - 1));
+                mbar_expect_tx(bar_qfull + qs, kTile * 4);
+                bulk_g2s(sQ + qs * kTile, qT + J * kTile, kTile * 4, bar_qfull + qs);
+                const unsigned char* srcB = reinterpret_cast<const unsigned char*>(B_tab) + (size_t)J * b_bytes;
+                unsigned char* dstB = sB + (size_t)s * b_bytes;
+                mbar_expect_tx(bar_full + s, b_bytes);
+                for (uint32_t off = 0; off < b_bytes; off += 8 * kChunkBytes) {
+                    const uint32_t len = min(b_bytes - off, (uint32_t)(8 * kChunkBytes));
+                    bulk_g2s(dstB + off, srcB + off, len, bar_full + s);
+                }
+                if (++s == kStages) { s = 0; ph ^= 1u; }
+            }
+        }
+    } else if (warp == 1) {
+        // ===== MMA issuer: the accumulator stages alternate over EXECUTED tiles (vt), the B stage over column tiles
+        mbar_wait(bar_aready, 0);
+        tc_fence_after();
+        int s = 0;
+        uint32_t ph = 0, vt = 0;
+        int nact = 0;
+        for (uint32_t it = 0; it < (uint32_t)n_local; ++it) {
+            nact = grow_active(nact, (uint32_t)j_begin + it);
+            mbar_wait(bar_full + s, ph);
+            const uint64_t b_desc = smem_desc(smem_u32(sB) + (uint32_t)s * b_bytes, 0);
+            for (int r = 0; r < nact; ++r, ++vt) {
+                const int ts = (int)(vt & 1);
+                mbar_wait(bar_tempty + ts, ((vt >> 1) & 1) ^ 1u);
+                tc_fence_after();
+                const uint32_t d_addr = tmem_base + (uint32_t)(ts * kTile);
+                const uint32_t a_addr = tmem_base + (uint32_t)(kTmemA + r * 8 * KS);
+                if (elect_one()) {
+                    constexpr uint32_t cu = kChunkBytes >> 4;
+#pragma unroll
+                    for (int ks = 0; ks < S32; ++ks) {
+                        const uint64_t db = b_desc + (uint64_t)((uint32_t)(2 * ks) * cu + (cu << 16));
+                        umma_tf32_ts(d_addr, a_addr + (uint32_t)(8 * ks), db, kIdesc, ks > 0 ? 1u : 0u);
+                    }
+#pragma unroll
+                    for (int k = 0; k < S16; ++k) {
+                        const uint64_t db = b_desc + (uint64_t)((uint32_t)(K32 + 2 * k) * cu + (cu << 16));
+                        umma_bf16_ts(d_addr, a_addr + (uint32_t)(8 * (S32 + k)), db, kIdescBf16, (S32 + k) > 0 ? 1u : 0u);
+                    }
+                    if (r + 1 == nact) umma_commit(bar_empty + s);      // the stage is free once the LAST row tile has read it
+                    umma_commit(bar_tfull + ts);
+                }
+                __syncwarp();
+            }
+            if (++s == kStages) { s = 0; ph ^= 1u; }
+        }
+    } else {
+        // ===== epilogue warps 2..9: lane quarter lqi = warp & 3, column half cs = (warp - 2) >> 2
+        const int lqi = warp & 3;
+        const int lq = lqi * 32;
+        const int cs = (warp - 2) >> 2;
+        const int colbase = cs * 8 * MC;
+        const int n = prm.n;
+        for (int r = 0; r < nvalid; ++r) {
+            // A operand of row tile r (same construction as tcs_tiles_kernel), TMEM columns kTmemA + r 8 KS ...
+            const int L = lq + lane;
+            const int64_t i = (I0 + (int64_t)prm.tile_stride * r) * kTile + L;
+            float sv[NP], gr[NP];
+#pragma unroll
+            for (int c = 0; c < NC; ++c) {
+                const float4 s4 = *reinterpret_cast<const float4*>(ST + i * NP + 4 * c);
+                sv[4 * c] = s4.x; sv[4 * c + 1] = s4.y; sv[4 * c + 2] = s4.z; sv[4 * c + 3] = s4.w;
+            }
+#pragma unroll
+            for (int p = 0; p < NP; ++p) {
+                const float v = prm.gamma * (1.f - sv[p]);
+                gr[p] = (p < n) ? (((i >> p) & 1) ? -v : v) : 0.f;
+            }
+            const float Ci = (FMT == 3) ? 0.f : Cst[i];
+            auto bitf = [&](int p) -> float { return (p < n && ((i >> p) & 1)) ? 1.f : 0.f; };
+            auto a32 = [&](int chunk, int e) -> float {
+                if (FMT == 3) return chunk < NC ? tf_hi(sv[4 * chunk + e]) : 0.f;
+                if (FMT == 2) {
+                    if (chunk < NC) return tf_hi(sv[4 * chunk + e]);
+                    if (chunk < NC + 4) {
+                        const int p = 4 * ((chunk - NC) & 1) + e;
+                        if (p >= 7) return 0.f;
+                        return chunk < NC + 2 ? tf_hi(gr[p]) : bitf(p);
+                    }
+                    if (chunk == NC + 4) return e == 0 ? tf_hi(Ci) : e == 1 ? tf_lo(Ci) : 1.f;
+                    return 0.f;
+                }
+                if (chunk > 3 * NC) return 0.f;
+                if (chunk == 3 * NC) return e == 0 ? tf_hi(Ci) : e == 1 ? tf_lo(Ci) : 1.f;
+                const int f = chunk / NC, p = 4 * (chunk - f * NC) + e;
+                return f == 0 ? tf_hi(sv[p]) : f == 1 ? tf_hi(gr[p]) : bitf(p);
+            };
+            auto a16 = [&](int e) -> float {
+                if (FMT == 3) return e < NP ? sv[e] : e < 2 * NP ? tf_lo(sv[e - NP]) : 0.f;
+                if (FMT == 2) {
+                    if (e < NP) return sv[e];
+                    if (e < 2 * NP) return tf_lo(sv[e - NP]);
+                    const int p = (e - 2 * NP) & 7;
+                    if (e >= 2 * NP + 16 || p >= 7) return 0.f;
+                    return e < 2 * NP + 8 ? tf_lo(gr[p]) : bitf(p);
+                }
+                const int f = e / NP, p = e - f * NP;
+                if (FMT == 0) return f == 0 ? sv[p] : f == 1 ? tf_lo(sv[p]) : f == 2 ? tf_lo(gr[p]) : bitf(p);
+                if (f < 7) {
+                    if (f >= 5) return bitf(p);
+                    const float full = f < 3 ? sv[p] : gr[p];
+                    const float x1 = bf_round(full);
+                    return (f == 2 || f == 4) ? bf_round(full - x1) : x1;
+                }
+                const int k = e - 7 * NP;
+                if (k >= 6) return 0.f;
+                if (k >= 3) return 1.f;
+                const float c1 = bf_round(Ci), c2 = bf_round(Ci - c1);
+                return k == 0 ? c1 : k == 1 ? c2 : bf_round(Ci - c1 - c2);
+            };
+#pragma unroll
+            for (int ks = 0; ks < KS; ++ks) {
+                if ((ks % CS) == cs) {
+                    uint32_t av[8];
+                    if (ks < S32) {
+#pragma unroll
+                        for (int e = 0; e < 4; ++e) {
+                            av[e] = __float_as_uint(a32(2 * ks, e));
+                            av[4 + e] = __float_as_uint(a32(2 * ks + 1, e));
+                        }
+                    } else {
+#pragma unroll
+                        for (int c = 0; c < 8; ++c)
+                            av[c] = bf16_pack(a16(16 * (ks - S32) + 2 * c), a16(16 * (ks - S32) + 2 * c + 1));
+                    }
+                    asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};"
+                                 ::"r"(tmem_base + ((uint32_t)lq << 16) + (uint32_t)(kTmemA + r * 8 * KS + 8 * ks)),
+                                   "r"(av[0]), "r"(av[1]), "r"(av[2]), "r"(av[3]), "r"(av[4]), "r"(av[5]), "r"(av[6]), "r"(av[7])
+                                 : "memory");
+                }
+            }
+        }
+        asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(bar_aready);
+
+        const int t = lane;
+        const int rq = lq + (t >> 2);
+        float2 T2[3][2];                                   // a^(in-tile Hamming distance), packed over e
+        {
+            const int i0 = (t >> 2) & 1;
+            const int c0 = __popc((unsigned)(((t >> 3) & 3) ^ (t & 3)));
+#pragma unroll
+            for (int h = 0; h < 3; ++h)
+#pragma unroll
+                for (int mh = 0; mh < 2; ++mh) {
+                    const int e0 = c0 + h + __popc((unsigned)((((colbase >> 5) + mh) ^ lqi) & 3));
+                    T2[h][mh] = make_float2(sWl[e0 + i0], sWl[e0 + (i0 ^ 1)]);
+                }
+        }
+        float qi[RT][4];
+        float uhi[RT][4], ulo[RT][4], uch[RT][4];
+#pragma unroll
+        for (int r = 0; r < RT; ++r)
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                qi[r][k] = r < nvalid ? qT[(I0 + (int64_t)prm.tile_stride * r) * kTile + rq + 8 * k] : 0.f;
+                uhi[r][k] = ulo[r][k] = uch[r][k] = 0.f;
+            }
+        const bool b4 = (t & 16) != 0, b3 = (t & 8) != 0, b2 = (t & 4) != 0;
+        const uint32_t n_loc = (uint32_t)n_local, I32 = (uint32_t)I0, j0 = (uint32_t)j_begin, stride = (uint32_t)prm.tile_stride;
+        uint32_t vt = 0;
+        int nact = 0;
+        for (uint32_t it = 0; it < n_loc; ++it) {
+            const int qs = (int)(it & (kQSlots - 1));
+            const uint32_t qph = (it / kQSlots) & 1;
+            const uint32_t J = j0 + it;
+            nact = grow_active(nact, J);
+            mbar_wait(bar_qfull + qs, qph);
+            float2 qj[MC];
+            {
+                const float2* q2 = reinterpret_cast<const float2*>(sQ + qs * kTile + colbase + 2 * (t & 3));
+#pragma unroll
+                for (int m = 0; m < MC; ++m) qj[m] = q2[4 * m];
+            }
+            float2 cacc[MC];
+#pragma unroll
+            for (int m = 0; m < MC; ++m) cacc[m] = make_float2(0.f, 0.f);
+#pragma unroll
+            for (int r = 0; r < RT; ++r) {
+                if (r < nact) {
+                    const int ts = (int)(vt & 1);
+                    const uint32_t tph = (vt >> 1) & 1;
+                    ++vt;
+                    const uint32_t Ir = I32 + stride * (uint32_t)r;
+                    const float wg = sWl[__popc(Ir ^ J)];
+                    const float wm = (J != Ir) ? wg : 0.f;       // a diagonal tile has no mirrored part
+                    float qw[4];
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) qw[k] = wm * qi[r][k];
+                    mbar_wait(bar_tfull + ts, tph);
+                    tc_fence_after();
+                    const uint32_t taddr = tmem_base + ((uint32_t)lq << 16) + (uint32_t)(ts * kTile + colbase);
+                    uint32_t v0[4 * MC], v1[4 * MC];
+                    TNK_LD_16x256b_x8(v0, taddr);
+                    TNK_LD_16x256b_x8(v1, taddr + (16u << 16));
+                    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+                    tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(bar_tempty + ts);
+                    float2 racc[4];
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) racc[k] = make_float2(0.f, 0.f);
+                    auto fold = [&](const uint32_t (&v)[4 * MC], const int hr) {
+#pragma unroll
+                        for (int m = 0; m < MC; ++m)
+#pragma unroll
+                            for (int rr = 0; rr < 2; ++rr) {
+                                const int k = 2 * hr + rr;
+                                const int d = (k ^ m) & 3;
+                                const float2 acc = make_float2(__uint_as_float(v[4 * m + 2 * rr]), __uint_as_float(v[4 * m + 2 * rr + 1]));
+                                const float2 p = __fmul2_rn(T2[(d & 1) + (d >> 1)][m >> 2], acc);
+                                racc[k] = __ffma2_rn(p, qj[m], racc[k]);
+                                cacc[m] = __ffma2_rn(p, make_float2(qw[k], qw[k]), cacc[m]);
+                            }
+                    };
+                    fold(v0, 0);
+                    fold(v1, 1);
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) uch[r][k] = fmaf(wg, racc[k].x + racc[k].y, uch[r][k]);
+                }
+            }
+            if ((it & 7) == 7 || it + 1 == n_loc) {
+#pragma unroll
+                for (int r = 0; r < RT; ++r)
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) {
+                        const float sum = uhi[r][k] + uch[r][k];      // TwoSum
+                        const float bb = sum - uhi[r][k];
+                        ulo[r][k] += (uhi[r][k] - (sum - bb)) + (uch[r][k] - bb);
+                        uhi[r][k] = sum;
+                        uch[r][k] = 0.f;
+                    }
+            }
+            if (!(nact == 1 && J == I32) && !(prm.ablate & 1)) {
+                // mirrored sums of all row tiles of this column tile: one transposing exchange, one RED pair
+                auto xadd = [&](const float2 keep, const float2 send, const int mask) {
+                    return __fadd2_rn(keep, make_float2(__shfl_xor_sync(0xffffffffu, send.x, mask),
+                                                        __shfl_xor_sync(0xffffffffu, send.y, mask)));
+                };
+                float2 c1[4], c2[2];
+#pragma unroll
+                for (int k = 0; k < 4; ++k) c1[k] = xadd(b4 ? cacc[k + 4] : cacc[k], b4 ? cacc[k] : cacc[k + 4], 16);
+#pragma unroll
+                for (int k = 0; k < 2; ++k) c2[k] = xadd(b3 ? c1[k + 2] : c1[k], b3 ? c1[k] : c1[k + 2], 8);
+                const float2 c3 = xadd(b2 ? c2[1] : c2[0], b2 ? c2[0] : c2[1], 4);
+                if (!(prm.ablate & 2)) {
+                    double* dst = ucol + (size_t)J * kTile + colbase + 2 * t;
+                    atomicAdd(dst, (double)c3.x);
+                    atomicAdd(dst + 1, (double)c3.y);
+                }
+            }
+        }
+        // row sums: over the 4 threads sharing a row, then over the two column halves
+#pragma unroll
+        for (int r = 0; r < RT; ++r) {
+            double ud[4];
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                double x = (double)uhi[r][k] + (double)ulo[r][k];
+                x += __shfl_xor_sync(0xffffffffu, x, 1);
+                x += __shfl_xor_sync(0xffffffffu, x, 2);
+                ud[k] = x;
+            }
+            if (cs > 0 && (t & 3) == 0) {
+#pragma unroll
+                for (int k = 0; k < 4; ++k) sRed[r * kTile + rq + 8 * k] = ud[k];
+            }
+            asm volatile("bar.sync 1, %0;" ::"n"(128 * CS) : "memory");   // the epilogue warps only
+            if (cs == 0 && (t & 3) == 0 && r < nvalid) {
+#pragma unroll
+                for (int k = 0; k < 4; ++k)
+                    atomicAdd(ucol + (I0 + (int64_t)prm.tile_stride * r) * kTile + rq + 8 * k, ud[k] + sRed[r * kTile + rq + 8 * k]);
+            }
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        __syncwarp();
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(kTmemCols) : "memory");
+    }
+}
+
 }  // namespace
 
 // Host planner: chunk products (A-chunk x B-chunk) of the bracket, two per MMA K-step.
@@ -1217,12 +1585,36 @@ int launch_sym_cs(const TcsParams& prm, dim3 grid, const float* B_tab, const flo
     TNK_CUDA_OK(cudaGetLastError());
     return 0;
 }
+template <int NC, int FMT, int RT>
+int launch_symN(const TcsParams& prm, dim3 grid, const float* B_tab, const float* ST, const float* Cst,
+                const float* qT, double* ucol, cudaStream_t st) {
+    const size_t smem = TcsSmem<NC, FMT>::total;
+    auto kern = tcs_tilesN_kernel<NC, FMT, RT>;
+    TNK_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    grid.x = (grid.x + RT - 1) / RT;
+    kern<<<grid, 64 + 128 * 2, smem, st>>>(prm, B_tab, ST, Cst, qT, ucol);
+    TNK_CUDA_OK(cudaGetLastError());
+    return 0;
+}
 template <int NC, int FMT>
 int launch_sym(const TcsParams& prm, dim3 grid, const float* B_tab, const float* ST, const float* Cst,
                const float* qT, double* ucol, cudaStream_t st) {
-    // CS = 2: 8 epilogue warps with 4 x 16 patches.  CS = 4 (16 warps, 4 x 8 patches, 88 registers) gives the same
-    // results but measured slower (n = 20: 183.1 vs 178.6 ms): the kernel is bound by power, not by exposed latency.
-    return launch_sym_cs<NC, FMT, 2>(prm, grid, B_tab, ST, Cst, qT, ucol, st);
+    // Row tiles per CTA: as many as fit in TMEM next to the two accumulator stages (4 for the dot format, else 2);
+    // n = 20, one B200: tf32_dot 133.2 (1) / 114.0 (2) / 111.0 ms (4), 13-step format 166.8 (1) / 146.5 ms (2).
+    // TNK_TCS_ROWTILES=1|2|4 overrides (1 = tcs_tiles_kernel; measurements in profiles/r02_sym_ablations_rt*.log).
+    // Epilogue warps: CS = 2 (8 warps, 4 x 16 patches); CS = 4 measured slower on the one-tile kernel (183.1 vs 178.6 ms).
+    constexpr int KS = tcs_steps32(NC, FMT) + tcs_steps16(NC, FMT);
+    constexpr bool fits4 = 2 * kTile + 4 * 8 * KS <= kTmemCols;
+    int rt = fits4 ? 4 : 2;
+    if (const char* e = getenv("TNK_TCS_ROWTILES")) {
+        const int v = atoi(e);
+        if (v == 1 || v == 2 || (v == 4 && fits4)) rt = v;
+    }
+    if (rt == 1) return launch_sym_cs<NC, FMT, 2>(prm, grid, B_tab, ST, Cst, qT, ucol, st);
+    if constexpr (fits4) {
+        if (rt == 4) return launch_symN<NC, FMT, 4>(prm, grid, B_tab, ST, Cst, qT, ucol, st);
+    }
+    return launch_symN<NC, FMT, 2>(prm, grid, B_tab, ST, Cst, qT, ucol, st);
 }
 }  // namespace
 
@@ -1254,7 +1646,7 @@ int tnk_tcs_launch(int n, int fmt, double gamma, const double* wl, const float* 
     if (row_tiles <= 0) return 0;
     TcsParams prm;
     prm.n = n; prm.tile_offset = tile_offset; prm.tile_stride = tile_stride; prm.n_tiles = col_tiles;
-    prm.col_splits = splits; prm.gamma = (float)gamma;
+    prm.col_splits = splits; prm.row_tiles = row_tiles; prm.gamma = (float)gamma;
     {
         const char* e = getenv("TNK_TCS_ABLATE");      // ablation runs of scripts/sym_ablate.py: results are WRONG when set
         prm.ablate = e ? atoi(e) : 0;
