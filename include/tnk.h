@@ -40,7 +40,7 @@ extern "C" {
 #define TNK_MAX_LATENT 30
 #define TNK_MAX_PEERS 8   /* GPUs of one NVSwitch box (tnk_ksd_rows_peers) */
 
-#define TNK_ABI_VERSION 200   /* bumped whenever a signature below changes; tnk_version() returns the built value */
+#define TNK_ABI_VERSION 201   /* bumped whenever a signature below changes; tnk_version() returns the built value */
 
 const char* tnk_last_error(void);
 int tnk_version(void);
@@ -94,6 +94,24 @@ int tnk_ksd_rows(int n_latent, double length_scale, int precision,
                  int64_t row_begin, int64_t row_end,
                  double* u, double* ksd_part,
                  void* workspace, size_t workspace_bytes, int* n_launch, void* stream);
+
+/* tnk_ksd_rows without a caller-provided workspace and without any allocation.  It has no counterpart in the
+ * reference and was added for callers that cannot call cudaMalloc (code under
+ * CUDA graph capture, tight serving loops, harnesses that forbid it).  The scratch memory of tnk_ksd_rows lives in a
+ * static device array of TNK_STATIC_SCRATCH_BYTES inside the library (held by every GPU that loads it until the
+ * process exits); the call enqueues the same kernels with the same arguments otherwise and calls no cudaMalloc,
+ * cudaFree or allocating library routine.  Problems whose tnk_ksd_workspace_bytes exceeds the array are rejected
+ * with an error naming both sizes (16 MiB holds whole evaluations up to n = 19 in TNK_PREC_FP64, n = 20 in
+ * TNK_PREC_FP32 and n = 15 in TNK_PREC_TC32; larger n only for row ranges whose workspace fits).
+ * All calls on one device share the array: calls that overlap on the GPU (two streams, concurrent graph replays)
+ * race - serialise them.  Nothing in it carries over from one call to the next.
+ *   tnk_ksd_rows_static_capacity   TNK_STATIC_SCRATCH_BYTES of the built library */
+#define TNK_STATIC_SCRATCH_BYTES (16u << 20)
+size_t tnk_ksd_rows_static_capacity(void);
+int tnk_ksd_rows_static(int n_latent, double length_scale, int precision,
+                        const void* q, int q_dtype, const void* ST, const void* Cst,
+                        int64_t row_begin, int64_t row_end,
+                        double* u, double* ksd_part, int* n_launch, void* stream);
 
 /* tnk_ksd_rows with the exchange step of the row-sharded evaluation fused into its reduction
  * kernels (replaces the all_gather + all_reduce a host would otherwise issue after

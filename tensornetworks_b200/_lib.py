@@ -27,7 +27,7 @@ SYM_SPLIT = {"tf32": 0, "bf16x2": 1, "tf32_tile": 2, "tf32_dot": 3}  # TNK_SYM_S
 
 # every symbol include/tnk.h declares
 EXPORTS = ["tnk_last_error", "tnk_version", "tnk_bn_joint", "tnk_ksd_layout", "tnk_score",
-           "tnk_ksd_workspace_bytes", "tnk_ksd_rows", "tnk_ksd_rows_peers", "tnk_ksd_timing_events", "tnk_alu_peak",
+           "tnk_ksd_workspace_bytes", "tnk_ksd_rows", "tnk_ksd_rows_static", "tnk_ksd_rows_static_capacity", "tnk_ksd_rows_peers", "tnk_ksd_timing_events", "tnk_alu_peak",
            "tnk_ksd_modeproduct_workspace_bytes", "tnk_modeproduct_tables", "tnk_modeproduct_plan_limit", "tnk_ksd_modeproduct", "tnk_tc_plan",
            "tnk_born_blocks", "tnk_born_forward", "tnk_born_backward",
            "tnk_ksd_sym_workspace_bytes", "tnk_ksd_sym",
@@ -48,7 +48,7 @@ def _stale():
     return any(os.path.getmtime(d) > built for d in deps)
 
 
-ABI_VERSION = 200   # tnk_version() of the library these ctypes signatures were written for (bumped with include/tnk.h)
+ABI_VERSION = 201   # tnk_version() of the library these ctypes signatures were written for (bumped with include/tnk.h)
 
 
 def build(force=False, verbose=False):
@@ -128,6 +128,11 @@ def load():
     lib.tnk_ksd_rows.restype = c_int
     lib.tnk_ksd_rows.argtypes = [c_int, c_dbl, c_int, c_vp, c_int, c_vp, c_vp, c_i64, c_i64, c_vp, c_vp,
                                  c_vp, c_sz, ctypes.POINTER(c_int), c_vp]
+    lib.tnk_ksd_rows_static_capacity.restype = c_sz
+    lib.tnk_ksd_rows_static_capacity.argtypes = []
+    lib.tnk_ksd_rows_static.restype = c_int
+    lib.tnk_ksd_rows_static.argtypes = [c_int, c_dbl, c_int, c_vp, c_int, c_vp, c_vp, c_i64, c_i64, c_vp, c_vp,
+                                        ctypes.POINTER(c_int), c_vp]
     lib.tnk_ksd_rows_peers.restype = c_int
     lib.tnk_ksd_rows_peers.argtypes = [c_int, c_dbl, c_int, c_vp, c_int, c_vp, c_vp, c_i64, c_i64,
                                        c_int, c_int, ctypes.POINTER(c_vp), ctypes.POINTER(c_vp), c_vp,

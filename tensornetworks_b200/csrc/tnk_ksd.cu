@@ -24,6 +24,7 @@
 // folded into q_j, the upper part is one LUT fetch per (thread, 8 columns).
 #include "tnk_common.cuh"
 #include "tnk_tc.cuh"
+#include <mutex>
 
 namespace {
 
@@ -799,4 +800,61 @@ extern "C" int tnk_ksd_sym_allreduce(int n_latent, double length_scale, int spli
     TNK_CUDA_OK(cudaMemcpyAsync(ksd, recv + N, sizeof(double), cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
     if (n_launch) *n_launch = l1 + l2;
     return 0;
+}
+
+// ---- tnk_ksd_rows_static: tnk_ksd_rows for callers that cannot provide (or allocate) a workspace --------------------
+// No counterpart in the reference; added for callers that must not call
+// cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  The workspace of
+// tnk_ksd_rows (packed q, per-split row partials, block partials, and for TNK_PREC_TC32 the operand tables) lives in a
+// file-scope device array of TNK_STATIC_SCRATCH_BYTES instead; every GPU that loads the library holds that array until
+// the process exits.  `g_static_scratch` is a host-side stand-in for the symbol in host code, not a device address:
+// the address is looked up once per device with cudaGetSymbolAddress (that device current) and handed to the kernels.
+// Nothing in the workspace accumulates across calls (every slot a kernel reads is written earlier in the same call),
+// so nothing has to be cleared; all calls on one device share the array, so calls that overlap on the GPU (different
+// streams, or graph replays running concurrently) race - serialise them.
+static __device__ __align__(256) unsigned char g_static_scratch[TNK_STATIC_SCRATCH_BYTES];
+
+namespace {
+constexpr int kMaxDevices = 64;
+void* g_static_addr[kMaxDevices];                 // device address of g_static_scratch, per device ordinal
+std::mutex g_static_mutex;
+
+int static_scratch_address(void** out) {
+    int dev = -1;
+    TNK_CUDA_OK(cudaGetDevice(&dev));
+    TNK_REQUIRE(dev >= 0 && dev < kMaxDevices, "tnk_ksd_rows_static: device ordinal %d outside [0,%d)", dev, kMaxDevices);
+    std::lock_guard<std::mutex> lock(g_static_mutex);
+    if (!g_static_addr[dev]) {
+        void* p = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress(&p, g_static_scratch);
+        TNK_REQUIRE(e == cudaSuccess && p, "tnk_ksd_rows_static: cudaGetSymbolAddress failed on device %d: %s", dev,
+                    cudaGetErrorString(e));
+        g_static_addr[dev] = p;
+    }
+    *out = g_static_addr[dev];
+    return 0;
+}
+}  // namespace
+
+extern "C" size_t tnk_ksd_rows_static_capacity(void) { return (size_t)TNK_STATIC_SCRATCH_BYTES; }
+
+extern "C" int tnk_ksd_rows_static(int n_latent, double length_scale, int precision,
+                                   const void* q, int q_dtype, const void* ST, const void* Cst,
+                                   int64_t row_begin, int64_t row_end,
+                                   double* u, double* ksd_part, int* n_launch, void* stream) {
+    Plan p;
+    TNK_REQUIRE(make_plan(n_latent, precision, row_begin, row_end, &p) == 0,
+                "tnk_ksd_rows_static: bad arguments n=%d precision=%d rows=[%lld,%lld)", n_latent, precision,
+                (long long)row_begin, (long long)row_end);
+    TNK_REQUIRE(p.total <= (size_t)TNK_STATIC_SCRATCH_BYTES,
+                "tnk_ksd_rows_static: n=%d precision=%d rows=[%lld,%lld) needs %zu bytes of scratch, the static array holds %zu "
+                "(TNK_STATIC_SCRATCH_BYTES); use tnk_ksd_rows with a caller-provided workspace",
+                n_latent, precision, (long long)row_begin, (long long)row_end, p.total, (size_t)TNK_STATIC_SCRATCH_BYTES);
+    void* scratch = nullptr;
+    if (const int rc = static_scratch_address(&scratch)) return rc;
+    PeerSinks none;
+    none.n = 0;
+    none.rank = 0;
+    return ksd_rows_impl(n_latent, length_scale, precision, q, q_dtype, ST, Cst, row_begin, row_end, u, ksd_part,
+                         scratch, (size_t)TNK_STATIC_SCRATCH_BYTES, n_launch, stream, none);
 }
