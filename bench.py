@@ -403,6 +403,15 @@ def run_ours(args):
                 tables._ws.pop(("sym", rank, world, sp), None)
                 tables._sym_tables.discard(("sym", rank, world, sp))
             ctx["variants"] = variants
+            # ---- what bounds the headline kernel: its timing-only instances with parts of the pipeline compiled out
+            # (tnk_tc.cu DIAG, n = 17..20, 6-step format; results are wrong, nothing here is reported as throughput)
+            if sym_split == "tf32_dot" and 17 <= n <= 20 and not os.environ.get("TNK_TCS_ROWTILES"):
+                limits = {}
+                for name, flag in (("mma_only_ms", 13), ("read_no_fold_ms", 5), ("epilogue_only_ms", 16), ("no_mirrored_part_ms", 1)):
+                    os.environ["TNK_TCS_ABLATE"] = str(flag)
+                    limits[name], _ = time_kernel(lambda: tables.ksd_sym(q_dev, *ops.sym_tile_stripe(rank, world), split=sym_split))
+                os.environ.pop("TNK_TCS_ABLATE", None)
+                ctx["limits"] = limits
         # ---- the all-pairs tile kernel (tnk_ksd_rows, precision tc32) on this rank's rows
         if args.precision == "tc32" and sym:
             full_ms, (u_full, _) = time_kernel(lambda: tables.ksd_rows(q_dev, r0, r1))
@@ -622,8 +631,9 @@ def main():
                         "operand_format": r["sym_split"],
                         "note": ("format tf32_dot keeps only the rank-n score dot product on the MMAs (3 tf32 + 3 bf16 K-steps: the 3xTF32 "
                                  "split of ceil(n/8) algorithmic K-steps); C(z)+C(z') and the T1/T2 terms are added exactly by n+2 fp64 "
-                                 "Kronecker transforms before the tile kernel. With 6 K-steps the kernel is bound by the accumulator "
-                                 "read-out (tmem_readout below), not by the MMA rate: see tile_kernel_variants for the 13- and 9-step formats")}
+                                 "Kronecker transforms before the tile kernel. With 6 K-steps the kernel is bound by its epilogue - the fp32 fold "
+                                 "of every accumulator element into the row and mirrored column sums on the ALU (kernel_limits) - not by the "
+                                 "MMA rate or the TMEM read-out: see tile_kernel_variants for the 13- and 9-step formats")}
             if roofline["frac"] > 1.0:
                 roofline["frac_note"] = "above 1: the sustained peak is a matmul-loop average; see frac_of_burst_peak"
             # second limit of the same kernel: every accumulator tile (64 KB of fp32) leaves TMEM once through
@@ -632,7 +642,7 @@ def main():
             if sm_mhz:
                 tmem_peak = 148 * 64.0 * sm_mhz * 1e6                      # B/s at the clock measured under load
                 tmem_ach = tiles * 65536.0 / kernel_s
-                roofline["binding_limit"] = "tmem_readout" if tmem_ach / tmem_peak > roofline["frac"] else "tensor"
+                roofline["binding_limit"] = "epilogue (ALU fold of the accumulators)" if sum(sym_steps(n, r["sym_split"])) <= 6 else "tensor"
                 roofline["tmem_readout"] = {"achieved_TB/s": tmem_ach / 1e12, "peak_TB/s": tmem_peak / 1e12,
                                             "frac": tmem_ach / tmem_peak, "bytes_per_tile": 65536,
                                             "peak_source": "148 SMs x 64 B/clk x median SM clock of this run"}
@@ -640,7 +650,7 @@ def main():
                     roofline["tmem_readout"]["frac_note"] = (
                         "above 1: the 64 B/clk LDTM figure of B300_MICROARCH.md is not a hard limit for the .16x256b.x8 loads "
                         "used here; the hardware's own figure is sm__mem_tensor_cycles_active in the ncu summary under profiles/")
-            tag = "tcs_tiles"
+            tag = "tcs_tiles" if row_tiles_per_cta == 1 else "tcs_tilesN"
         elif r["algorithm"] == "pairs_sym64":
             tiles = sym64_tiles(n, 0, world)
             steps = (n + 3) // 4
@@ -714,6 +724,14 @@ def main():
                 for sp, ms in ctx["variants"].items()}
             line["tile_kernel_variants"]["note"] = ("tf32: whole bracket on the MMAs; tf32_tile: T1/T2 terms of bits >= 7 through the "
                                                     "Kronecker pass; tf32_dot: only the score dot product on the MMAs (headline)")
+        if "limits" in ctx:
+            lim = ctx["limits"]
+            line["roofline"]["kernel_limits"] = dict(lim, note=(
+                "the same kernel with parts compiled out (timing only): MMAs alone / accumulators read from TMEM but not folded / "
+                "epilogue alone without MMAs / full kernel without the mirrored column sums. The read-out rides on the MMA time, the "
+                "epilogue alone takes about as long as the whole kernel: the fold (1.5 packed fp32 instructions per pair of "
+                "accumulator elements, issue-bound with 2 epilogue warps per scheduler) is the limit, the tensor pipe waits for it"),
+                mma_only_frac_of_tensor_peak=line["roofline"]["achieved"] * r["kernel_ms"] / lim["mma_only_ms"] / line["roofline"]["peak"])
         if "full_ms" in ctx:
             line["full_tile_kernel"] = {"kernel": "tc_rows_kernel (all 4^n ordered pairs, tnk_ksd_rows precision tc32)",
                                         "kernel_ms": ctx["full_ms"], "value": pairs / (ctx["full_ms"] * 1e-3), "unit": UNIT,

@@ -599,7 +599,8 @@ struct TcsParams {
     int64_t n_tiles;               // 2^n / 128
     int col_splits;                // gridDim.y
     int row_tiles;                 // row tiles of this launch (tcs_tilesN_kernel: RT per CTA)
-    int ablate;                    // diagnostics only (TNK_TCS_ABLATE, wrong results): 1 = no mirrored part, 2 = mirrored sums not stored
+    int ablate;                    // diagnostics only (TNK_TCS_ABLATE, wrong results): 1 = no mirrored part, 2 = mirrored sums not stored;
+                                   // + 4 / 12 / 16 select the DIAG instances of tcs_tilesN_kernel<5, 3, RT> (scripts/sym_limits.py)
     float gamma;
     float wl[32];
 };
@@ -1123,7 +1124,9 @@ tcs_tiles_kernel(const __grid_constant__ TcsParams prm, const float* __restrict_
 // tiles are added in registers BEFORE the transposing exchange, so there is one exchange and one RED pair per column
 // tile and warp instead of one per executed tile.  Row tile r of CTA x is tile_offset + tile_stride * (RT x + r); the
 // tiles of a CTA are increasing, so the ones meeting column tile J (J >= I_r) are a prefix r < nact(J).
-template <int NC, int FMT, int RT>
+// DIAG (timing-only instances of scripts/sym_limits.py, results wrong): 4 = accumulators read from TMEM but not folded,
+// 12 = not read either (MMAs alone), 16 = no MMAs (the epilogue alone).
+template <int NC, int FMT, int RT, int DIAG = 0>
 __global__ void __launch_bounds__(64 + 128 * 2, 1)
 tcs_tilesN_kernel(const __grid_constant__ TcsParams prm, const float* __restrict__ B_tab,
                   const float* __restrict__ ST, const float* __restrict__ Cst, const float* __restrict__ qT,
@@ -1226,15 +1229,17 @@ tcs_tilesN_kernel(const __grid_constant__ TcsParams prm, const float* __restrict
                 const uint32_t a_addr = tmem_base + (uint32_t)(kTmemA + r * 8 * KS);
                 if (elect_one()) {
                     constexpr uint32_t cu = kChunkBytes >> 4;
+                    if constexpr (!(DIAG & 16)) {
 #pragma unroll
-                    for (int ks = 0; ks < S32; ++ks) {
-                        const uint64_t db = b_desc + (uint64_t)((uint32_t)(2 * ks) * cu + (cu << 16));
-                        umma_tf32_ts(d_addr, a_addr + (uint32_t)(8 * ks), db, kIdesc, ks > 0 ? 1u : 0u);
-                    }
+                        for (int ks = 0; ks < S32; ++ks) {
+                            const uint64_t db = b_desc + (uint64_t)((uint32_t)(2 * ks) * cu + (cu << 16));
+                            umma_tf32_ts(d_addr, a_addr + (uint32_t)(8 * ks), db, kIdesc, ks > 0 ? 1u : 0u);
+                        }
 #pragma unroll
-                    for (int k = 0; k < S16; ++k) {
-                        const uint64_t db = b_desc + (uint64_t)((uint32_t)(K32 + 2 * k) * cu + (cu << 16));
-                        umma_bf16_ts(d_addr, a_addr + (uint32_t)(8 * (S32 + k)), db, kIdescBf16, (S32 + k) > 0 ? 1u : 0u);
+                        for (int k = 0; k < S16; ++k) {
+                            const uint64_t db = b_desc + (uint64_t)((uint32_t)(K32 + 2 * k) * cu + (cu << 16));
+                            umma_bf16_ts(d_addr, a_addr + (uint32_t)(8 * (S32 + k)), db, kIdescBf16, (S32 + k) > 0 ? 1u : 0u);
+                        }
                     }
                     if (r + 1 == nact) umma_commit(bar_empty + s);      // the stage is free once the LAST row tile has read it
                     umma_commit(bar_tfull + ts);
@@ -1392,8 +1397,13 @@ tcs_tilesN_kernel(const __grid_constant__ TcsParams prm, const float* __restrict
                     tc_fence_after();
                     const uint32_t taddr = tmem_base + ((uint32_t)lq << 16) + (uint32_t)(ts * kTile + colbase);
                     uint32_t v0[4 * MC], v1[4 * MC];
-                    TNK_LD_16x256b_x8(v0, taddr);
-                    TNK_LD_16x256b_x8(v1, taddr + (16u << 16));
+                    if constexpr (!(DIAG & 8)) {
+                        TNK_LD_16x256b_x8(v0, taddr);
+                        TNK_LD_16x256b_x8(v1, taddr + (16u << 16));
+                    } else {
+#pragma unroll
+                        for (int x = 0; x < 4 * MC; ++x) v0[x] = v1[x] = 0u;
+                    }
                     asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
                     tc_fence_before();
                     __syncwarp();
@@ -1414,8 +1424,12 @@ tcs_tilesN_kernel(const __grid_constant__ TcsParams prm, const float* __restrict
                                 cacc[m] = __ffma2_rn(p, make_float2(qw[k], qw[k]), cacc[m]);
                             }
                     };
-                    fold(v0, 0);
-                    fold(v1, 1);
+                    if constexpr (!(DIAG & 4)) {
+                        fold(v0, 0);
+                        fold(v1, 1);
+                    } else {
+                        racc[0].x = __uint_as_float(v0[0] ^ v1[5]);      // keep the loads alive
+                    }
 #pragma unroll
                     for (int k = 0; k < 4; ++k) uch[r][k] = fmaf(wg, racc[k].x + racc[k].y, uch[r][k]);
                 }
@@ -1590,6 +1604,15 @@ int launch_symN(const TcsParams& prm, dim3 grid, const float* B_tab, const float
                 const float* qT, double* ucol, cudaStream_t st) {
     const size_t smem = TcsSmem<NC, FMT>::total;
     auto kern = tcs_tilesN_kernel<NC, FMT, RT>;
+    if constexpr (NC == 5 && FMT == 3) {
+        // timing-only instances of scripts/sym_limits.py (n = 17..20, 6-step format): parts of the pipeline compiled out
+        switch (prm.ablate & 28) {
+            case 4: kern = tcs_tilesN_kernel<NC, FMT, RT, 4>; break;     // accumulators read, not folded
+            case 12: kern = tcs_tilesN_kernel<NC, FMT, RT, 12>; break;   // accumulators not read: the MMAs alone
+            case 16: kern = tcs_tilesN_kernel<NC, FMT, RT, 16>; break;   // no MMAs: the epilogue alone
+            default: break;
+        }
+    }
     TNK_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     grid.x = (grid.x + RT - 1) / RT;
     kern<<<grid, 64 + 128 * 2, smem, st>>>(prm, B_tab, ST, Cst, qT, ucol);
