@@ -111,6 +111,15 @@ class ClassicalBornMachine(nn.Module):
         if c is None or c["key"] != key or c[which]:
             q, H = ops.born_softmax_entropy(self.params)
             c = self._pair_cache = {"key": key, "q": q, "H": H, "q_taken": False, "H_taken": False}
+            if q.requires_grad:
+                # q and H are two outputs of ONE autograd node: once a backward pass has run through either of them
+                # the node's buffers are freed, so the other half must not be handed out any more (separate backward
+                # calls for the KSD and the entropy term, gradient accumulation) - drop the pair when that happens
+                def _invalidate(_grad, pair=c):
+                    if self._pair_cache is pair:
+                        self._pair_cache = None
+                q.register_hook(_invalidate)
+                H.register_hook(_invalidate)
         c[which] = True
         return c["q"], c["H"]
 

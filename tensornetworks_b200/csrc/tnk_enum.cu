@@ -129,96 +129,115 @@ __device__ __forceinline__ double div_by(double a, double p, double rp) {
 }
 
 // NP = padded score length (compile time: the loops over score components unroll and the shared-memory
-// strides are constants), n <= NP at run time.
-template <typename T, int NP>
-__global__ void __launch_bounds__(256)
-score_kernel(int n, int64_t N, double alpha, double gamma,
+// strides are constants), n <= NP at run time.  One fp64 staging tile serves both outputs (S64 in variable order,
+// the packed table in bit order and compute type): 256 x (NP + 1) doubles = 43 KB at n = 20, five CTAs per SM, so the
+// gather / divide / copy-out phases of different CTAs overlap.
+constexpr int kScoreRows = 64;    // states per CTA of the score kernel
+// NN = n when it is a compile-time constant of the instance (NP - 3 <= n <= NP, n >= 1: the k < n tests, the flip masks
+// and the copy-out strides fold), -1 = run-time n (n = 0).
+template <typename T, int NP, int NN>
+__global__ void __launch_bounds__(kScoreRows)
+score_kernel(int n_rt, int64_t N, double alpha, double gamma,
              const double* __restrict__ P, double* __restrict__ S64,
              T* __restrict__ ST, T* __restrict__ Cst) {
-    // Rows are staged in shared memory with the ODD stride NP + 1 so that the per-thread row writes are
-    // bank-conflict-free; the copy-out then walks the tile linearly.
+    // Rows are staged with the ODD stride NP + 1 so that the per-thread row writes are bank-conflict-free; the
+    // copy-outs then walk the tile linearly.
     constexpr int kStride = NP + 1;
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    double* sS = reinterpret_cast<double*>(smem_raw);                                          // [256][NP+1], only if S64
-    T* sT = reinterpret_cast<T*>(smem_raw + (S64 ? (size_t)256 * kStride * sizeof(double) : 0)); // [256][NP+1]
+    double* sS = reinterpret_cast<double*>(smem_raw);                                          // [kScoreRows][NP+1]
+    const int n = NN >= 0 ? NN : n_rt;
     const int tid = threadIdx.x;
-    const int64_t base = (int64_t)blockIdx.x * 256;
+    const int64_t base = (int64_t)blockIdx.x * kScoreRows;
     const int64_t i = base + tid;
     double Rsum = 0.0, rho0 = 0.0;
-    if (ST) {
-#pragma unroll
-        for (int p = 0; p < NP; ++p) sT[tid * kStride + p] = (T)0;
-    }
     if (i < N) {
         const double p = P[i];
         const bool dead = fabs(p) < 1e-12;  // stein_utils.py:126
         const double rp = dead ? 0.0 : __drcp_rn(p);
         const uint32_t iu = (uint32_t)i;     // n <= 30
+        constexpr int G = (NP % 8 == 0) ? 8 : 4;     // flipped reads in flight; arithmetic in the original order
 #pragma unroll
-        for (int k0 = 0; k0 < NP; k0 += 4) {         // four flipped reads in flight; arithmetic in the original order
-            double pf[4];
+        for (int k0 = 0; k0 < NP; k0 += G) {
+            double pf[G];
 #pragma unroll
-            for (int c = 0; c < 4; ++c) {
+            for (int c = 0; c < G; ++c) {
                 const int k = k0 + c;
                 pf[c] = (k < n && !dead) ? P[iu ^ (1u << (n - 1 - k))] : 0.0;
             }
 #pragma unroll
-            for (int c = 0; c < 4; ++c) {
+            for (int c = 0; c < G; ++c) {
                 const int k = k0 + c;
+                double s = 0.0;
                 if (k < n) {
                     const int bit = n - 1 - k;
-                    double s = 0.0;
                     if (!dead) s = __dsub_rn(1.0, div_by(pf[c], p, rp));  // :134
-                    if (S64) sS[tid * kStride + k] = s;
-                    if (ST) sT[tid * kStride + bit] = (T)s;
                     const double r = 1.0 - s;
                     Rsum += r;
                     if ((iu >> bit) & 1u) rho0 += r;
                 }
+                sS[tid * kStride + k] = s;                                 // zero beyond n and in dead rows
             }
         }
         if (Cst) Cst[i] = (T)(alpha * Rsum + gamma * rho0);
-    } else if (Cst) {
-        Cst[i] = (T)0;  // padding rows of the packed table
+    } else {
+#pragma unroll
+        for (int k = 0; k < NP; ++k) sS[tid * kStride + k] = 0.0;          // padding rows of the packed table
+        if (Cst) Cst[i] = (T)0;
     }
     __syncthreads();
     if (S64 && n > 0) {
-        const int live = (int)(N - base < 256 ? (N - base > 0 ? N - base : 0) : 256) * n;
-        const int dq = 256 / n, dr = 256 % n;              // element t = tid + 256 j sits in row t / n, column t % n
+        const int live = (int)(N - base < kScoreRows ? (N - base > 0 ? N - base : 0) : kScoreRows) * n;
+        const int dq = kScoreRows / n, dr = kScoreRows % n;  // element t = tid + kScoreRows j sits in row t / n, column t % n
         int row = tid / n, col = tid % n;
         double* out = S64 + base * n;
-        for (int t = tid; t < live; t += 256) {
-            out[t] = sS[row * kStride + col];
+#pragma unroll
+        for (int t = tid; t < live; t += kScoreRows) {
+            __stcs(out + t, sS[row * kStride + col]);     // streaming stores: the tables must not evict P from L2
             row += dq; col += dr;
             if (col >= n) { col -= n; ++row; }
         }
     }
     if (ST) {
-        // 16-byte stores: a row of NP elements is NP*sizeof(T)/16 chunks
+        // 16-byte stores: a row of NP elements is NP*sizeof(T)/16 chunks; column `bit` of the packed table is
+        // variable n - 1 - bit, zero for bit >= n
         constexpr int kPer = 16 / (int)sizeof(T);           // elements per chunk
         constexpr int kChunksPerRow = NP / kPer;
         T* out = ST + base * NP;
 #pragma unroll
         for (int c = 0; c < kChunksPerRow; ++c) {
-            const int ch = tid + 256 * c;                   // chunk index in the tile
+            const int ch = tid + kScoreRows * c;                   // chunk index in the tile
             const int row = ch / kChunksPerRow, col = (ch % kChunksPerRow) * kPer;
             T v[kPer];
 #pragma unroll
-            for (int e = 0; e < kPer; ++e) v[e] = sT[row * kStride + col + e];
-            *reinterpret_cast<uint4*>(out + (size_t)ch * kPer) = *reinterpret_cast<const uint4*>(v);
+            for (int e = 0; e < kPer; ++e) {
+                const int k = n - 1 - (col + e);
+                v[e] = k >= 0 ? (T)sS[row * kStride + k] : (T)0;
+            }
+            __stcs(reinterpret_cast<uint4*>(out + (size_t)ch * kPer), *reinterpret_cast<const uint4*>(v));
         }
     }
 }
 
+template <typename T, int NP, int NN>
+int launch_score_n(int n, int64_t N, int64_t rows, double alpha, double gamma, const double* P, double* S64,
+                   T* ST, T* Cst, cudaStream_t st) {
+    const unsigned blocks = (unsigned)((rows + kScoreRows - 1) / kScoreRows);
+    const size_t smem = (size_t)kScoreRows * (NP + 1) * sizeof(double);
+    TNK_CUDA_OK(cudaFuncSetAttribute(score_kernel<T, NP, NN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    score_kernel<T, NP, NN><<<blocks, kScoreRows, smem, st>>>(n, N, alpha, gamma, P, S64, ST, Cst);
+    TNK_CUDA_OK(cudaGetLastError());
+    return 0;
+}
 template <typename T, int NP>
 int launch_score(int n, int64_t N, int64_t rows, double alpha, double gamma, const double* P, double* S64,
                  T* ST, T* Cst, cudaStream_t st) {
-    const unsigned blocks = (unsigned)((rows + 255) / 256);
-    const size_t smem = (size_t)256 * (NP + 1) * ((S64 ? sizeof(double) : 0) + sizeof(T));
-    TNK_CUDA_OK(cudaFuncSetAttribute(score_kernel<T, NP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    score_kernel<T, NP><<<blocks, 256, smem, st>>>(n, N, alpha, gamma, P, S64, ST, Cst);
-    TNK_CUDA_OK(cudaGetLastError());
-    return 0;
+    switch (NP - n) {
+        case 0: return launch_score_n<T, NP, NP>(n, N, rows, alpha, gamma, P, S64, ST, Cst, st);
+        case 1: return launch_score_n<T, NP, NP - 1>(n, N, rows, alpha, gamma, P, S64, ST, Cst, st);
+        case 2: return launch_score_n<T, NP, NP - 2>(n, N, rows, alpha, gamma, P, S64, ST, Cst, st);
+        case 3: return launch_score_n<T, NP, NP - 3>(n, N, rows, alpha, gamma, P, S64, ST, Cst, st);
+        default: return launch_score_n<T, NP, -1>(n, N, rows, alpha, gamma, P, S64, ST, Cst, st);
+    }
 }
 
 template <typename T>

@@ -100,6 +100,29 @@ def test_born_machine_streaming_matches_tensor_path():
     a.sum().backward(); b.sum().backward()
 
 
+def test_separate_backward_passes_for_q_and_entropy():
+    """q and H of one step come from one autograd node; a backward pass through q alone must not leave a cached H with
+    a freed graph behind (separate backward calls for the two loss terms, gradient accumulation)."""
+    from tensornetworks_b200.born_machine_classical_sim import ClassicalBornMachine
+    torch.manual_seed(1)
+    bm = ClassicalBornMachine(16, use_logits=True).cuda()
+    w = torch.linspace(0.0, 1.0, 1 << 16, device="cuda")
+    (bm.get_probabilities().squeeze() * w).sum().backward()          # backward through q only
+    g_q = bm.params.grad.clone()
+    bm.params.grad = None
+    (-0.01 * bm.entropy()).backward()                                 # no parameter update in between
+    g_h = bm.params.grad.clone()
+    bm.params.grad = None
+    p, H = bm.get_probabilities(), bm.entropy()
+    ((p.squeeze() * w).sum() - 0.01 * H).backward()
+    assert float((bm.params.grad - (g_q + g_h)).abs().max()) <= 1e-6 * float((g_q + g_h).abs().max()) + 1e-12
+    # the other order, and twice each
+    bm.params.grad = None
+    bm.entropy().backward()
+    bm.get_probabilities().sum().backward()
+    bm.entropy().backward()
+
+
 def test_trainer_epochs_with_and_without_streaming_kernels(monkeypatch):
     from tensornetworks_b200.born_machine_classical_sim import ClassicalBornMachine
     from tensornetworks_b200.ksd_vi import KSDVariationalInference
