@@ -528,10 +528,24 @@ class _KsdQuadraticForm(torch.autograd.Function):
                 u, part = combine_row_shards(u[r0:r1], part, N, rank, world, group)
         ctx.save_for_backward(u)
         ctx.q_meta = (q.dtype, q.device)
+        ctx.grad_host = None
+        if q.device.type == "cpu" and ctx.needs_input_grad[0]:
+            # q lives on the host and wants a gradient: dK/dq = 2u goes to pinned memory behind K on the same stream, so
+            # the one synchronisation below covers both and backward() finds its result on the host (no second kernel,
+            # copy and synchronisation after the autograd dispatch)
+            g = u * 2.0
+            if g.dtype != q.dtype:
+                g = g.to(q.dtype)
+            ctx.grad_host = torch.empty(g.shape, dtype=q.dtype, pin_memory=True)
+            ctx.grad_host.copy_(g, non_blocking=True)
         return _host_result(part.reshape(()), (torch.float64, q.device))
 
     @staticmethod
     def backward(ctx, grad_out):
+        if ctx.grad_host is not None and not grad_out.is_cuda:
+            g, ctx.grad_host = ctx.grad_host, None        # handed over once (autograd may adopt it as q.grad without a copy)
+            scale = float(grad_out)
+            return (g if scale == 1.0 else g.mul_(scale)), None, None, None, None
         (u,) = ctx.saved_tensors
         scale = grad_out.to(u.device, torch.float64) if grad_out.is_cuda else float(grad_out) * 1.0
         grad = u * (2.0 * scale)

@@ -201,6 +201,27 @@ def test_q_dtypes_and_cpu_q(ops, golden):
     assert np.allclose(q.grad.cpu().numpy(), golden["spr_g_ramp"] / (2 * np.sqrt(golden["spr_K_ramp"])), rtol=1e-9)
 
 
+def test_cpu_q_gradient_arrives_with_the_value(ops, golden):
+    """A host q that wants a gradient gets dK/dq downloaded behind K (one synchronisation); scaled upstream gradients,
+    a second backward through a retained graph and q that needs no gradient all give the reference's numbers."""
+    bn = get_sprinkler_network(False)
+    tabs = _tables(ops, bn, {'W': 1}, ['C', 'S', 'R'], "fp64")
+    gref, Kref = golden["spr_g_ramp"], float(golden["spr_K_ramp"])
+    q = torch.tensor(golden["spr_q_ramp"], dtype=torch.float64, requires_grad=True)          # CPU fp64
+    loss = torch.sqrt(ops.ksd_quadratic_form(q, tabs).clamp(min=1e-12))                       # upstream gradient != 1
+    loss.backward()
+    assert np.allclose(q.grad.numpy(), gref / (2 * np.sqrt(Kref)), rtol=1e-9)
+    q.grad = None
+    K = ops.ksd_quadratic_form(q, tabs)
+    K.backward(retain_graph=True)
+    assert np.allclose(q.grad.numpy(), gref, rtol=1e-9)
+    K.backward()                                                                              # second pass: accumulates
+    assert np.allclose(q.grad.numpy(), 2 * gref, rtol=1e-9)
+    with torch.no_grad():
+        assert np.isclose(ops.ksd_quadratic_form(q, tabs).item(), Kref, rtol=1e-9)
+    assert np.isclose(ops.ksd_quadratic_form(q.detach(), tabs).item(), Kref, rtol=1e-9)
+
+
 # ---------------------------------------------------------------- mode-product (Kronecker) path
 def _eval_mp(ops, tabs, q):
     qd = torch.as_tensor(q, dtype=torch.float64, device="cuda").requires_grad_(True)
