@@ -24,6 +24,7 @@
 // folded into q_j, the upper part is one LUT fetch per (thread, 8 columns).
 #include "tnk_common.cuh"
 #include "tnk_tc.cuh"
+#include <stdlib.h>
 #include <mutex>
 
 namespace {
@@ -681,9 +682,17 @@ int make_sym_plan(int n, int split, int tile_offset, int tile_stride, SymPlan* p
     p->T = p->N / TNK_TC_TILE;
     p->row_tiles = tile_offset < p->T ? (int)((p->T - tile_offset + tile_stride - 1) / tile_stride) : 0;
     const size_t b_bytes = tnk_tcs_table_bytes(n, split, p->N);
+    // column splits: enough CTAs (row-tile groups x splits) for the block scheduler to balance the triangle - a CTA of
+    // the row-tile kernel owns up to 4 row tiles, and the longest one must stay a small part of an SM's share
+    const int rt = split == TNK_SYM_SPLIT_TF32_DOT ? 4 : 2;
+    const int64_t row_groups = (p->row_tiles + rt - 1) / rt;
     int splits = 1;
-    while ((int64_t)p->row_tiles * splits < 8 * 148 && splits * 2 <= p->T) splits *= 2;
+    while (row_groups * splits < 32 * 148 && splits * 2 <= p->T) splits *= 2;   // scripts/sym_splits.py: 1/8 stripe at n = 20 14.56 (2 splits) -> 13.87 ms (32)
     while ((b_bytes / splits) > ((size_t)32 << 20) && splits * 2 <= p->T) splits *= 2;
+    if (const char* e = getenv("TNK_SYM_SPLITS")) {          // measurement override (scripts/sym_splits.py)
+        const int v = atoi(e);
+        if (v >= 1 && v <= p->T && (v & (v - 1)) == 0) splits = v;
+    }
     p->splits = splits;
     p->finish_blocks = (p->N + 255) / 256;
     size_t off = 0;
