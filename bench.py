@@ -724,6 +724,14 @@ def main():
                 for sp, ms in ctx["variants"].items()}
             line["tile_kernel_variants"]["note"] = ("tf32: whole bracket on the MMAs; tf32_tile: T1/T2 terms of bits >= 7 through the "
                                                     "Kronecker pass; tf32_dot: only the score dot product on the MMAs (headline)")
+        if r["algorithm"] == "pairs_sym":
+            # the epilogue's own roofline: 3 fp32 lane-operations per executed pair (weight, row sum, mirrored sum) against the
+            # FMA rate measured in this run (packed FFMA2 occupies the FMA pipe for two cycles: no gain over FFMA in lane-ops)
+            fold_ops = line["roofline"]["executed_tiles_128x128"] * 16384.0 * 3.0
+            line["roofline"]["epilogue_alu"] = {
+                "lane_ops_per_executed_pair": 3, "achieved": fold_ops / (r["kernel_ms"] * 1e-3) / 1e12, "peak": r["peak_rate"] / 1e12,
+                "unit": "Tlane-op/s", "frac": fold_ops / (r["kernel_ms"] * 1e-3) / r["peak_rate"],
+                "peak_source": "tnk_alu_peak FFMA2-chain probe measured in this run"}
         if "limits" in ctx:
             lim = ctx["limits"]
             line["roofline"]["kernel_limits"] = dict(lim, note=(

@@ -224,3 +224,29 @@ def test_sym_tile_format(ops, n, seed, split):
     q32 = q.float()
     u3, k3 = tabs.ksd_sym(q32, split=split)
     assert (u3 - u1).abs().max().item() <= 1e-5 * scale
+
+
+@pytest.mark.parametrize("split", ["tf32", "tf32_tile", "tf32_dot"])
+@pytest.mark.parametrize("rowtiles,splits", [("1", "1"), ("2", "4"), ("4", "2"), ("4", "16")])
+def test_row_tile_instances_and_column_splits_agree(ops, monkeypatch, split, rowtiles, splits):
+    """Every instance of the tile kernel (TNK_TCS_ROWTILES = 1: one row tile per CTA, 2 / 4: tcs_tilesN_kernel) and any
+    number of column splits gives the oracle's result, on stripes with a ragged last CTA (22 and 21 row tiles) and on the
+    whole problem."""
+    n = 13
+    monkeypatch.setenv("TNK_TCS_ROWTILES", rowtiles)
+    monkeypatch.setenv("TNK_SYM_SPLITS", splits)
+    bn, lat, obs, x = random_binary_bn(n, seed=4)
+    tabs = ops.SteinTables.from_network(bn, x, lat, precision="tc32")
+    S = orc.score_table(orc.joint_table(bn, x, lat), n)
+    q = random_q(1 << n, seed=4)
+    Kref, gref = orc.ksd_modeproduct(q.numpy(), S, n)
+    qd = q.cuda()
+    u = torch.zeros(1 << n, dtype=torch.float64, device="cuda")
+    K = 0.0
+    for off in range(3):                                   # 64 tiles dealt to 3 "ranks": 22, 21, 21 row tiles
+        up, part = tabs.ksd_sym(qd, off, 3, split=split)
+        u += up
+        K += float(part.item())
+    _check(K, 2.0 * u.cpu().numpy(), Kref, gref)
+    up, part = tabs.ksd_sym(qd, split=split)               # 64 row tiles, one call
+    _check(float(part.item()), 2.0 * up.cpu().numpy(), Kref, gref)
