@@ -407,7 +407,8 @@ def run_ours(args):
             # (tnk_tc.cu DIAG, n = 17..20, 6-step format; results are wrong, nothing here is reported as throughput)
             if sym_split == "tf32_dot" and 17 <= n <= 20 and not os.environ.get("TNK_TCS_ROWTILES"):
                 limits = {}
-                for name, flag in (("mma_only_ms", 13), ("read_no_fold_ms", 5), ("epilogue_only_ms", 16), ("no_mirrored_part_ms", 1)):
+                for name, flag in (("mma_only_ms", 13), ("read_no_fold_ms", 5), ("epilogue_only_ms", 16), ("epilogue_only_no_mirrored_ms", 17),
+                                   ("readout_loop_only_ms", 21), ("no_mirrored_part_ms", 1)):
                     os.environ["TNK_TCS_ABLATE"] = str(flag)
                     limits[name], _ = time_kernel(lambda: tables.ksd_sym(q_dev, *ops.sym_tile_stripe(rank, world), split=sym_split))
                 os.environ.pop("TNK_TCS_ABLATE", None)
@@ -737,8 +738,9 @@ def main():
             line["roofline"]["kernel_limits"] = dict(lim, note=(
                 "the same kernel with parts compiled out (timing only): MMAs alone / accumulators read from TMEM but not folded / "
                 "epilogue alone without MMAs / full kernel without the mirrored column sums. The read-out rides on the MMA time, the "
-                "epilogue alone takes about as long as the whole kernel: the fold (1.5 packed fp32 instructions per pair of "
-                "accumulator elements, issue-bound with 2 epilogue warps per scheduler) is the limit, the tensor pipe waits for it"),
+                "epilogue alone takes about as long as the whole kernel, and it is the sum of the read-out loop alone and the fold "
+                "(epilogue_only_no_mirrored = readout_loop_only + fold at the FMA-pipe floor): TMEM read-out and fp32 fold of a "
+                "scheduler do not overlap; the tensor pipe waits for them"),
                 mma_only_frac_of_tensor_peak=line["roofline"]["achieved"] * r["kernel_ms"] / lim["mma_only_ms"] / line["roofline"]["peak"],
                 mma_only_frac_note="above 1 is possible: the sustained peak is a long matmul-loop average under power limits, "
                                    "the MMA-only instance draws less power than a full GEMM")

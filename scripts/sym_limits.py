@@ -16,7 +16,8 @@ a.record(); b.record()
 out = {}
 for split in ("tf32_dot",):
     for name, flag in (("full", 0), ("no mirrored part", 1), ("read, no fold, no mirrored part", 5), ("MMAs only (no read, no fold)", 13),
-                       ("epilogue only (no MMAs)", 16), ("epilogue only, no mirrored part", 17)):
+                       ("epilogue only (no MMAs)", 16), ("epilogue only, no mirrored part", 17),
+                       ("read-out loop only (no MMAs, no fold, no mirrored part)", 21)):
         os.environ["TNK_TCS_ABLATE"] = str(flag)
         tc.ksd_sym(q, split=split)
         times = []

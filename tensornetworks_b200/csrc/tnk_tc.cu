@@ -1125,7 +1125,7 @@ tcs_tiles_kernel(const __grid_constant__ TcsParams prm, const float* __restrict_
 // tile and warp instead of one per executed tile.  Row tile r of CTA x is tile_offset + tile_stride * (RT x + r); the
 // tiles of a CTA are increasing, so the ones meeting column tile J (J >= I_r) are a prefix r < nact(J).
 // DIAG (timing-only instances of scripts/sym_limits.py, results wrong): 4 = accumulators read from TMEM but not folded,
-// 12 = not read either (MMAs alone), 16 = no MMAs (the epilogue alone).
+// 12 = not read either (MMAs alone), 16 = no MMAs (the epilogue alone), 20 = no MMAs and no fold (the read-out loop alone).
 template <int NC, int FMT, int RT, int DIAG = 0>
 __global__ void __launch_bounds__(64 + 128 * 2, 1)
 tcs_tilesN_kernel(const __grid_constant__ TcsParams prm, const float* __restrict__ B_tab,
@@ -1610,6 +1610,7 @@ int launch_symN(const TcsParams& prm, dim3 grid, const float* B_tab, const float
             case 4: kern = tcs_tilesN_kernel<NC, FMT, RT, 4>; break;     // accumulators read, not folded
             case 12: kern = tcs_tilesN_kernel<NC, FMT, RT, 12>; break;   // accumulators not read: the MMAs alone
             case 16: kern = tcs_tilesN_kernel<NC, FMT, RT, 16>; break;   // no MMAs: the epilogue alone
+            case 20: kern = tcs_tilesN_kernel<NC, FMT, RT, 20>; break;   // no MMAs, accumulators read but not folded: the read-out loop alone
             default: break;
         }
     }
