@@ -1674,6 +1674,11 @@ int tnk_tcs_launch(int n, int fmt, double gamma, const double* wl, const float* 
     {
         const char* e = getenv("TNK_TCS_ABLATE");      // ablation runs of scripts/sym_ablate.py: results are WRONG when set
         prm.ablate = e ? atoi(e) : 0;
+        static bool warned = false;
+        if (prm.ablate && !warned) {
+            warned = true;
+            fprintf(stderr, "libtnk_b200: TNK_TCS_ABLATE=%d - timing-only mode of tnk_ksd_sym, its results are WRONG\n", prm.ablate);
+        }
     }
     for (int h = 0; h < 32; ++h) prm.wl[h] = (float)wl[h];
     if (ev_start) TNK_CUDA_OK(cudaEventRecord(ev_start, st));
