@@ -43,6 +43,8 @@ __device__ __forceinline__ float2 ffma2(float2 a, float2 b, float2 c) {
 // MODE 3: loads (16x256b) then 96 FFMA2 on the loaded registers, per warp (the tile kernel's order: serial per warp)
 // MODE 4: warps 0-3 only load, warps 4-7 only compute (two warps per scheduler: one loads, one computes)
 // MODE 5: loads for the NEXT iteration issued before the 96 FFMA2 on the current registers (register double buffer)
+// MODE 6: 96 FFMA2 per warp on warps 0-3 only (one warp per scheduler): the per-warp issue cadence of FFMA2
+// MODE 7: warps 0-3 load and compute on even iterations, warps 4-7 on odd ones (two warps per scheduler, alternate tiles)
 template <int MODE>
 __global__ void __launch_bounds__(256, 1) probe(float* out, int iters, long long* cycles) {
     __shared__ uint32_t slot;
@@ -105,6 +107,14 @@ __global__ void __launch_bounds__(256, 1) probe(float* out, int iters, long long
             } else {
                 compute(v0, v1);
             }
+        } else if (MODE == 6) {
+            if (warp < 4) compute(v0, v1);
+        } else if (MODE == 7) {
+            if (((warp >> 2) ^ it) & 1) {
+                load(v0, v1);
+                asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+                compute(v0, v1);
+            }
         } else if (MODE == 5) {
             asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
             if (it & 1) { load(v0, v1); compute(w0, w1); } else { load(w0, w1); compute(v0, v1); }
@@ -161,5 +171,7 @@ int main() {
     run<3>("load then 96 FFMA2 per warp (serial per warp), 8 warps", 65536.0, 8 * 96.0);
     run<4>("warps 0-3 load (32 KB), warps 4-7 compute", 32768.0, 4 * 96.0);
     run<5>("register double buffer: next loads in flight during 96 FFMA2", 65536.0, 8 * 96.0);
+    run<6>("96 FFMA2 per warp, warps 0-3 only (one warp per scheduler)", 0.0, 4 * 96.0);
+    run<7>("alternate iterations: warps 0-3 even, warps 4-7 odd, load (32 KB) then 96 FFMA2", 32768.0, 4 * 96.0);
     return 0;
 }
