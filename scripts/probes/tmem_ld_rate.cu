@@ -44,10 +44,14 @@ __device__ __forceinline__ float2 ffma2(float2 a, float2 b, float2 c) {
 // MODE 4: warps 0-3 only load, warps 4-7 only compute (two warps per scheduler: one loads, one computes)
 // MODE 5: loads for the NEXT iteration issued before the 96 FFMA2 on the current registers (register double buffer)
 // MODE 6: 96 FFMA2 per warp on warps 0-3 only (one warp per scheduler): the per-warp issue cadence of FFMA2
+// MODE 8: as MODE 0 with the tcgen05 fences of the tile kernel around the loads (after_thread_sync before, before_thread_sync after)
+// MODE 9: as MODE 8 plus __syncwarp and an mbarrier arrive by lane 0 (the stage release of the tile kernel)
 // MODE 7: warps 0-3 load and compute on even iterations, warps 4-7 on odd ones (two warps per scheduler, alternate tiles)
 template <int MODE>
 __global__ void __launch_bounds__(256, 1) probe(float* out, int iters, long long* cycles) {
     __shared__ uint32_t slot;
+    __shared__ uint64_t bar;
+    if (threadIdx.x == 0) asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"((uint32_t)__cvta_generic_to_shared(&bar)), "r"(8));
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     if (warp == 0) {
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"((uint32_t)__cvta_generic_to_shared(&slot)), "r"(512) : "memory");
@@ -106,6 +110,15 @@ __global__ void __launch_bounds__(256, 1) probe(float* out, int iters, long long
                 asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
             } else {
                 compute(v0, v1);
+            }
+        } else if (MODE == 8 || MODE == 9) {
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            load(v0, v1);
+            asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+            asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+            if (MODE == 9) {
+                __syncwarp();
+                if (lane == 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"((uint32_t)__cvta_generic_to_shared(&bar)) : "memory");
             }
         } else if (MODE == 6) {
             if (warp < 4) compute(v0, v1);
@@ -171,6 +184,8 @@ int main() {
     run<3>("load then 96 FFMA2 per warp (serial per warp), 8 warps", 65536.0, 8 * 96.0);
     run<4>("warps 0-3 load (32 KB), warps 4-7 compute", 32768.0, 4 * 96.0);
     run<5>("register double buffer: next loads in flight during 96 FFMA2", 65536.0, 8 * 96.0);
+    run<8>("read tile with tcgen05.fence after/before around the loads", 65536.0, 0.0);
+    run<9>("read tile with fences, __syncwarp and mbarrier arrive", 65536.0, 0.0);
     run<6>("96 FFMA2 per warp, warps 0-3 only (one warp per scheduler)", 0.0, 4 * 96.0);
     run<7>("alternate iterations: warps 0-3 even, warps 4-7 odd, load (32 KB) then 96 FFMA2", 32768.0, 4 * 96.0);
     return 0;
