@@ -702,8 +702,9 @@ int make_sym_plan(int n, int split, int tile_offset, int tile_stride, SymPlan* p
     p->off_block = take((size_t)(p->finish_blocks + 1) * sizeof(double));
     p->off_b = take(b_bytes);
     p->off_hib = off;
-    if (split == TNK_SYM_SPLIT_TF32_TILE && tile_offset == 0) p->off_hib = take(tnk_hibits_ws_bytes(n, 7, 0));
-    if (split == TNK_SYM_SPLIT_TF32_DOT && tile_offset == 0) p->off_hib = take(tnk_hibits_ws_bytes(n, 0, 1));
+    // every call takes its share of the Kronecker side pass (bit positions offset, offset + stride, ...; C terms with offset 0)
+    if (split == TNK_SYM_SPLIT_TF32_TILE) p->off_hib = take(tnk_hibits_ws_bytes(n, 7, 0, tile_offset, tile_stride));
+    if (split == TNK_SYM_SPLIT_TF32_DOT) p->off_hib = take(tnk_hibits_ws_bytes(n, 0, tile_offset == 0, tile_offset, tile_stride));
     p->total = off;
     return 0;
 }

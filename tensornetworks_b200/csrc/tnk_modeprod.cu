@@ -563,60 +563,77 @@ namespace {
 // g and C from the packed tables in their own type (fp32: exactly as the tile kernel forms them; fp64 for tnk_ksd_sym64)
 template <typename TS>
 __global__ void __launch_bounds__(256)
-hib_build_kernel(int n, int np, int p_lo, int with_c, int64_t N, TS gamma, const TS* __restrict__ ST,
+hib_build_kernel(int n, int np, int p0, int p_stride, int cnt, int with_c, int64_t N, TS gamma, const TS* __restrict__ ST,
                  const TS* __restrict__ Cst, const TS* __restrict__ qT, double* __restrict__ V) {
     const int64_t z = (int64_t)blockIdx.x * 256 + threadIdx.x;
     if (z >= N) return;
     const double q = (double)qT[z];
     V[z] = q;
-    for (int p = p_lo; p < n; ++p) {
+    for (int k = 0; k < cnt; ++k) {                      // the owned bit positions p0, p0 + stride, ...
+        const int p = p0 + k * p_stride;
         const TS v = gamma * ((TS)1 - ST[z * np + p]);
-        V[(int64_t)(1 + p - p_lo) * N + z] = (double)(((z >> p) & 1) ? -v : v) * q;
+        V[(int64_t)(1 + k) * N + z] = (double)(((z >> p) & 1) ? -v : v) * q;
     }
-    if (with_c) V[(int64_t)(1 + n - p_lo) * N + z] = (double)Cst[z] * q;
+    if (with_c) V[(int64_t)(1 + cnt) * N + z] = (double)Cst[z] * q;
 }
 
 template <typename TS>
 __global__ void __launch_bounds__(256)
-hib_fold_kernel(int n, int np, int p_lo, int with_c, int64_t N, TS gamma, double a, const TS* __restrict__ ST,
+hib_fold_kernel(int n, int np, int p0, int p_stride, int cnt, int with_c, int64_t N, TS gamma, double a, const TS* __restrict__ ST,
                 const TS* __restrict__ Cst, const double* __restrict__ V, double* __restrict__ u) {
     const int64_t z = (int64_t)blockIdx.x * 256 + threadIdx.x;
     if (z >= N) return;
     const double inv = 1.0 / (1.0 - a * a);
     double acc = 0.0;
-    for (int p = p_lo; p < n; ++p) {
+    for (int k = 0; k < cnt; ++k) {
+        const int p = p0 + k * p_stride;
         const int64_t bitp = (int64_t)1 << p;
         const bool on = (z & bitp) != 0;
         const TS v = gamma * ((TS)1 - ST[z * np + p]);
         const double g = (double)(on ? -v : v);
         const double A = (on ? 1.0 : a) * (V[z | bitp] - a * V[z & ~bitp]) * inv;      // K(b_p .* q)_z from w = V[0]
         acc += g * A;
-        if (on) acc += V[(int64_t)(1 + p - p_lo) * N + z];                            // b_p(z) K(g_p .* q)_z
+        if (on) acc += V[(int64_t)(1 + k) * N + z];                                   // b_p(z) K(g_p .* q)_z
     }
-    if (with_c) acc += (double)Cst[z] * V[z] + V[(int64_t)(1 + n - p_lo) * N + z];     // sum_j a^h (C_z + C_j) q_j
+    if (with_c) acc += (double)Cst[z] * V[z] + V[(int64_t)(1 + cnt) * N + z];          // sum_j a^h (C_z + C_j) q_j
     u[z] = acc;
 }
 
 }  // namespace
 
-size_t tnk_hibits_ws_bytes(int n, int p_lo, int with_c) {
-    if (n <= p_lo && !with_c) return 0;
-    return (size_t)(1 + n - p_lo + (with_c ? 1 : 0)) * ((size_t)1 << n) * sizeof(double);
+// bit positions p_lo + share_offset + k * share_stride < n: the share of one call (rank) of a strided evaluation
+int tnk_hibits_count(int n, int p_lo, int share_offset, int share_stride) {
+    const int first = p_lo + share_offset;
+    return (share_offset < share_stride && first < n) ? (n - first + share_stride - 1) / share_stride : 0;
 }
 
-int tnk_hibits_pass(int n, int p_lo, int with_c, double a, double gamma, const void* ST, const void* Cst, const void* qT,
-                    int elem_bytes, double* u, double* ws, int* launches, cudaStream_t st) {
+size_t tnk_hibits_ws_bytes(int n, int p_lo, int with_c, int share_offset, int share_stride) {
+    const int cnt = tnk_hibits_count(n, p_lo, share_offset, share_stride);
+    if (cnt == 0 && !with_c) return 0;
+    return (size_t)(1 + cnt + (with_c ? 1 : 0)) * ((size_t)1 << n) * sizeof(double);
+}
+
+int tnk_hibits_pass(int n, int p_lo, int with_c, int share_offset, int share_stride, double a, double gamma, const void* ST,
+                    const void* Cst, const void* qT, int elem_bytes, double* u, double* ws, int* launches, cudaStream_t st) {
     const int64_t N = (int64_t)1 << n;
     const int np = ((n + 3) / 4) * 4;
-    const int nvec = 1 + n - p_lo + (with_c ? 1 : 0);
-    TNK_REQUIRE(n >= 7 && n <= 24 && p_lo >= 0 && p_lo <= n && ws, "tnk_hibits_pass: bad arguments n=%d p_lo=%d", n, p_lo);
+    TNK_REQUIRE(n >= 7 && n <= 24 && p_lo >= 0 && p_lo <= n && share_stride >= 1 && share_offset >= 0,
+                "tnk_hibits_pass: bad arguments n=%d p_lo=%d share=(%d,%d)", n, p_lo, share_offset, share_stride);
+    const int cnt = tnk_hibits_count(n, p_lo, share_offset, share_stride);
+    const int p0 = p_lo + share_offset;
+    if (cnt == 0 && !with_c) {           // nothing of the pass falls to this call: its partial starts at zero
+        TNK_CUDA_OK(cudaMemsetAsync(u, 0, (size_t)N * sizeof(double), st));
+        return 0;
+    }
+    TNK_REQUIRE(ws, "tnk_hibits_pass: NULL workspace");
+    const int nvec = 1 + cnt + (with_c ? 1 : 0);
     const unsigned blocks = (unsigned)((N + 255) / 256);
     if (elem_bytes == 4)
-        hib_build_kernel<float><<<blocks, 256, 0, st>>>(n, np, p_lo, with_c, N, (float)gamma, (const float*)ST, (const float*)Cst,
-                                                        (const float*)qT, ws);
+        hib_build_kernel<float><<<blocks, 256, 0, st>>>(n, np, p0, share_stride, cnt, with_c, N, (float)gamma, (const float*)ST,
+                                                        (const float*)Cst, (const float*)qT, ws);
     else
-        hib_build_kernel<double><<<blocks, 256, 0, st>>>(n, np, p_lo, with_c, N, gamma, (const double*)ST, (const double*)Cst,
-                                                         (const double*)qT, ws);
+        hib_build_kernel<double><<<blocks, 256, 0, st>>>(n, np, p0, share_stride, cnt, with_c, N, gamma, (const double*)ST,
+                                                         (const double*)Cst, (const double*)qT, ws);
     TNK_CUDA_OK(cudaGetLastError());
     TNK_CUDA_OK(cudaFuncSetAttribute(mp_transform_kernel<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMpSmem));
     // all n bits of every vector: bits [0, min(n,13)) on contiguous tiles, the rest on 2^g x 2^(13-g) tiles
@@ -635,9 +652,9 @@ int tnk_hibits_pass(int n, int p_lo, int with_c, double a, double gamma, const v
         ++nl;
     }
     if (elem_bytes == 4)
-        hib_fold_kernel<float><<<blocks, 256, 0, st>>>(n, np, p_lo, with_c, N, (float)gamma, a, (const float*)ST, (const float*)Cst, ws, u);
+        hib_fold_kernel<float><<<blocks, 256, 0, st>>>(n, np, p0, share_stride, cnt, with_c, N, (float)gamma, a, (const float*)ST, (const float*)Cst, ws, u);
     else
-        hib_fold_kernel<double><<<blocks, 256, 0, st>>>(n, np, p_lo, with_c, N, gamma, a, (const double*)ST, (const double*)Cst, ws, u);
+        hib_fold_kernel<double><<<blocks, 256, 0, st>>>(n, np, p0, share_stride, cnt, with_c, N, gamma, a, (const double*)ST, (const double*)Cst, ws, u);
     TNK_CUDA_OK(cudaGetLastError());
     if (launches) *launches += nl + 1;
     return 0;

@@ -392,11 +392,10 @@ int make_plan64(int n, int unit_offset, int unit_stride, Sym64Plan* p) {
     p->off_row = take((size_t)B * p->N * sizeof(double));
     p->off_col = take((size_t)B * p->N * sizeof(double));
     p->off_block = take((size_t)(p->finish_blocks + 1) * sizeof(double));
-    p->off_extra = p->off_hib = off;
-    if (unit_offset == 0) {              // the call that owns unit 0 adds the terms that left the pair kernel
-        p->off_extra = take((size_t)p->N * sizeof(double));
-        p->off_hib = take(tnk_hibits_ws_bytes(n, 0, 1));
-    }
+    // every call adds its share of the terms that left the pair kernel (Kronecker pass: bit positions offset, offset + stride,
+    // ...; the C terms with offset 0)
+    p->off_extra = take((size_t)p->N * sizeof(double));
+    p->off_hib = take(tnk_hibits_ws_bytes(n, 0, unit_offset == 0, unit_offset, unit_stride));
     p->total = off;
     return 0;
 }
@@ -481,9 +480,10 @@ extern "C" int tnk_ksd_sym64(int n_latent, double length_scale, const void* q, i
     ++launches;
 
     double* extra = nullptr;
-    if (unit_offset == 0) {
+    if (unit_offset == 0 || tnk_hibits_count(n, 0, unit_offset, unit_stride) > 0) {
         extra = (double*)(ws + p.off_extra);
-        const int rc_hi = tnk_hibits_pass(n, 0, 1, prm.a, prm.gamma, ST, Cst, qT, 8, extra, (double*)(ws + p.off_hib), &launches, st);
+        const int rc_hi = tnk_hibits_pass(n, 0, unit_offset == 0, unit_offset, unit_stride, prm.a, prm.gamma, ST, Cst, qT, 8, extra,
+                                          (double*)(ws + p.off_hib), &launches, st);
         if (rc_hi) return rc_hi;
     }
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;

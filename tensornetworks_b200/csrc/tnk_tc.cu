@@ -1660,9 +1660,11 @@ int tnk_tcs_launch(int n, int fmt, double gamma, const double* wl, const float* 
         TNK_CUDA_OK(cudaGetLastError());
         if (launches) *launches += 1;
     }
-    if ((fmt == 3 || (fmt == 2 && n > 7)) && tile_offset == 0) {
-        // the terms that left the pair kernel, for ALL rows, once (the call that owns row tile 0 adds them)
-        const int rc_hi = tnk_hibits_pass(n, fmt == 3 ? 0 : 7, fmt == 3, wl[1], gamma, ST, Cst, qT, 4, ucol, hibits_ws, launches, st);
+    if (fmt == 3 || (fmt == 2 && n > 7)) {
+        // the terms that left the pair kernel, for ALL rows: this call's share of the bit positions (the calls of one stride
+        // split the pass between them; offset 0 also takes the C terms), written into ucol before the tile kernel adds its part
+        const int rc_hi = tnk_hibits_pass(n, fmt == 3 ? 0 : 7, fmt == 3 && tile_offset == 0, tile_offset, tile_stride, wl[1], gamma,
+                                          ST, Cst, qT, 4, ucol, hibits_ws, launches, st);
         if (rc_hi) return rc_hi;
     } else {
         TNK_CUDA_OK(cudaMemsetAsync(ucol, 0, (size_t)N * sizeof(double), st));

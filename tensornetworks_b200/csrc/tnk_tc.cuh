@@ -101,7 +101,11 @@ int tnk_tcs_launch(int n, int fmt, double gamma, const double* wl, const float* 
 // Formats 2, 3 of the symmetric variant: u[z] = the terms of ALL pairs (z, j) that left the pair kernel - the T1/T2 terms of
 // the bit positions p >= p_lo, g_p(z) K(b_p .* q)_z + b_p(z) K(g_p .* q)_z, and (with_c) C(z) K(q)_z + K(C .* q)_z -
 // through 1 + n - p_lo (+1) fp64 Kronecker transforms (tnk_modeprod.cu).
+// The pass is linear in its terms, so a strided evaluation splits it: the call with share (offset, stride) takes the bit
+// positions p_lo + offset + k * stride (and, with_c, the C terms - the caller gives them to offset 0); every call needs
+// w = K q itself.  offset >= stride or no bit left: the call only zeroes u.
 // ws: tnk_hibits_ws_bytes bytes.  Overwrites u (the tile kernel then adds the remaining terms).
-size_t tnk_hibits_ws_bytes(int n, int p_lo, int with_c);
-int tnk_hibits_pass(int n, int p_lo, int with_c, double a, double gamma, const void* ST, const void* Cst, const void* qT,
-                    int elem_bytes, double* u, double* ws, int* launches, cudaStream_t st);
+int tnk_hibits_count(int n, int p_lo, int share_offset, int share_stride);
+size_t tnk_hibits_ws_bytes(int n, int p_lo, int with_c, int share_offset, int share_stride);
+int tnk_hibits_pass(int n, int p_lo, int with_c, int share_offset, int share_stride, double a, double gamma, const void* ST,
+                    const void* Cst, const void* qT, int elem_bytes, double* u, double* ws, int* launches, cudaStream_t st);
