@@ -154,7 +154,7 @@ class SteinTables:
           "bf16x2"    the whole bracket, two bf16 pieces per factor (10 K-steps, errors ~1e-5)
           "tf32_tile" the T1/T2 terms of the bit positions >= 7 leave the pair kernel (9 K-steps)
           "tf32_dot"  only the score dot product stays in the pair kernel (6 K-steps); for both, the removed terms are
-                      added for all rows by a pass of fp64 Kronecker transforms (O(n^2 2^n), in the call owning tile 0).
+                      added for all rows by a pass of fp64 Kronecker transforms (O(n^2 2^n); the calls of one stride split it between them).
         out: optional (u [N], part [1]) fp64 device tensors to write into (e.g. views of PeerComm.sendbuf)."""
         split = DEFAULT_SYM_SPLIT if split is None else split
         if split not in _lib.SYM_SPLIT:
