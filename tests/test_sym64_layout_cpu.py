@@ -88,3 +88,31 @@ def test_unit_enumeration_is_a_bijection():
             assert pa * B - pa * (pa - 1) // 2 + (pb - pa) == k
             seen.add((pa, pb))
         assert len(seen) == B * (B + 1) // 2
+
+
+@pytest.mark.parametrize("n,G", [(9, 2), (10, 3), (9, 8), (8, 16)])
+def test_side_pass_shares_add_up(n, G):
+    """The Kronecker side pass is dealt over the G calls of a stride (tnk_hibits_pass: share g takes the bit positions
+    g, g + G, ...; share 0 also the C terms; shares beyond the last bit are empty): the shares must add up to the whole."""
+    S, N, a_, z, s, bit, g, C = _setup(n, random_binary_bn)
+    q = random_q(N, seed=n).numpy()
+    wl = np.exp(-np.arange(n + 1) / n)
+    Kb = wl[_popc(z[:, None] ^ z[None, :])]
+    T = sum(np.outer(g[:, p], bit[:, p]) + np.outer(bit[:, p], g[:, p]) for p in range(n)) + C[:, None] + C[None, :]
+    want = (Kb * T) @ q
+    w = Kb @ q
+    total = np.zeros(N)
+    owned = []
+    for share in range(G):
+        bits = list(range(share, n, G))
+        owned += bits
+        part = np.zeros(N)
+        for p in bits:
+            on = bit[:, p].astype(bool)
+            A = np.where(on, 1.0, a_) * (w[z | (1 << p)] - a_ * w[z & ~(1 << p)]) / (1.0 - a_ * a_)
+            part += g[:, p] * A + np.where(on, Kb @ (g[:, p] * q), 0.0)
+        if share == 0:
+            part += C * w + Kb @ (C * q)
+        total += part
+    assert sorted(owned) == list(range(n))
+    assert np.max(np.abs(total - want)) <= 1e-12 * np.max(np.abs(want))
