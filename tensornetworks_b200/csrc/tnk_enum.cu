@@ -1,6 +1,7 @@
 // Enumeration kernels: K1 joint table p(x,z) and K2 score / packed-table builder.
 // HBM-bound streaming kernels over the 2^n packed states (one thread per state).
 #include "tnk_common.cuh"
+#include <type_traits>
 
 static thread_local char g_err[512] = "";
 
@@ -135,7 +136,9 @@ __device__ __forceinline__ double div_by(double a, double p, double rp) {
 constexpr int kScoreRows = 64;    // states per CTA of the score kernel
 // NN = n when it is a compile-time constant of the instance (NP - 3 <= n <= NP, n >= 1: the k < n tests, the flip masks
 // and the copy-out strides fold), -1 = run-time n (n = 0).
-template <typename T, int NP, int NN>
+// KEEP: S64 is written too, so the staging tile holds doubles; without it the tile holds the packed table's own type
+// (a third of the shared memory for fp32 tables: full occupancy for the gathers).
+template <typename T, int NP, int NN, bool KEEP>
 __global__ void __launch_bounds__(kScoreRows)
 score_kernel(int n_rt, int64_t N, double alpha, double gamma,
              const double* __restrict__ P, double* __restrict__ S64,
@@ -144,7 +147,8 @@ score_kernel(int n_rt, int64_t N, double alpha, double gamma,
     // copy-outs then walk the tile linearly.
     constexpr int kStride = NP + 1;
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    double* sS = reinterpret_cast<double*>(smem_raw);                                          // [kScoreRows][NP+1]
+    using E = typename std::conditional<KEEP, double, T>::type;
+    E* sS = reinterpret_cast<E*>(smem_raw);                                                    // [kScoreRows][NP+1]
     const int n = NN >= 0 ? NN : n_rt;
     const int tid = threadIdx.x;
     const int64_t base = (int64_t)blockIdx.x * kScoreRows;
@@ -175,24 +179,24 @@ score_kernel(int n_rt, int64_t N, double alpha, double gamma,
                     Rsum += r;
                     if ((iu >> bit) & 1u) rho0 += r;
                 }
-                sS[tid * kStride + k] = s;                                 // zero beyond n and in dead rows
+                sS[tid * kStride + k] = (E)s;                              // zero beyond n and in dead rows
             }
         }
         if (Cst) Cst[i] = (T)(alpha * Rsum + gamma * rho0);
     } else {
 #pragma unroll
-        for (int k = 0; k < NP; ++k) sS[tid * kStride + k] = 0.0;          // padding rows of the packed table
+        for (int k = 0; k < NP; ++k) sS[tid * kStride + k] = (E)0;         // padding rows of the packed table
         if (Cst) Cst[i] = (T)0;
     }
     __syncthreads();
-    if (S64 && n > 0) {
+    if (KEEP && n > 0) {
         const int live = (int)(N - base < kScoreRows ? (N - base > 0 ? N - base : 0) : kScoreRows) * n;
         const int dq = kScoreRows / n, dr = kScoreRows % n;  // element t = tid + kScoreRows j sits in row t / n, column t % n
         int row = tid / n, col = tid % n;
         double* out = S64 + base * n;
 #pragma unroll
         for (int t = tid; t < live; t += kScoreRows) {
-            __stcs(out + t, sS[row * kStride + col]);     // streaming stores: the tables must not evict P from L2
+            __stcs(out + t, (double)sS[row * kStride + col]);   // streaming stores: the tables must not evict P from L2
             row += dq; col += dr;
             if (col >= n) { col -= n; ++row; }
         }
@@ -222,9 +226,15 @@ template <typename T, int NP, int NN>
 int launch_score_n(int n, int64_t N, int64_t rows, double alpha, double gamma, const double* P, double* S64,
                    T* ST, T* Cst, cudaStream_t st) {
     const unsigned blocks = (unsigned)((rows + kScoreRows - 1) / kScoreRows);
-    const size_t smem = (size_t)kScoreRows * (NP + 1) * sizeof(double);
-    TNK_CUDA_OK(cudaFuncSetAttribute(score_kernel<T, NP, NN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    score_kernel<T, NP, NN><<<blocks, kScoreRows, smem, st>>>(n, N, alpha, gamma, P, S64, ST, Cst);
+    if (S64) {
+        const size_t smem = (size_t)kScoreRows * (NP + 1) * sizeof(double);
+        TNK_CUDA_OK(cudaFuncSetAttribute(score_kernel<T, NP, NN, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        score_kernel<T, NP, NN, true><<<blocks, kScoreRows, smem, st>>>(n, N, alpha, gamma, P, S64, ST, Cst);
+    } else {
+        const size_t smem = (size_t)kScoreRows * (NP + 1) * sizeof(T);
+        TNK_CUDA_OK(cudaFuncSetAttribute(score_kernel<T, NP, NN, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        score_kernel<T, NP, NN, false><<<blocks, kScoreRows, smem, st>>>(n, N, alpha, gamma, P, S64, ST, Cst);
+    }
     TNK_CUDA_OK(cudaGetLastError());
     return 0;
 }
